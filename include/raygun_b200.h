@@ -1,0 +1,190 @@
+/* raygun_b200.h -- C ABI of libraygun_b200.so (sm_100a only).
+ *
+ * This is the drop-in boundary of the B200-native hot path of htem/raygun: the 3D
+ * convolution forward/backward, normalisation, activation, pooling, skip and loss
+ * arithmetic that the reference obtains from torch.nn (-> cuDNN / ATen).  The
+ * reference has no FFI of its own (it is pure Python); the seam is the set of
+ * torch.nn call sites inside raygun.torch.networks / losses / predict.worker.
+ * Every entry point below cites the reference call site it replaces
+ * (paths relative to /root/reference/src/raygun/torch unless noted).
+ *
+ * Conventions
+ *  - plain pointers + sizes only; all pointers are DEVICE pointers unless named h_*.
+ *  - every function returns int: 0 = ok, negative = RG_E_*; text via rg_last_error().
+ *  - every launch is asynchronous on the caller's cudaStream_t (passed as void*).
+ *  - the library never allocates user-visible memory; the caller owns all tensors.
+ *  - tensors are described by rg_tensor5 (logical N,C,D,H,W + element strides), so the
+ *    same entry points serve NCDHW fp32 and NDHWC (channels-last-3d) bf16 storage.
+ */
+#ifndef RAYGUN_B200_H
+#define RAYGUN_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RG_VERSION 100
+
+enum { RG_OK = 0, RG_E_BADARG = -1, RG_E_UNSUPPORTED = -2, RG_E_CUDA = -3, RG_E_ARCH = -4 };
+enum { RG_F32 = 0, RG_BF16 = 1, RG_U8 = 2 };
+enum { RG_ACT_NONE = 0, RG_ACT_RELU = 1, RG_ACT_LEAKY = 2, RG_ACT_TANH = 3, RG_ACT_SIGMOID = 4 };
+enum { RG_PAD_ZEROS = 0, RG_PAD_REFLECT = 1, RG_PAD_REPLICATE = 2 };
+enum { RG_NORM_INSTANCE = 0, RG_NORM_BATCH = 1 };
+enum { RG_LOSS_MSE_CONST = 0, RG_LOSS_SMOOTHL1 = 1, RG_LOSS_L1 = 2, RG_LOSS_MEAN = 3 };
+
+/* Logical (N,C,D,H,W) tensor view: sizes + strides in ELEMENTS + dtype. */
+typedef struct rg_tensor5 {
+  int64_t n, c, d, h, w;
+  int64_t sn, sc, sd, sh, sw;
+  int32_t dtype; /* RG_F32 | RG_BF16 | RG_U8 */
+  int32_t _pad;
+} rg_tensor5;
+
+/* Geometry of one Conv3d / ConvTranspose3d (zero padding only: reflect / replicate
+ * shells are materialised by rg_pad3d, as the reference does with F.pad / *Pad3d). */
+typedef struct rg_conv_geom {
+  int32_t kernel[3];  /* kD,kH,kW */
+  int32_t stride[3];
+  int32_t pad[3];     /* zero padding, per side */
+  int32_t groups;     /* UNet.py:75-83 x_init_map uses groups=min(Cin,Cout) */
+  int32_t act;        /* fused epilogue activation RG_ACT_* (fprop only) */
+  float slope;        /* LeakyReLU negative slope */
+} rg_conv_geom;
+
+/* ---- library ------------------------------------------------------------------- */
+int rg_version(void);
+const char* rg_last_error(void);          /* thread-local message of the last failure */
+int rg_device_check(int device);          /* RG_E_ARCH unless the device is sm_100   */
+
+/* ---- direct (CUDA-core, fp32-accumulate) convolutions ---------------------------
+ * Replace nn.Conv3d / nn.ConvTranspose3d forward+backward for ANY shape
+ * (UNet.py:61-69,75-83,150-165,265-269; ResNet.py:271-338,407-416;
+ *  NLayerDiscriminator.py:137-174; systems/BaseSystem.py:209-224).  Weights are the
+ * checkpoint-layout fp32 tensors: Conv3d [Cout,Cin/g,kD,kH,kW]; ConvTranspose3d is
+ * expressed through the same three kernels (its forward is dgrad of the conv whose
+ * weight it shares: [Cin_T,Cout_T,k...] == [Cout_conv,Cin_conv,k...]).
+ * x / y / dy / dx may be f32 or bf16 in any strided layout; accumulation is fp32. */
+int rg_conv3d_direct_fprop(const rg_tensor5* xd, const void* x, const float* w, const float* bias,
+                           const rg_tensor5* yd, void* y, const rg_conv_geom* g, void* stream);
+int rg_conv3d_direct_dgrad(const rg_tensor5* dyd, const void* dy, const float* w, const float* bias,
+                           const rg_tensor5* dxd, void* dx, const rg_conv_geom* g, void* stream);
+/* dw (fp32, [Cout,Cin/g,kD,kH,kW]) must be zeroed by the caller unless accumulate!=0;
+ * dbias may be NULL. */
+int rg_conv3d_direct_wgrad(const rg_tensor5* xd, const void* x, const rg_tensor5* dyd, const void* dy,
+                           float* dw, float* dbias, const rg_conv_geom* g, int accumulate, void* stream);
+
+/* ---- tcgen05 / TMEM / TMA implicit-GEMM convolutions (bf16 NDHWC, fp32 accumulate) --
+ * The performance path for the same call sites when Cin%64==0 and Cout%16==0.
+ * A plan owns the CUtensorMap descriptors of one (layer, shape) pair. */
+typedef struct rg_plan rg_plan;
+
+typedef struct rg_igemm_desc {
+  int32_t mode;        /* 0 = fprop, 1 = dgrad (also ConvTranspose3d forward), 2 = wgrad */
+  int32_t n, cin, cout;          /* of the CONVOLUTION (fprop direction)             */
+  int32_t in_dhw[3], out_dhw[3]; /* fprop input / output spatial extents             */
+  int32_t kernel[3], stride[3], pad[3];
+  /* element strides of the bf16 NDHWC buffers (channel stride must be 1)            */
+  int64_t x_strides[4];  /* n,d,h,w of the fprop-input-side tensor  (x or dx)        */
+  int64_t y_strides[4];  /* n,d,h,w of the fprop-output-side tensor (y or dy)        */
+  int32_t act; float slope;      /* fused epilogue activation (fprop / convT fwd)    */
+  int32_t has_bias, want_stats;  /* epilogue: +bias[c]; accumulate sum / sumsq [n,c] */
+  int32_t out_f32;               /* write fp32 instead of bf16 (unused: reserved)    */
+} rg_igemm_desc;
+
+int rg_plan_create(const rg_igemm_desc* desc, rg_plan** out);
+int rg_plan_destroy(rg_plan* plan);
+size_t rg_plan_workspace_bytes(const rg_plan* plan);
+/* Re-pack fp32 checkpoint weights [Cout,Cin,kD,kH,kW] into the bf16 K-major layouts the
+ * plans read: fprop pack [Cout][tap][Cin]; dgrad pack [Cin][tap][Cout].             */
+int rg_pack_weights(const float* w, int cout, int cin, int taps, void* w_fprop_bf16, void* w_dgrad_bf16,
+                    void* stream);
+/* in -> out of the plan's mode.  fprop: in = x, out = y.  dgrad: in = dy, out = dx.
+ * stats_sum/sumsq: fp32 [n*cout] accumulators (zeroed by caller) or NULL.           */
+int rg_igemm_run(const rg_plan* plan, const void* in, const void* w_packed, const float* bias, void* out,
+                 float* stats_sum, float* stats_sqsum, void* workspace, void* stream);
+/* wgrad: dw fp32 [Cout,Cin,kD,kH,kW] (+= ; caller zeroes), dbias optional.          */
+int rg_igemm_wgrad(const rg_plan* plan, const void* x, const void* dy, float* dw, float* dbias,
+                   void* workspace, void* stream);
+
+/* ---- data movement: strided copy / cast / crop / concat-slice ------------------------
+ * Replaces the reference's center `crop` + torch.cat (UNet.py:327-351), ResNet crop
+ * (ResNet.py:436-443), dtype/layout casts and .float() (predict/worker.py:101-107).
+ * dst[i] (+)= src[i] over the logical shape of dst (src must have the same shape).  */
+int rg_copy5(const rg_tensor5* dd, void* dst, const rg_tensor5* sd, const void* src, int accumulate,
+             void* stream);
+
+/* ---- padding (nn.ReflectionPad3d / ReplicationPad3d / F.pad; ResNet.py:270-279,392-401,
+ *      UNet.py:61-69 padding_mode="reflect") and its adjoint ----------------------------*/
+int rg_pad3d_fwd(const rg_tensor5* xd, const void* x, const rg_tensor5* yd, void* y,
+                 const int32_t lo[3], int mode, void* stream);
+/* dx (zeroed by caller) += fold(dy) */
+int rg_pad3d_bwd(const rg_tensor5* dyd, const void* dy, const rg_tensor5* dxd, void* dx,
+                 const int32_t lo[3], int mode, void* stream);
+
+/* ---- normalisation (nn.InstanceNorm3d / nn.BatchNorm3d; ResNet.py:236,284,299,334,408,417;
+ *      NLayerDiscriminator.py:112,146-168; UNet.py:84-88) --------------------------------
+ * stats: sum[g], sqsum[g] (fp32, zeroed by caller) with g = n*C+c (instance) or c (batch). */
+int rg_norm_stats(const rg_tensor5* xd, const void* x, int kind, float* sum, float* sqsum, void* stream);
+/* mean/rstd from sum/sqsum: count elements per group, biased variance, eps inside sqrt. */
+int rg_norm_finalize(const float* sum, const float* sqsum, int groups, double count, float eps,
+                     float* mean, float* rstd, float* var_out, void* stream);
+/* y = act((x-mean)*rstd*gamma+beta (+ residual)); gamma/beta/residual may be NULL.
+ * kind selects how mean/rstd are indexed (per (n,c) or per c).                       */
+int rg_norm_apply(const rg_tensor5* xd, const void* x, int kind, const float* mean, const float* rstd,
+                  const float* gamma, const float* beta, const rg_tensor5* rd, const void* residual,
+                  int act, float slope, const rg_tensor5* yd, void* y, void* stream);
+/* Backward of y = act(norm(x)): needs x, dy and (for act!=NONE) y.  Two launches inside:
+ * reductions (sum g, sum g*xhat per group; dgamma/dbeta) then the dx pass.
+ * red: fp32 scratch [2*groups], zeroed by caller.  training=0 -> statistics are constants. */
+int rg_norm_bwd(const rg_tensor5* xd, const void* x, const rg_tensor5* dyd, const void* dy,
+                const rg_tensor5* yd, const void* y, int kind, int training, const float* mean,
+                const float* rstd, const float* gamma, int act, float slope, float* red,
+                float* dgamma, float* dbeta, const rg_tensor5* dxd, void* dx, void* stream);
+
+/* ---- activations (nn.ReLU / LeakyReLU(0.2) / Tanh / Sigmoid; UNet.py:41-47,
+ *      NLayerDiscriminator.py:138, BaseSystem.py:175-176) -------------------------------*/
+int rg_act_fwd(const rg_tensor5* xd, const void* x, int act, float slope, const rg_tensor5* yd, void* y,
+               void* stream);
+/* dx = dy * act'(.) evaluated from the OUTPUT y (valid for all four supported kinds). */
+int rg_act_bwd(const rg_tensor5* yd, const void* y, const rg_tensor5* dyd, const void* dy, int act,
+               float slope, const rg_tensor5* dxd, void* dx, void* stream);
+
+/* ---- pooling / nearest up-sampling (UNet.py:209-218 MaxPool3d; UNet.py:273 nn.Upsample) --*/
+int rg_maxpool3d_fwd(const rg_tensor5* xd, const void* x, const int32_t f[3], const rg_tensor5* yd, void* y,
+                     void* stream);
+/* dx must be zeroed by the caller when the input is not an exact multiple of f. First max wins. */
+int rg_maxpool3d_bwd(const rg_tensor5* xd, const void* x, const rg_tensor5* yd, const void* y,
+                     const rg_tensor5* dyd, const void* dy, const int32_t f[3], const rg_tensor5* dxd,
+                     void* dx, void* stream);
+int rg_upsample_nearest_fwd(const rg_tensor5* xd, const void* x, const int32_t f[3], const rg_tensor5* yd,
+                            void* y, void* stream);
+int rg_upsample_nearest_bwd(const rg_tensor5* dyd, const void* dy, const int32_t f[3], const rg_tensor5* dxd,
+                            void* dx, void* stream);
+
+/* ---- losses (losses/GANLoss.py:24-25,48-64 MSELoss vs constant label;
+ *      losses/LinkCycleLoss.py:22,99-105 SmoothL1Loss / L1Loss), warp-shuffle reductions ----
+ * loss[0] += scale_loss * mean(f(a, b|target)); grad_a = scale_grad * d mean/da (may be NULL).
+ * b is ignored for MSE_CONST / MEAN (target used instead).  a,b share a logical shape.  */
+int rg_loss_fwd_grad(int kind, const rg_tensor5* ad, const void* a, const rg_tensor5* bd, const void* b,
+                     float target, float beta, float scale_loss, float* loss, float scale_grad,
+                     const rg_tensor5* gd, void* grad_a, void* stream);
+
+/* ---- blockwise prediction arithmetic (predict/worker.py:100-114 and :133-147) ---------- */
+/* y = (float(u8) - 0) / 255 * scale + shift */
+int rg_u8_normalise(const uint8_t* x, int64_t count, float scale, float shift, int out_dtype, void* y,
+                    void* stream);
+/* out = uint8(trunc(clamp(x*255, 0, 255))) over a cropped strided view */
+int rg_denorm_clamp_u8(const rg_tensor5* xd, const void* x, uint8_t* out, void* stream);
+
+/* ---- optimiser (torch.optim.Adam call sites losses/LinkCycleLoss.py:78,128) -------------
+ * One fused pass over a flat fp32 parameter bucket: m,v,p update (no amsgrad, no decay). */
+int rg_adam_step(float* p, const float* g, float* m, float* v, int64_t count, float lr, float beta1,
+                 float beta2, float eps, int step, float grad_scale, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RAYGUN_B200_H */

@@ -1,0 +1,236 @@
+// HBM-bound kernels of the hot path: strided copy/cast/crop, padding (+adjoint), activations,
+// max-pool, nearest up-sampling, u8 normalise / denormalise, fused Adam.
+// All kernels are grid-stride loops sized to a multiple of the 148 SMs; the loop order follows the
+// innermost storage dimension of the destination so that stores (and usually loads) coalesce.
+#include "common.cuh"
+
+namespace rg {
+
+// ------------------------------------------------------------------------------------------
+// copy5: dst (+)= src over dst's logical shape
+// ------------------------------------------------------------------------------------------
+template <typename TS, typename TD>
+__global__ void copy5_kernel(T5 dd, TD* __restrict__ dst, T5 sd, const TS* __restrict__ src, bool c_inner,
+                             bool accumulate) {
+  long long total = dd.numel();
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    Idx5 p = unravel(i, dd, c_inner);
+    float v = ldf(src + sd.off(p.n, p.c, p.d, p.h, p.w));
+    TD* q = dst + dd.off(p.n, p.c, p.d, p.h, p.w);
+    if (accumulate) v += ldf(q);
+    stf(q, v);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// padding
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ long long pad_src(long long o, long long lo, long long size, int mode, bool& valid) {
+  long long i = o - lo;
+  valid = true;
+  if (i >= 0 && i < size) return i;
+  if (mode == RG_PAD_REFLECT) {
+    if (i < 0) i = -i;
+    if (i >= size) i = 2 * (size - 1) - i;
+    return i;
+  }
+  if (mode == RG_PAD_REPLICATE) return i < 0 ? 0 : size - 1;
+  valid = false;
+  return 0;
+}
+
+template <typename TS, typename TD>
+__global__ void pad_fwd_kernel(T5 xd, const TS* __restrict__ x, T5 yd, TD* __restrict__ y, int lo_d, int lo_h,
+                               int lo_w, int mode, bool c_inner) {
+  long long total = yd.numel();
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    Idx5 p = unravel(i, yd, c_inner);
+    bool vd, vh, vw;
+    long long id = pad_src(p.d, lo_d, xd.d, mode, vd);
+    long long ih = pad_src(p.h, lo_h, xd.h, mode, vh);
+    long long iw = pad_src(p.w, lo_w, xd.w, mode, vw);
+    float v = (vd && vh && vw) ? ldf(x + xd.off(p.n, p.c, id, ih, iw)) : 0.f;
+    stf(y + yd.off(p.n, p.c, p.d, p.h, p.w), v);
+  }
+}
+
+// Adjoint of pad: gather formulation (deterministic).  For every input voxel, sum the up-to-27
+// padded-output positions that read it.  Per dimension an input index i is read by o = i+lo and, for
+// reflect, by the mirror images about both faces; for replicate, border voxels absorb the whole shell.
+__device__ __forceinline__ int pad_preimages(long long i, long long lo, long long size, long long osize, int mode,
+                                             long long* out, int* rep_lo, int* rep_hi) {
+  int cnt = 0;
+  *rep_lo = 0; *rep_hi = 0;
+  long long o = i + lo;
+  if (o >= 0 && o < osize) out[cnt++] = o;
+  if (mode == RG_PAD_REFLECT) {
+    long long o1 = lo - i;                    // mirror about the low face (i>0)
+    if (i > 0 && o1 >= 0 && o1 < lo) out[cnt++] = o1;
+    long long o2 = lo + 2 * (size - 1) - i;   // mirror about the high face (i<size-1)
+    if (i < size - 1 && o2 >= lo + size && o2 < osize) out[cnt++] = o2;
+  } else if (mode == RG_PAD_REPLICATE) {
+    if (i == 0) *rep_lo = (int)lo;
+    if (i == size - 1) *rep_hi = (int)(osize - lo - size);
+  }
+  return cnt;
+}
+
+template <typename TS, typename TD>
+__global__ void pad_bwd_kernel(T5 dyd, const TS* __restrict__ dy, T5 dxd, TD* __restrict__ dx, int lo_d, int lo_h,
+                               int lo_w, int mode, bool c_inner) {
+  long long total = dxd.numel();
+  for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    Idx5 p = unravel(idx, dxd, c_inner);
+    // enumerate pre-images per dimension (explicit lists; replicate shells expanded as ranges)
+    long long od[3 + 0], oh[3], ow[3];
+    int rl, rh;
+    long long ld[64], lh[64], lw[64];
+    int nd = 0, nh = 0, nw = 0;
+    int c = pad_preimages(p.d, lo_d, dxd.d, dyd.d, mode, od, &rl, &rh);
+    for (int k = 0; k < c; ++k) ld[nd++] = od[k];
+    for (int k = 0; k < rl && nd < 64; ++k) ld[nd++] = k;
+    for (int k = 0; k < rh && nd < 64; ++k) ld[nd++] = lo_d + dxd.d + k;
+    c = pad_preimages(p.h, lo_h, dxd.h, dyd.h, mode, oh, &rl, &rh);
+    for (int k = 0; k < c; ++k) lh[nh++] = oh[k];
+    for (int k = 0; k < rl && nh < 64; ++k) lh[nh++] = k;
+    for (int k = 0; k < rh && nh < 64; ++k) lh[nh++] = lo_h + dxd.h + k;
+    c = pad_preimages(p.w, lo_w, dxd.w, dyd.w, mode, ow, &rl, &rh);
+    for (int k = 0; k < c; ++k) lw[nw++] = ow[k];
+    for (int k = 0; k < rl && nw < 64; ++k) lw[nw++] = k;
+    for (int k = 0; k < rh && nw < 64; ++k) lw[nw++] = lo_w + dxd.w + k;
+    float acc = 0.f;
+    for (int a = 0; a < nd; ++a)
+      for (int b = 0; b < nh; ++b)
+        for (int e = 0; e < nw; ++e) acc += ldf(dy + dyd.off(p.n, p.c, ld[a], lh[b], lw[e]));
+    TD* q = dx + dxd.off(p.n, p.c, p.d, p.h, p.w);
+    stf(q, acc + ldf(q));
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// activations
+// ------------------------------------------------------------------------------------------
+template <typename TS, typename TD>
+__global__ void act_fwd_kernel(T5 xd, const TS* __restrict__ x, T5 yd, TD* __restrict__ y, int act, float slope,
+                               bool c_inner) {
+  long long total = yd.numel();
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    Idx5 p = unravel(i, yd, c_inner);
+    float v = ldf(x + xd.off(p.n, p.c, p.d, p.h, p.w));
+    stf(y + yd.off(p.n, p.c, p.d, p.h, p.w), act_apply(v, act, slope));
+  }
+}
+
+template <typename TY, typename TG, typename TD>
+__global__ void act_bwd_kernel(T5 yd, const TY* __restrict__ y, T5 gd, const TG* __restrict__ dy, T5 dxd,
+                               TD* __restrict__ dx, int act, float slope, bool c_inner) {
+  long long total = dxd.numel();
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    Idx5 p = unravel(i, dxd, c_inner);
+    float yy = ldf(y + yd.off(p.n, p.c, p.d, p.h, p.w));
+    float g = ldf(dy + gd.off(p.n, p.c, p.d, p.h, p.w));
+    stf(dx + dxd.off(p.n, p.c, p.d, p.h, p.w), g * act_grad_from_y(yy, act, slope));
+  }
+}
+
+}  // namespace rg
+
+using namespace rg;
+
+extern "C" {
+
+int rg_copy5(const rg_tensor5* dd, void* dst, const rg_tensor5* sd, const void* src, int accumulate,
+             void* stream) {
+  RG_CHECK_ARG(dd && sd && dst && src, "rg_copy5: null argument");
+  RG_CHECK_ARG(same_shape(dd, sd), "rg_copy5: shape mismatch");
+  long long total = view(dd).numel();
+  if (total == 0) return RG_OK;
+  bool ci = channels_inner(dd);
+  cudaStream_t st = (cudaStream_t)stream;
+  int grid = grid_for(total, 256);
+  RG_DISPATCH_FLOAT(sd->dtype, TS, RG_DISPATCH_FLOAT(dd->dtype, TD, {
+    copy5_kernel<TS, TD><<<grid, 256, 0, st>>>(view(dd), (TD*)dst, view(sd), (const TS*)src, ci, accumulate != 0);
+  }))
+  RG_LAUNCH_CHECK("rg_copy5");
+  return RG_OK;
+}
+
+int rg_pad3d_fwd(const rg_tensor5* xd, const void* x, const rg_tensor5* yd, void* y, const int32_t lo[3],
+                 int mode, void* stream) {
+  RG_CHECK_ARG(xd && yd && x && y && lo, "rg_pad3d_fwd: null argument");
+  RG_CHECK_ARG(xd->n == yd->n && xd->c == yd->c, "rg_pad3d_fwd: N/C mismatch");
+  RG_CHECK_ARG(mode >= RG_PAD_ZEROS && mode <= RG_PAD_REPLICATE, "rg_pad3d_fwd: bad mode %d", mode);
+  if (mode == RG_PAD_REFLECT) {
+    // nn.ReflectionPad3d requires pad < size in every dimension
+    RG_CHECK_ARG(lo[0] < xd->d && lo[1] < xd->h && lo[2] < xd->w &&
+                 yd->d - xd->d - lo[0] < xd->d && yd->h - xd->h - lo[1] < xd->h && yd->w - xd->w - lo[2] < xd->w,
+                 "rg_pad3d_fwd: reflect padding must be smaller than the input");
+  }
+  long long total = view(yd).numel();
+  if (total == 0) return RG_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  int grid = grid_for(total, 256);
+  bool ci = channels_inner(yd);
+  RG_DISPATCH_FLOAT(xd->dtype, TS, RG_DISPATCH_FLOAT(yd->dtype, TD, {
+    pad_fwd_kernel<TS, TD><<<grid, 256, 0, st>>>(view(xd), (const TS*)x, view(yd), (TD*)y, lo[0], lo[1], lo[2], mode, ci);
+  }))
+  RG_LAUNCH_CHECK("rg_pad3d_fwd");
+  return RG_OK;
+}
+
+int rg_pad3d_bwd(const rg_tensor5* dyd, const void* dy, const rg_tensor5* dxd, void* dx, const int32_t lo[3],
+                 int mode, void* stream) {
+  RG_CHECK_ARG(dyd && dxd && dy && dx && lo, "rg_pad3d_bwd: null argument");
+  RG_CHECK_ARG(dxd->n == dyd->n && dxd->c == dyd->c, "rg_pad3d_bwd: N/C mismatch");
+  RG_CHECK_ARG(lo[0] < 30 && lo[1] < 30 && lo[2] < 30, "rg_pad3d_bwd: pad too large");
+  long long total = view(dxd).numel();
+  if (total == 0) return RG_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  int grid = grid_for(total, 128);
+  bool ci = channels_inner(dxd);
+  RG_DISPATCH_FLOAT(dyd->dtype, TS, RG_DISPATCH_FLOAT(dxd->dtype, TD, {
+    pad_bwd_kernel<TS, TD><<<grid, 128, 0, st>>>(view(dyd), (const TS*)dy, view(dxd), (TD*)dx, lo[0], lo[1], lo[2], mode, ci);
+  }))
+  RG_LAUNCH_CHECK("rg_pad3d_bwd");
+  return RG_OK;
+}
+
+int rg_act_fwd(const rg_tensor5* xd, const void* x, int act, float slope, const rg_tensor5* yd, void* y,
+               void* stream) {
+  RG_CHECK_ARG(xd && yd && x && y, "rg_act_fwd: null argument");
+  RG_CHECK_ARG(same_shape(xd, yd), "rg_act_fwd: shape mismatch");
+  long long total = view(yd).numel();
+  if (total == 0) return RG_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  int grid = grid_for(total, 256);
+  bool ci = channels_inner(yd);
+  RG_DISPATCH_FLOAT(xd->dtype, TS, RG_DISPATCH_FLOAT(yd->dtype, TD, {
+    act_fwd_kernel<TS, TD><<<grid, 256, 0, st>>>(view(xd), (const TS*)x, view(yd), (TD*)y, act, slope, ci);
+  }))
+  RG_LAUNCH_CHECK("rg_act_fwd");
+  return RG_OK;
+}
+
+int rg_act_bwd(const rg_tensor5* yd, const void* y, const rg_tensor5* dyd, const void* dy, int act, float slope,
+               const rg_tensor5* dxd, void* dx, void* stream) {
+  RG_CHECK_ARG(yd && dyd && dxd && y && dy && dx, "rg_act_bwd: null argument");
+  RG_CHECK_ARG(same_shape(yd, dyd) && same_shape(yd, dxd), "rg_act_bwd: shape mismatch");
+  RG_CHECK_ARG(yd->dtype == dyd->dtype, "rg_act_bwd: y / dy dtype mismatch");
+  long long total = view(dxd).numel();
+  if (total == 0) return RG_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  int grid = grid_for(total, 256);
+  bool ci = channels_inner(dxd);
+  RG_DISPATCH_FLOAT(yd->dtype, TS, RG_DISPATCH_FLOAT(dxd->dtype, TD, {
+    act_bwd_kernel<TS, TS, TD><<<grid, 256, 0, st>>>(view(yd), (const TS*)y, view(dyd), (const TS*)dy, view(dxd), (TD*)dx, act, slope, ci);
+  }))
+  RG_LAUNCH_CHECK("rg_act_bwd");
+  return RG_OK;
+}
+
+}  // extern "C"

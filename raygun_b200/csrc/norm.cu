@@ -1,0 +1,285 @@
+// InstanceNorm3d / BatchNorm3d: statistics, apply (fused activation + residual), backward.
+// HBM-bound: stats 1 read; apply 1 read + 1 write; backward = 1 reduction pass (x, dy, y) + 1 pass.
+#include "common.cuh"
+
+namespace rg {
+
+struct NormCtx {
+  int kind;            // RG_NORM_INSTANCE | RG_NORM_BATCH
+  int act; float slope;
+  const float* mean; const float* rstd; const float* gamma;
+};
+
+__device__ __forceinline__ int group_of(int kind, long long n, long long c, long long C) {
+  return kind == RG_NORM_INSTANCE ? (int)(n * C + c) : (int)c;
+}
+
+// MODE 0: (x, x^2).  MODE 1: (g, g*xhat) with g = dy * act'(y).
+template <int MODE, typename TX, typename TG>
+__device__ __forceinline__ void red_terms(const NormCtx& cx, int grp, const T5& xd, const TX* x, const T5& gd,
+                                          const TG* dy, const T5& yd, const TG* y, long long n, long long c,
+                                          long long d, long long h, long long w, float& a, float& b) {
+  float xv = ldf(x + xd.off(n, c, d, h, w));
+  if (MODE == 0) {
+    a = xv; b = xv * xv;
+  } else {
+    float g = ldf(dy + gd.off(n, c, d, h, w));
+    if (cx.act != RG_ACT_NONE) g *= act_grad_from_y(ldf(y + yd.off(n, c, d, h, w)), cx.act, cx.slope);
+    float xhat = (xv - cx.mean[grp]) * cx.rstd[grp];
+    a = g; b = g * xhat;
+  }
+}
+
+// W-innermost storage: blockIdx.y = (n*C+c), blockIdx.x = chunk of the D*H*W extent.
+template <int MODE, typename TX, typename TG>
+__global__ void reduce2_w_inner(NormCtx cx, T5 xd, const TX* __restrict__ x, T5 gd, const TG* __restrict__ dy, T5 yd,
+                                const TG* __restrict__ y, float* __restrict__ out0, float* __restrict__ out1) {
+  long long n = blockIdx.y / xd.c, c = blockIdx.y % xd.c;
+  int grp = group_of(cx.kind, n, c, xd.c);
+  long long vox = xd.d * xd.h * xd.w;
+  float s0 = 0.f, s1 = 0.f;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < vox;
+       i += (long long)gridDim.x * blockDim.x) {
+    long long w = i % xd.w, t = i / xd.w;
+    long long h = t % xd.h, d = t / xd.h;
+    float a, b;
+    red_terms<MODE>(cx, grp, xd, x, gd, dy, yd, y, n, c, d, h, w, a, b);
+    s0 += a; s1 += b;
+  }
+  __shared__ float sh0[32], sh1[32];
+  s0 = warp_sum(s0); s1 = warp_sum(s1);
+  int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  if (lane == 0) { sh0[wid] = s0; sh1[wid] = s1; }
+  __syncthreads();
+  if (wid == 0) {
+    int nw = blockDim.x >> 5;
+    s0 = lane < nw ? sh0[lane] : 0.f; s1 = lane < nw ? sh1[lane] : 0.f;
+    s0 = warp_sum(s0); s1 = warp_sum(s1);
+    if (lane == 0) { atomicAdd(out0 + grp, s0); atomicAdd(out1 + grp, s1); }
+  }
+}
+
+// C-innermost storage (NDHWC): blockIdx.y = n, blockIdx.x = chunk of voxels.  Lane = channel
+// within a 32-channel tile, warps stride over voxels; cross-warp reduce in smem; one atomic per
+// (block, channel).
+template <int MODE, typename TX, typename TG>
+__global__ void reduce2_c_inner(NormCtx cx, T5 xd, const TX* __restrict__ x, T5 gd, const TG* __restrict__ dy, T5 yd,
+                                const TG* __restrict__ y, float* __restrict__ out0, float* __restrict__ out1,
+                                long long vox_per_block) {
+  long long n = blockIdx.y;
+  long long vox = xd.d * xd.h * xd.w;
+  long long v0 = blockIdx.x * vox_per_block;
+  long long v1 = v0 + vox_per_block < vox ? v0 + vox_per_block : vox;
+  int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  __shared__ float sh0[8][33], sh1[8][33];
+  for (long long c0 = 0; c0 < xd.c; c0 += 32) {
+    long long c = c0 + lane;
+    float s0 = 0.f, s1 = 0.f;
+    if (c < xd.c) {
+      int grp = group_of(cx.kind, n, c, xd.c);
+      for (long long i = v0 + wid; i < v1; i += nw) {
+        long long w = i % xd.w, t = i / xd.w;
+        long long h = t % xd.h, d = t / xd.h;
+        float a, b;
+        red_terms<MODE>(cx, grp, xd, x, gd, dy, yd, y, n, c, d, h, w, a, b);
+        s0 += a; s1 += b;
+      }
+    }
+    sh0[wid][lane] = s0; sh1[wid][lane] = s1;
+    __syncthreads();
+    if (wid == 0 && c < xd.c) {
+      for (int k = 1; k < nw; ++k) { s0 += sh0[k][lane]; s1 += sh1[k][lane]; }
+      int grp = group_of(cx.kind, n, c, xd.c);
+      atomicAdd(out0 + grp, s0); atomicAdd(out1 + grp, s1);
+    }
+    __syncthreads();
+  }
+}
+
+__global__ void finalize_kernel(const float* __restrict__ sum, const float* __restrict__ sq, int groups, double count,
+                                float eps, float* __restrict__ mean, float* __restrict__ rstd, float* __restrict__ var_out) {
+  int g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= groups) return;
+  double m = (double)sum[g] / count;
+  double v = (double)sq[g] / count - m * m;
+  if (v < 0.0) v = 0.0;
+  mean[g] = (float)m;
+  rstd[g] = (float)(1.0 / sqrt(v + (double)eps));
+  if (var_out) var_out[g] = (float)v;
+}
+
+template <typename TX, typename TR, typename TY>
+__global__ void norm_apply_kernel(NormCtx cx, const float* __restrict__ beta, T5 xd, const TX* __restrict__ x, T5 rd,
+                                  const TR* __restrict__ res, T5 yd, TY* __restrict__ y, bool c_inner) {
+  long long total = yd.numel();
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    Idx5 p = unravel(i, yd, c_inner);
+    float v = ldf(x + xd.off(p.n, p.c, p.d, p.h, p.w));
+    if (cx.mean) {
+      int grp = group_of(cx.kind, p.n, p.c, xd.c);
+      v = (v - cx.mean[grp]) * cx.rstd[grp];
+    }
+    if (cx.gamma) v = v * cx.gamma[p.c];
+    if (beta) v += beta[p.c];
+    if (res) v += ldf(res + rd.off(p.n, p.c, p.d, p.h, p.w));
+    stf(y + yd.off(p.n, p.c, p.d, p.h, p.w), act_apply(v, cx.act, cx.slope));
+  }
+}
+
+template <typename TX, typename TG, typename TD>
+__global__ void norm_bwd_dx_kernel(NormCtx cx, int training, const float* __restrict__ red, float inv_count, T5 xd,
+                                   const TX* __restrict__ x, T5 gd, const TG* __restrict__ dy, T5 yd,
+                                   const TG* __restrict__ y, T5 dxd, TD* __restrict__ dx, int groups, bool c_inner) {
+  long long total = dxd.numel();
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    Idx5 p = unravel(i, dxd, c_inner);
+    int grp = group_of(cx.kind, p.n, p.c, xd.c);
+    float g = ldf(dy + gd.off(p.n, p.c, p.d, p.h, p.w));
+    if (cx.act != RG_ACT_NONE) g *= act_grad_from_y(ldf(y + yd.off(p.n, p.c, p.d, p.h, p.w)), cx.act, cx.slope);
+    float gam = cx.gamma ? cx.gamma[p.c] : 1.f;
+    float r = cx.rstd[grp];
+    float out;
+    if (training) {
+      float xhat = (ldf(x + xd.off(p.n, p.c, p.d, p.h, p.w)) - cx.mean[grp]) * r;
+      out = gam * r * (g - red[grp] * inv_count - xhat * red[groups + grp] * inv_count);
+    } else {
+      out = gam * r * g;
+    }
+    stf(dx + dxd.off(p.n, p.c, p.d, p.h, p.w), out);
+  }
+}
+
+// dgamma[c] = sum_n S2[n,c]; dbeta[c] = sum_n S1[n,c]
+__global__ void affine_grad_kernel(const float* __restrict__ red, int kind, int N, int C, int groups,
+                                   float* __restrict__ dgamma, float* __restrict__ dbeta) {
+  int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  float a = 0.f, b = 0.f;
+  if (kind == RG_NORM_INSTANCE) {
+    for (int n = 0; n < N; ++n) { a += red[n * C + c]; b += red[groups + n * C + c]; }
+  } else {
+    a = red[c]; b = red[groups + c];
+  }
+  if (dbeta) dbeta[c] = a;
+  if (dgamma) dgamma[c] = b;
+}
+
+template <int MODE, typename TX, typename TG>
+static int launch_reduce2(const NormCtx& cx, const rg_tensor5* xd, const TX* x, const rg_tensor5* gd, const TG* dy,
+                          const rg_tensor5* yd, const TG* y, float* out0, float* out1, cudaStream_t st) {
+  T5 xv = view(xd), gv = gd ? view(gd) : xv, yv = yd ? view(yd) : xv;
+  long long vox = xv.d * xv.h * xv.w;
+  if (channels_inner(xd)) {
+    long long blocks_x = (148LL * 8 + xv.n - 1) / xv.n;
+    long long vpb = (vox + blocks_x - 1) / blocks_x;
+    if (vpb < 64) vpb = 64;
+    blocks_x = (vox + vpb - 1) / vpb;
+    dim3 grid((unsigned)blocks_x, (unsigned)xv.n);
+    reduce2_c_inner<MODE, TX, TG><<<grid, 256, 0, st>>>(cx, xv, x, gv, dy, yv, y, out0, out1, vpb);
+  } else {
+    long long groups = xv.n * xv.c;
+    long long bx = (148LL * 8 + groups - 1) / groups;
+    long long maxbx = (vox + 1023) / 1024;
+    if (bx > maxbx) bx = maxbx;
+    if (bx < 1) bx = 1;
+    RG_CHECK_ARG(groups <= 65535, "norm reduce: N*C=%lld exceeds grid.y limit", groups);
+    dim3 grid((unsigned)bx, (unsigned)groups);
+    reduce2_w_inner<MODE, TX, TG><<<grid, 256, 0, st>>>(cx, xv, x, gv, dy, yv, y, out0, out1);
+  }
+  return RG_OK;
+}
+
+}  // namespace rg
+
+using namespace rg;
+
+extern "C" {
+
+int rg_norm_stats(const rg_tensor5* xd, const void* x, int kind, float* sum, float* sqsum, void* stream) {
+  RG_CHECK_ARG(xd && x && sum && sqsum, "rg_norm_stats: null argument");
+  RG_CHECK_ARG(kind == RG_NORM_INSTANCE || kind == RG_NORM_BATCH, "rg_norm_stats: bad kind");
+  if (view(xd).numel() == 0) return RG_OK;
+  NormCtx cx{kind, RG_ACT_NONE, 0.f, nullptr, nullptr, nullptr};
+  cudaStream_t st = (cudaStream_t)stream;
+  int rc = RG_OK;
+  RG_DISPATCH_FLOAT(xd->dtype, TX, {
+    rc = launch_reduce2<0, TX, TX>(cx, xd, (const TX*)x, nullptr, nullptr, nullptr, nullptr, sum, sqsum, st);
+  })
+  if (rc) return rc;
+  RG_LAUNCH_CHECK("rg_norm_stats");
+  return RG_OK;
+}
+
+int rg_norm_finalize(const float* sum, const float* sqsum, int groups, double count, float eps, float* mean,
+                     float* rstd, float* var_out, void* stream) {
+  RG_CHECK_ARG(sum && sqsum && mean && rstd && groups > 0 && count > 0, "rg_norm_finalize: bad argument");
+  finalize_kernel<<<(groups + 127) / 128, 128, 0, (cudaStream_t)stream>>>(sum, sqsum, groups, count, eps, mean, rstd, var_out);
+  RG_LAUNCH_CHECK("rg_norm_finalize");
+  return RG_OK;
+}
+
+int rg_norm_apply(const rg_tensor5* xd, const void* x, int kind, const float* mean, const float* rstd,
+                  const float* gamma, const float* beta, const rg_tensor5* rd, const void* residual, int act,
+                  float slope, const rg_tensor5* yd, void* y, void* stream) {
+  RG_CHECK_ARG(xd && x && yd && y, "rg_norm_apply: null argument");
+  RG_CHECK_ARG(same_shape(xd, yd), "rg_norm_apply: shape mismatch");
+  RG_CHECK_ARG((mean == nullptr) == (rstd == nullptr), "rg_norm_apply: mean/rstd must come together");
+  if (residual) RG_CHECK_ARG(rd && same_shape(xd, rd), "rg_norm_apply: residual shape mismatch");
+  long long total = view(yd).numel();
+  if (total == 0) return RG_OK;
+  NormCtx cx{kind, act, slope, mean, rstd, gamma};
+  cudaStream_t st = (cudaStream_t)stream;
+  int grid = grid_for(total, 256);
+  bool ci = channels_inner(yd);
+  int rdt = residual ? rd->dtype : xd->dtype;
+  T5 rv = residual ? view(rd) : view(xd);
+  RG_DISPATCH_FLOAT(xd->dtype, TX, RG_DISPATCH_FLOAT(rdt, TR, RG_DISPATCH_FLOAT(yd->dtype, TY, {
+    norm_apply_kernel<TX, TR, TY><<<grid, 256, 0, st>>>(cx, beta, view(xd), (const TX*)x, rv, (const TR*)residual, view(yd), (TY*)y, ci);
+  })))
+  RG_LAUNCH_CHECK("rg_norm_apply");
+  return RG_OK;
+}
+
+int rg_norm_bwd(const rg_tensor5* xd, const void* x, const rg_tensor5* dyd, const void* dy, const rg_tensor5* yd,
+                const void* y, int kind, int training, const float* mean, const float* rstd, const float* gamma,
+                int act, float slope, float* red, float* dgamma, float* dbeta, const rg_tensor5* dxd, void* dx,
+                void* stream) {
+  RG_CHECK_ARG(xd && x && dyd && dy && mean && rstd && red, "rg_norm_bwd: null argument");
+  RG_CHECK_ARG(same_shape(xd, dyd), "rg_norm_bwd: shape mismatch");
+  if (act != RG_ACT_NONE) RG_CHECK_ARG(yd && y && same_shape(xd, yd) && yd->dtype == dyd->dtype, "rg_norm_bwd: y required for fused activation");
+  if (dx) RG_CHECK_ARG(dxd && same_shape(xd, dxd), "rg_norm_bwd: dx shape mismatch");
+  T5 xv = view(xd);
+  if (xv.numel() == 0) return RG_OK;
+  int groups = kind == RG_NORM_INSTANCE ? (int)(xv.n * xv.c) : (int)xv.c;
+  double count = kind == RG_NORM_INSTANCE ? (double)(xv.d * xv.h * xv.w) : (double)(xv.n * xv.d * xv.h * xv.w);
+  NormCtx cx{kind, act, slope, mean, rstd, gamma};
+  cudaStream_t st = (cudaStream_t)stream;
+  int rc = RG_OK;
+  bool need_red = training || dgamma || dbeta;
+  if (need_red) {
+    RG_DISPATCH_FLOAT(xd->dtype, TX, RG_DISPATCH_FLOAT(dyd->dtype, TG, {
+      rc = launch_reduce2<1, TX, TG>(cx, xd, (const TX*)x, dyd, (const TG*)dy, yd, (const TG*)y, red, red + groups, st);
+    }))
+    if (rc) return rc;
+    RG_LAUNCH_CHECK("rg_norm_bwd reduce");
+    if (dgamma || dbeta) {
+      affine_grad_kernel<<<(int)((xv.c + 127) / 128), 128, 0, st>>>(red, kind, (int)xv.n, (int)xv.c, groups, dgamma, dbeta);
+      RG_LAUNCH_CHECK("rg_norm_bwd affine");
+    }
+  }
+  if (dx) {
+    long long total = xv.numel();
+    int grid = grid_for(total, 256);
+    bool ci = channels_inner(dxd);
+    T5 yv = (yd && y) ? view(yd) : xv;
+    RG_DISPATCH_FLOAT(xd->dtype, TX, RG_DISPATCH_FLOAT(dyd->dtype, TG, RG_DISPATCH_FLOAT(dxd->dtype, TD, {
+      norm_bwd_dx_kernel<TX, TG, TD><<<grid, 256, 0, st>>>(cx, training, red, (float)(1.0 / count), xv, (const TX*)x, view(dyd), (const TG*)dy, yv, (const TG*)y, view(dxd), (TD*)dx, groups, ci);
+    })))
+    RG_LAUNCH_CHECK("rg_norm_bwd dx");
+  }
+  return RG_OK;
+}
+
+}  // extern "C"
