@@ -1,0 +1,201 @@
+"""Convolution dispatch: tcgen05 implicit GEMM (bf16 NDHWC) when eligible, direct kernels otherwise.
+
+Weights are always the checkpoint-layout fp32 tensors (``[Cout, Cin/g, kD, kH, kW]``); the bf16
+K-major packs the tensor-core kernels read are derived caches, re-packed when the parameter's
+version counter changes (i.e. after every optimizer step), never serialised.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import weakref
+
+import torch
+
+from . import _C
+from . import kernels as K
+from ._C import ACT_NONE, ConvGeom, IgemmDesc, check, count_launch, i3, lib, ptr, require_device, stream_ptr, t5
+
+stats = {"igemm": 0, "direct": 0}     # which path convolutions took (tests / bench inspect this)
+
+
+def _geom(kernel, stride, pad, groups=1, act=ACT_NONE, slope=0.0):
+    g = ConvGeom()
+    g.kernel[:] = [int(k) for k in kernel]
+    g.stride[:] = [int(s) for s in stride]
+    g.pad[:] = [int(p) for p in pad]
+    g.groups, g.act, g.slope = int(groups), int(act), float(slope)
+    return g
+
+
+def out_size(i, k, s, p):
+    return (i + 2 * p - k) // s + 1
+
+
+# --------------------------------------------------------------------------------------------
+# packed-weight and plan caches
+# --------------------------------------------------------------------------------------------
+_packs: "dict[int, tuple]" = {}
+
+
+def packed_weights(w: torch.Tensor):
+    """(w_fprop [Cout][tap][Cin], w_dgrad [Cin][tap][Cout]) bf16 packs of a conv-layout weight."""
+    key = id(w)
+    ent = _packs.get(key)
+    ver = w._version
+    if ent is not None and ent[0]() is w and ent[1] == ver and ent[2] == w.data_ptr():
+        return ent[3], ent[4]
+    cout, cin = w.shape[0], w.shape[1]
+    taps = w.shape[2] * w.shape[3] * w.shape[4]
+    wsrc = w.detach()
+    if not wsrc.is_contiguous():
+        wsrc = wsrc.contiguous()
+    wf = torch.empty(cout, taps, cin, dtype=torch.bfloat16, device=w.device)
+    wd = torch.empty(cin, taps, cout, dtype=torch.bfloat16, device=w.device)
+    check(lib().rg_pack_weights(ptr(wsrc), C.c_int(cout), C.c_int(cin), C.c_int(taps), ptr(wf), ptr(wd),
+                                stream_ptr(w.device)), "rg_pack_weights")
+    count_launch()
+    if len(_packs) > 4096:
+        for k in [k for k, e in _packs.items() if e[0]() is None]:
+            del _packs[k]
+    _packs[key] = (weakref.ref(w), ver, w.data_ptr(), wf, wd)
+    return wf, wd
+
+
+class _Plan:
+    def __init__(self, handle):
+        self.handle = handle
+
+    def __del__(self):
+        try:
+            if self.handle:
+                lib().rg_plan_destroy(self.handle)
+        except Exception:
+            pass
+
+
+_plans: "dict[tuple, _Plan | None]" = {}
+
+
+def _get_plan(mode, n, cin, cout, in_dhw, out_dhw, kernel, stride, pad, xs, ys, act, slope):
+    key = (mode, n, cin, cout, tuple(in_dhw), tuple(out_dhw), tuple(kernel), tuple(stride), tuple(pad), tuple(xs),
+           tuple(ys), act, slope)
+    if key in _plans:
+        return _plans[key]
+    d = IgemmDesc()
+    d.mode, d.n, d.cin, d.cout = mode, n, cin, cout
+    d.in_dhw[:] = list(in_dhw)
+    d.out_dhw[:] = list(out_dhw)
+    d.kernel[:] = list(kernel)
+    d.stride[:] = list(stride)
+    d.pad[:] = list(pad)
+    d.x_strides[:] = list(xs)
+    d.y_strides[:] = list(ys)
+    d.act, d.slope = act, slope
+    handle = C.c_void_p()
+    rc = lib().rg_plan_create(C.byref(d), C.byref(handle))
+    if rc == _C.E_UNSUPPORTED:
+        _plans[key] = None
+        return None
+    check(rc, "rg_plan_create")
+    _plans[key] = _Plan(handle)
+    return _plans[key]
+
+
+def _sp_strides(t):
+    s = t.stride()
+    return (s[0], s[2], s[3], s[4])
+
+
+def _igemm_ok(cin, cout, kernel, stride, groups):
+    return (K.get_precision() == "bf16" and K.use_tensor_cores() and groups == 1 and cin % 64 == 0
+            and cout % 64 == 0 and all(s in (1, 2) for s in stride) and all(1 <= k <= 8 for k in kernel))
+
+
+# --------------------------------------------------------------------------------------------
+# the three convolution kernels, as raw tensor functions
+# --------------------------------------------------------------------------------------------
+def conv_fprop(x, w, bias, stride, pad, groups=1, act=ACT_NONE, slope=0.0, want_stats=False, out_dtype=None):
+    """y = act(conv3d(x, w) + bias) with zero padding `pad`.  Returns (y, sum, sqsum) -- the two
+    per-(n,cout) statistics are None unless want_stats and the tensor-core epilogue produced them."""
+    require_device(x)
+    n, cin_t, d, h, wd_ = x.shape
+    cout = w.shape[0]
+    kernel = tuple(w.shape[2:])
+    od = [out_size(i, k, s, p) for i, k, s, p in zip((d, h, wd_), kernel, stride, pad)]
+    if min(od) < 1:
+        raise RuntimeError(f"conv3d: kernel {kernel} does not fit input {tuple(x.shape)}")
+    cdt = out_dtype or K.compute_dtype()
+    bias_f = bias.detach() if bias is not None else None
+    if _igemm_ok(cin_t, cout, kernel, stride, groups) and cdt == torch.bfloat16:
+        xb = K.convert(x, torch.bfloat16)
+        y = K.empty5((n, cout, *od), torch.bfloat16, x.device)
+        plan = _get_plan(0, n, cin_t, cout, (d, h, wd_), od, kernel, stride, pad, _sp_strides(xb), _sp_strides(y),
+                         act, float(slope))
+        if plan is not None:
+            wf, _ = packed_weights(w)
+            st = torch.zeros(2, n * cout, dtype=torch.float32, device=x.device) if want_stats else None
+            check(lib().rg_igemm_run(plan.handle, ptr(xb), ptr(wf), ptr(bias_f), ptr(y),
+                                     ptr(st[0]) if want_stats else None, ptr(st[1]) if want_stats else None, None,
+                                     stream_ptr(x.device)), "rg_igemm_run(fprop)")
+            count_launch()
+            stats["igemm"] += 1
+            return (y, st[0], st[1]) if want_stats else (y, None, None)
+    y = K.empty5((n, cout, *od), cdt, x.device)
+    g = _geom(kernel, stride, pad, groups, act, slope)
+    wc = w.detach()
+    if not wc.is_contiguous():
+        wc = wc.contiguous()
+    check(lib().rg_conv3d_direct_fprop(C.byref(t5(x)), ptr(x), ptr(wc), ptr(bias_f), C.byref(t5(y)), ptr(y),
+                                       C.byref(g), stream_ptr(x.device)), "rg_conv3d_direct_fprop")
+    count_launch(groups)
+    stats["direct"] += 1
+    return y, None, None
+
+
+def conv_dgrad(dy, w, x_shape, stride, pad, groups=1, bias=None, act=ACT_NONE, slope=0.0, want_stats=False,
+               out_dtype=None):
+    """dx of the conv whose weight is `w` ([Cout,Cin/g,k..]); also ConvTranspose3d forward
+    (then `bias`/`act` are the transposed conv's epilogue and x_shape its output shape)."""
+    require_device(dy)
+    n, cout_t, od, oh, ow = dy.shape
+    cin_t = x_shape[1]
+    kernel = tuple(w.shape[2:])
+    cdt = out_dtype or K.compute_dtype()
+    bias_f = bias.detach() if bias is not None else None
+    if _igemm_ok(cin_t, cout_t, kernel, stride, groups) and cdt == torch.bfloat16:
+        dyb = K.convert(dy, torch.bfloat16)
+        dx = K.empty5(tuple(x_shape), torch.bfloat16, dy.device)
+        plan = _get_plan(1, n, cin_t, cout_t, tuple(x_shape[2:]), (od, oh, ow), kernel, stride, pad, _sp_strides(dx),
+                         _sp_strides(dyb), act, float(slope))
+        if plan is not None:
+            _, wdp = packed_weights(w)
+            st = torch.zeros(2, n * cin_t, dtype=torch.float32, device=dy.device) if want_stats else None
+            check(lib().rg_igemm_run(plan.handle, ptr(dyb), ptr(wdp), ptr(bias_f), ptr(dx),
+                                     ptr(st[0]) if want_stats else None, ptr(st[1]) if want_stats else None, None,
+                                     stream_ptr(dy.device)), "rg_igemm_run(dgrad)")
+            count_launch(stride[0] * stride[1] * stride[2])
+            stats["igemm"] += 1
+            return (dx, st[0], st[1]) if want_stats else (dx, None, None)
+    dx = K.empty5(tuple(x_shape), cdt, dy.device)
+    g = _geom(kernel, stride, pad, groups, act, slope)
+    wc = w.detach()
+    if not wc.is_contiguous():
+        wc = wc.contiguous()
+    check(lib().rg_conv3d_direct_dgrad(C.byref(t5(dy)), ptr(dy), ptr(wc), ptr(bias_f), C.byref(t5(dx)), ptr(dx),
+                                       C.byref(g), stream_ptr(dy.device)), "rg_conv3d_direct_dgrad")
+    count_launch(groups)
+    stats["direct"] += 1
+    return dx, None, None
+
+
+def conv_wgrad(x, dy, w_shape, stride, pad, groups=1, want_bias=False):
+    """dw (fp32, conv layout) and optionally dbias = sum(dy)."""
+    require_device(x)
+    dw = torch.empty(tuple(w_shape), dtype=torch.float32, device=x.device)
+    db = torch.empty(w_shape[0], dtype=torch.float32, device=x.device) if want_bias else None
+    g = _geom(tuple(w_shape[2:]), stride, pad, groups)
+    check(lib().rg_conv3d_direct_wgrad(C.byref(t5(x)), ptr(x), C.byref(t5(dy)), ptr(dy), ptr(dw), ptr(db),
+                                       C.byref(g), C.c_int(0), stream_ptr(x.device)), "rg_conv3d_direct_wgrad")
+    count_launch(groups)
+    stats["direct"] += 1
+    return dw, db

@@ -1,0 +1,400 @@
+"""Autograd layer: ``torch.autograd.Function`` wrappers around the sm_100a kernels.
+
+Each Function is the replacement of one torch.nn call site of the reference (cited per class).
+Forward and backward both run hand-written kernels only; autograd is used for graph bookkeeping.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import conv as CV
+from . import kernels as K
+from ._C import (ACT_LEAKY, ACT_NONE, ACT_RELU, ACT_SIGMOID, ACT_TANH, LOSS_L1, LOSS_MEAN, LOSS_MSE_CONST, LOSS_SMOOTHL1,
+                 NORM_BATCH, NORM_INSTANCE, PAD_REFLECT, PAD_REPLICATE, PAD_ZEROS)
+
+PAD_MODES = {"zeros": PAD_ZEROS, "constant": PAD_ZEROS, "reflect": PAD_REFLECT, "replicate": PAD_REPLICATE}
+
+
+def _t3(v):
+    return (int(v),) * 3 if isinstance(v, int) else tuple(int(a) for a in v)
+
+
+# ---------------------------------------------------------------------------------------------
+# casts
+# ---------------------------------------------------------------------------------------------
+class _Cast(torch.autograd.Function):
+    """dtype / layout change (reference: implicit; predict/worker.py:101-107 .float())."""
+
+    @staticmethod
+    def forward(ctx, x, dtype):
+        ctx.src_dtype = x.dtype
+        return K.convert(x, dtype)
+
+    @staticmethod
+    def backward(ctx, dy):
+        return K.convert(dy, ctx.src_dtype), None
+
+
+def cast(x, dtype):
+    if x.dtype == dtype and (K.is_ndhwc(x) if dtype == torch.bfloat16 else x.is_contiguous()):
+        return x
+    return _Cast.apply(x, dtype)
+
+
+def to_compute(x):
+    """Bring an input into the storage of the active precision mode."""
+    return cast(x, K.compute_dtype())
+
+
+# ---------------------------------------------------------------------------------------------
+# convolution
+# ---------------------------------------------------------------------------------------------
+class _Conv3d(torch.autograd.Function):
+    """nn.Conv3d forward/backward with zero padding and a fused activation epilogue
+    (UNet.py:61-69, ResNet.py:271-298,407-416, NLayerDiscriminator.py:137-174, BaseSystem.py:209-224).
+    Returns (y, sum, sqsum): the statistics feed the following norm layer (non-differentiable)."""
+
+    @staticmethod
+    def forward(ctx, x, w, bias, stride, pad, groups, act, slope, want_stats):
+        y, s, q = CV.conv_fprop(x, w, bias, stride, pad, groups, act, slope, want_stats)
+        ctx.geom = (stride, pad, groups, act, slope)
+        ctx.has_bias = bias is not None
+        ctx.save_for_backward(x, w, y if act != ACT_NONE else None)
+        if s is None:
+            s = q = x.new_empty(0, dtype=torch.float32)
+        ctx.mark_non_differentiable(s, q)
+        return y, s, q
+
+    @staticmethod
+    def backward(ctx, dy, _ds, _dq):
+        x, w, y = ctx.saved_tensors
+        stride, pad, groups, act, slope = ctx.geom
+        if act != ACT_NONE:
+            dy = K.act_bwd(y, dy, act, slope)
+        dx = dw = db = None
+        if ctx.needs_input_grad[0]:
+            dx, _, _ = CV.conv_dgrad(dy, w, x.shape, stride, pad, groups, out_dtype=x.dtype)
+        if ctx.needs_input_grad[1] or (ctx.has_bias and ctx.needs_input_grad[2]):
+            dw, db = CV.conv_wgrad(x, dy, w.shape, stride, pad, groups, want_bias=ctx.has_bias)
+            if not ctx.needs_input_grad[1]:
+                dw = None
+        return dx, dw, db, None, None, None, None, None, None
+
+
+def conv3d(x, w, bias=None, stride=1, padding=0, groups=1, act=ACT_NONE, slope=0.0, want_stats=False):
+    y, s, q = _Conv3d.apply(x, w, bias, _t3(stride), _t3(padding), int(groups), act, float(slope), bool(want_stats))
+    if want_stats:
+        return y, (s, q) if s.numel() else None
+    return y
+
+
+class _ConvTranspose3d(torch.autograd.Function):
+    """nn.ConvTranspose3d (UNet.py:265-269 k=s=factor; ResNet.py:325-333 k3 s2 p1 op1).
+    Forward is the data-gradient kernel of the conv that shares the weight [Cin_T, Cout_T, k..]."""
+
+    @staticmethod
+    def forward(ctx, x, w, bias, stride, pad, out_pad, act, slope, want_stats):
+        n, cin, d, h, wd_ = x.shape
+        k = w.shape[2:]
+        osz = [(i - 1) * s - 2 * p + kk + op for i, s, p, kk, op in zip((d, h, wd_), stride, pad, k, out_pad)]
+        y, s, q = CV.conv_dgrad(x, w, (n, w.shape[1], *osz), stride, pad, 1, bias=bias, act=act, slope=slope,
+                                want_stats=want_stats)
+        ctx.geom = (stride, pad, act, slope)
+        ctx.has_bias = bias is not None
+        ctx.save_for_backward(x, w, y if act != ACT_NONE else None)
+        if s is None:
+            s = q = x.new_empty(0, dtype=torch.float32)
+        ctx.mark_non_differentiable(s, q)
+        return y, s, q
+
+    @staticmethod
+    def backward(ctx, dy, _ds, _dq):
+        x, w, y = ctx.saved_tensors
+        stride, pad, act, slope = ctx.geom
+        if act != ACT_NONE:
+            dy = K.act_bwd(y, dy, act, slope)
+        dx = dw = db = None
+        if ctx.needs_input_grad[0]:
+            dx, _, _ = CV.conv_fprop(dy, w, None, stride, pad, 1, out_dtype=x.dtype)
+        if ctx.needs_input_grad[1] or (ctx.has_bias and ctx.needs_input_grad[2]):
+            # conv' : dy (Cout_T) -> x (Cin_T); its wgrad has "x" = dy and "dy" = x; bias grad = sum(dy)
+            dw, _ = CV.conv_wgrad(dy, x, w.shape, stride, pad, 1, want_bias=False)
+            if ctx.has_bias:
+                s, _ = K.norm_stats(dy, NORM_BATCH)
+                db = s
+            if not ctx.needs_input_grad[1]:
+                dw = None
+        return dx, dw, db, None, None, None, None, None, None
+
+
+def conv_transpose3d(x, w, bias=None, stride=1, padding=0, output_padding=0, act=ACT_NONE, slope=0.0,
+                     want_stats=False):
+    y, s, q = _ConvTranspose3d.apply(x, w, bias, _t3(stride), _t3(padding), _t3(output_padding), act, float(slope),
+                                     bool(want_stats))
+    if want_stats:
+        return y, (s, q) if s.numel() else None
+    return y
+
+
+# ---------------------------------------------------------------------------------------------
+# padding
+# ---------------------------------------------------------------------------------------------
+class _Pad3d(torch.autograd.Function):
+    """nn.ReflectionPad3d / ReplicationPad3d / F.pad (ResNet.py:270-279,392-401; Conv3d padding_mode)."""
+
+    @staticmethod
+    def forward(ctx, x, lo, hi, mode):
+        ctx.args = (tuple(x.shape), lo, mode)
+        return K.pad3d(x, lo, hi, mode)
+
+    @staticmethod
+    def backward(ctx, dy):
+        shape, lo, mode = ctx.args
+        return K.pad3d_bwd(dy, shape, lo, mode), None, None, None
+
+
+def pad3d(x, lo, hi=None, mode="reflect"):
+    lo = _t3(lo)
+    hi = lo if hi is None else _t3(hi)
+    if not any(lo) and not any(hi):
+        return x
+    return _Pad3d.apply(x, lo, hi, PAD_MODES[mode] if isinstance(mode, str) else mode)
+
+
+# ---------------------------------------------------------------------------------------------
+# normalisation (+ fused activation and residual add)
+# ---------------------------------------------------------------------------------------------
+class _NormAct(torch.autograd.Function):
+    """y = act(norm(x) * gamma + beta [+ residual]).  nn.InstanceNorm3d / nn.BatchNorm3d
+    (ResNet.py:236-417, NLayerDiscriminator.py:146-168, UNet.py:84-88) fused with the activation
+    that follows it and with the ResnetBlock skip add (ResNet.py:436-443).
+    kind None = no normalisation (plain `act(x + residual)`)."""
+
+    @staticmethod
+    def forward(ctx, x, kind, mean, rstd, gamma, beta, residual, act, slope, training):
+        y = K.norm_apply(x, kind if kind is not None else NORM_INSTANCE, mean, rstd, gamma, beta, residual, act, slope)
+        ctx.cfg = (kind, act, slope, training, gamma is not None, residual is not None)
+        ctx.save_for_backward(x if kind is not None else None, mean, rstd, gamma, y if act != ACT_NONE else None)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, mean, rstd, gamma, y = ctx.saved_tensors
+        kind, act, slope, training, affine, has_res = ctx.cfg
+        if kind is None:
+            g = K.act_bwd(y, dy, act, slope) if act != ACT_NONE else dy
+            return (g if ctx.needs_input_grad[0] else None, None, None, None, None, None,
+                    g if has_res and ctx.needs_input_grad[6] else None, None, None, None)
+        dres = None
+        if has_res and ctx.needs_input_grad[6]:
+            dres = K.act_bwd(y, dy, act, slope) if act != ACT_NONE else dy
+        dx, dgamma, dbeta = K.norm_bwd(x, dy, y, kind, training, mean, rstd, gamma, act, slope, want_affine=affine,
+                                       need_dx=ctx.needs_input_grad[0])
+        return dx, None, None, None, dgamma, dbeta, dres, None, None, None
+
+
+def norm_act(x, kind, mean, rstd, gamma=None, beta=None, residual=None, act=ACT_NONE, slope=0.0, training=True):
+    return _NormAct.apply(x, kind, mean, rstd, gamma, beta, residual, act, float(slope), bool(training))
+
+
+def add_act(x, residual, act=ACT_NONE, slope=0.0):
+    """act(x + residual): residual adds of ResNet.py:436-443, UNet.py:111-117, ResidualUNet.py:689-701."""
+    return _NormAct.apply(x, None, None, None, None, None, residual, act, float(slope), False)
+
+
+def batch_stats(x, kind, eps, precomputed=None):
+    """mean / rstd / biased var per group from fresh or epilogue-provided sums."""
+    n, c = x.shape[0], x.shape[1]
+    vox = x.shape[2] * x.shape[3] * x.shape[4]
+    if precomputed is not None:
+        s, q = precomputed
+        if kind == NORM_BATCH:  # epilogue sums are per (n,c)
+            s, q = s.view(n, c).sum(0), q.view(n, c).sum(0)
+    else:
+        s, q = K.norm_stats(x.detach(), kind)
+    count = vox if kind == NORM_INSTANCE else n * vox
+    return K.norm_finalize(s, q, count, eps)
+
+
+# ---------------------------------------------------------------------------------------------
+# activation, pooling, up-sampling
+# ---------------------------------------------------------------------------------------------
+class _Act(torch.autograd.Function):
+    """nn.ReLU / LeakyReLU / Tanh / Sigmoid (UNet.py:41-47, NLayerDiscriminator.py:138, BaseSystem.py:175-176)."""
+
+    @staticmethod
+    def forward(ctx, x, act, slope):
+        y = K.act_fwd(x, act, slope)
+        ctx.cfg = (act, slope)
+        ctx.save_for_backward(y)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (y,) = ctx.saved_tensors
+        return K.act_bwd(y, dy, *ctx.cfg), None, None
+
+
+def activation(x, act, slope=0.0):
+    return x if act == ACT_NONE else _Act.apply(x, act, float(slope))
+
+
+class _MaxPool3d(torch.autograd.Function):
+    """nn.MaxPool3d(f, stride=f) (UNet.py:209-218)."""
+
+    @staticmethod
+    def forward(ctx, x, f):
+        ctx.f = f
+        ctx.save_for_backward(x)
+        return K.maxpool_fwd(x, f)
+
+    @staticmethod
+    def backward(ctx, dy):
+        (x,) = ctx.saved_tensors
+        return K.maxpool_bwd(x, dy, ctx.f), None
+
+
+def max_pool3d(x, f):
+    return _MaxPool3d.apply(x, _t3(f))
+
+
+class _UpsampleNearest(torch.autograd.Function):
+    """nn.Upsample(scale_factor=f, mode='nearest') (UNet.py:273)."""
+
+    @staticmethod
+    def forward(ctx, x, f):
+        ctx.f = f
+        return K.upsample_fwd(x, f)
+
+    @staticmethod
+    def backward(ctx, dy):
+        return K.upsample_bwd(dy, ctx.f), None
+
+
+def upsample_nearest(x, f):
+    return _UpsampleNearest.apply(x, _t3(f))
+
+
+# ---------------------------------------------------------------------------------------------
+# crop / concat
+# ---------------------------------------------------------------------------------------------
+def center_crop_view(x, spatial):
+    """Centre crop as a strided VIEW (no copy): UNet.py:97-106,327-336; ResNet.py:436-440."""
+    sl = [slice(None), slice(None)]
+    for have, want in zip(x.shape[2:], spatial):
+        o = (have - want) // 2
+        sl.append(slice(o, o + want))
+    return x[tuple(sl)]
+
+
+class _CropCat(torch.autograd.Function):
+    """torch.cat([crop(f_left), crop(g_up)], dim=1) (UNet.py:338-351) as two strided copies into one
+    buffer; backward hands out strided views / zero-padded slices of dy."""
+
+    @staticmethod
+    def forward(ctx, a, b, spatial):
+        av, bv = center_crop_view(a, spatial), center_crop_view(b, spatial)
+        n = a.shape[0]
+        dt = a.dtype if a.dtype == b.dtype else K.compute_dtype()
+        out = K.empty5((n, a.shape[1] + b.shape[1], *spatial), dt, a.device)
+        K.copy_into(out[:, : a.shape[1]], av)
+        K.copy_into(out[:, a.shape[1]:], bv)
+        ctx.shapes = (tuple(a.shape), tuple(b.shape), tuple(spatial), a.dtype, b.dtype)
+        return out
+
+    @staticmethod
+    def backward(ctx, dy):
+        sa, sb, spatial, da, db = ctx.shapes
+
+        def part(sl, shape, dt):
+            g = dy[:, sl]
+            if tuple(shape[2:]) == spatial:
+                return K.convert(g, dt)
+            full = K.empty5(shape, dt, dy.device)
+            full.zero_()
+            K.copy_into(center_crop_view(full, spatial), g)
+            return full
+
+        ga = part(slice(0, sa[1]), sa, da) if ctx.needs_input_grad[0] else None
+        gb = part(slice(sa[1], sa[1] + sb[1]), sb, db) if ctx.needs_input_grad[1] else None
+        return ga, gb, None
+
+
+def crop_cat(a, b, spatial):
+    return _CropCat.apply(a, b, tuple(int(s) for s in spatial))
+
+
+class _Crop(torch.autograd.Function):
+    """centre crop that materialises (used where a contiguous tensor is needed downstream)."""
+
+    @staticmethod
+    def forward(ctx, x, spatial):
+        ctx.shape = tuple(x.shape)
+        ctx.spatial = spatial
+        v = center_crop_view(x, spatial)
+        return K.copy_into(K.empty5(v.shape, x.dtype, x.device), v)
+
+    @staticmethod
+    def backward(ctx, dy):
+        full = K.empty5(ctx.shape, dy.dtype, dy.device)
+        full.zero_()
+        K.copy_into(center_crop_view(full, ctx.spatial), dy)
+        return full, None
+
+
+def center_crop(x, spatial):
+    spatial = tuple(int(s) for s in spatial)
+    if tuple(x.shape[2:]) == spatial:
+        return x
+    return _Crop.apply(x, spatial)
+
+
+# ---------------------------------------------------------------------------------------------
+# losses
+# ---------------------------------------------------------------------------------------------
+class _Loss(torch.autograd.Function):
+    """Mean-reduced losses with the gradient produced in the same pass.
+    MSE vs a constant label: GANLoss.py:24-25,48-64.  SmoothL1 / L1: LinkCycleLoss.py:22,99-105."""
+
+    @staticmethod
+    def forward(ctx, kind, a, b, target, beta):
+        want = a.requires_grad or (b is not None and b.requires_grad)
+        loss, grad = K.loss_fwd_grad(kind, a.detach(), b.detach() if b is not None else None, target, beta, want)
+        ctx.save_for_backward(grad)
+        ctx.b_dtype = b.dtype if b is not None else None
+        return loss
+
+    @staticmethod
+    def backward(ctx, dl):
+        (grad,) = ctx.saved_tensors
+        ga = gb = None
+        if grad is not None:
+            # scale by the incoming scalar on the device (no host sync): y = act-less norm_apply w/ gamma=dl
+            scale = dl.to(torch.float32).reshape(1)
+            if ctx.needs_input_grad[1]:
+                ga = _scale(grad, scale)
+            if ctx.needs_input_grad[2]:
+                gb = _scale(grad, -scale)
+        return None, ga, gb, None, None
+
+
+def _scale(x, scale1):
+    """x * scalar (device scalar), via the norm-apply kernel with a per-channel gamma."""
+    gamma = scale1.expand(x.shape[1]).contiguous()
+    return K.norm_apply(x, NORM_INSTANCE, None, None, gamma, None, None, ACT_NONE, 0.0)
+
+
+def mse_const_loss(pred, target: float):
+    return _Loss.apply(LOSS_MSE_CONST, pred, None, float(target), 1.0)
+
+
+def mean_loss(pred):
+    return _Loss.apply(LOSS_MEAN, pred, None, 0.0, 1.0)
+
+
+def smooth_l1_loss(a, b, beta: float = 1.0):
+    return _Loss.apply(LOSS_SMOOTHL1, a, b, 0.0, float(beta))
+
+
+def l1_loss(a, b):
+    return _Loss.apply(LOSS_L1, a, b, 0.0, 1.0)

@@ -1,0 +1,261 @@
+"""Raw (non-autograd) operator layer: torch tensors in, C-ABI calls out.
+
+Every function here allocates its outputs with torch (PyTorch owns all memory), describes the
+tensors as ``rg_tensor5`` views and launches hand-written sm_100a kernels from
+``libraygun_b200.so`` on the current CUDA stream.  Nothing here calls a torch compute kernel.
+"""
+from __future__ import annotations
+
+import contextlib
+import ctypes as C
+import os
+import threading
+
+import torch
+
+from . import _C
+from ._C import (ACT_NONE, NORM_BATCH, NORM_INSTANCE, PAD_REFLECT, PAD_REPLICATE, PAD_ZEROS, check, count_launch, i3,
+                 lib, ptr, require_device, stream_ptr, t5)
+
+# --------------------------------------------------------------------------------------------
+# precision mode
+# --------------------------------------------------------------------------------------------
+_state = threading.local()
+
+
+def get_precision() -> str:
+    """'bf16' (tensor-core path, bf16 NDHWC activations) or 'fp32' (CUDA-core parity path)."""
+    return getattr(_state, "precision", None) or os.environ.get("RAYGUN_B200_PRECISION", "bf16")
+
+
+def set_precision(p: str):
+    if p not in ("bf16", "fp32"):
+        raise ValueError(f"precision must be 'bf16' or 'fp32', got {p!r}")
+    _state.precision = p
+
+
+@contextlib.contextmanager
+def precision(p: str):
+    old = getattr(_state, "precision", None)
+    set_precision(p)
+    try:
+        yield
+    finally:
+        _state.precision = old
+
+
+def use_tensor_cores() -> bool:
+    return os.environ.get("RAYGUN_B200_IGEMM", "1") != "0"
+
+
+def compute_dtype():
+    return torch.bfloat16 if get_precision() == "bf16" else torch.float32
+
+
+def empty5(shape, dtype, device):
+    """Allocate an activation: bf16 -> NDHWC (channels_last_3d) storage, fp32 -> NCDHW."""
+    if dtype == torch.bfloat16:
+        return torch.empty(shape, dtype=dtype, device=device, memory_format=torch.channels_last_3d)
+    return torch.empty(shape, dtype=dtype, device=device)
+
+
+def is_ndhwc(t: torch.Tensor) -> bool:
+    n, c, d, h, w = t.shape
+    return t.dtype == torch.bfloat16 and tuple(t.stride()) == (d * h * w * c, 1, h * w * c, w * c, c)
+
+
+# --------------------------------------------------------------------------------------------
+# data movement
+# --------------------------------------------------------------------------------------------
+def copy_into(dst: torch.Tensor, src: torch.Tensor, accumulate: bool = False):
+    require_device(src)
+    check(lib().rg_copy5(C.byref(t5(dst)), ptr(dst), C.byref(t5(src)), ptr(src), C.c_int(int(accumulate)),
+                         stream_ptr(src.device)), "rg_copy5")
+    count_launch()
+    return dst
+
+
+def convert(x: torch.Tensor, dtype) -> torch.Tensor:
+    """Cast / re-layout to the canonical storage of `dtype` (no-op if already there)."""
+    if x.dtype == dtype and (is_ndhwc(x) if dtype == torch.bfloat16 else x.is_contiguous()):
+        return x
+    return copy_into(empty5(x.shape, dtype, x.device), x)
+
+
+def pad3d(x, lo, hi, mode):
+    require_device(x)
+    n, c, d, h, w = x.shape
+    y = empty5((n, c, d + lo[0] + hi[0], h + lo[1] + hi[1], w + lo[2] + hi[2]), x.dtype, x.device)
+    check(lib().rg_pad3d_fwd(C.byref(t5(x)), ptr(x), C.byref(t5(y)), ptr(y), i3(lo), C.c_int(mode),
+                             stream_ptr(x.device)), "rg_pad3d_fwd")
+    count_launch()
+    return y
+
+
+def pad3d_bwd(dy, x_shape, lo, mode):
+    dx = empty5(x_shape, dy.dtype, dy.device)
+    dx.zero_()  # memset (driver), not a compute kernel
+    check(lib().rg_pad3d_bwd(C.byref(t5(dy)), ptr(dy), C.byref(t5(dx)), ptr(dx), i3(lo), C.c_int(mode),
+                             stream_ptr(dy.device)), "rg_pad3d_bwd")
+    count_launch()
+    return dx
+
+
+# --------------------------------------------------------------------------------------------
+# activations / pooling / upsampling
+# --------------------------------------------------------------------------------------------
+def act_fwd(x, act, slope=0.0, out_dtype=None):
+    require_device(x)
+    y = empty5(x.shape, out_dtype or x.dtype, x.device)
+    check(lib().rg_act_fwd(C.byref(t5(x)), ptr(x), C.c_int(act), C.c_float(slope), C.byref(t5(y)), ptr(y),
+                           stream_ptr(x.device)), "rg_act_fwd")
+    count_launch()
+    return y
+
+
+def act_bwd(y, dy, act, slope=0.0):
+    if dy.dtype != y.dtype:
+        dy = convert(dy, y.dtype)
+    dx = empty5(y.shape, y.dtype, y.device)
+    check(lib().rg_act_bwd(C.byref(t5(y)), ptr(y), C.byref(t5(dy)), ptr(dy), C.c_int(act), C.c_float(slope),
+                           C.byref(t5(dx)), ptr(dx), stream_ptr(y.device)), "rg_act_bwd")
+    count_launch()
+    return dx
+
+
+def maxpool_fwd(x, f):
+    require_device(x)
+    n, c, d, h, w = x.shape
+    y = empty5((n, c, d // f[0], h // f[1], w // f[2]), x.dtype, x.device)
+    check(lib().rg_maxpool3d_fwd(C.byref(t5(x)), ptr(x), i3(f), C.byref(t5(y)), ptr(y), stream_ptr(x.device)),
+          "rg_maxpool3d_fwd")
+    count_launch()
+    return y
+
+
+def maxpool_bwd(x, dy, f):
+    if dy.dtype != x.dtype:
+        dy = convert(dy, x.dtype)
+    dx = empty5(x.shape, x.dtype, x.device)
+    if any(s % k for s, k in zip(x.shape[2:], f)):
+        dx.zero_()
+    check(lib().rg_maxpool3d_bwd(C.byref(t5(x)), ptr(x), None, None, C.byref(t5(dy)), ptr(dy), i3(f),
+                                 C.byref(t5(dx)), ptr(dx), stream_ptr(x.device)), "rg_maxpool3d_bwd")
+    count_launch()
+    return dx
+
+
+def upsample_fwd(x, f):
+    require_device(x)
+    n, c, d, h, w = x.shape
+    y = empty5((n, c, d * f[0], h * f[1], w * f[2]), x.dtype, x.device)
+    check(lib().rg_upsample_nearest_fwd(C.byref(t5(x)), ptr(x), i3(f), C.byref(t5(y)), ptr(y),
+                                        stream_ptr(x.device)), "rg_upsample_nearest_fwd")
+    count_launch()
+    return y
+
+
+def upsample_bwd(dy, f):
+    n, c, d, h, w = dy.shape
+    dx = empty5((n, c, d // f[0], h // f[1], w // f[2]), dy.dtype, dy.device)
+    check(lib().rg_upsample_nearest_bwd(C.byref(t5(dy)), ptr(dy), i3(f), C.byref(t5(dx)), ptr(dx),
+                                        stream_ptr(dy.device)), "rg_upsample_nearest_bwd")
+    count_launch()
+    return dx
+
+
+# --------------------------------------------------------------------------------------------
+# normalisation
+# --------------------------------------------------------------------------------------------
+def norm_stats(x, kind):
+    """sum / sum-of-squares per (n,c) [instance] or per c [batch]; fp32."""
+    require_device(x)
+    groups = x.shape[0] * x.shape[1] if kind == NORM_INSTANCE else x.shape[1]
+    s = torch.zeros(2, groups, dtype=torch.float32, device=x.device)
+    check(lib().rg_norm_stats(C.byref(t5(x)), ptr(x), C.c_int(kind), ptr(s[0]), ptr(s[1]), stream_ptr(x.device)),
+          "rg_norm_stats")
+    count_launch()
+    return s[0], s[1]
+
+
+def norm_finalize(ssum, ssq, count, eps):
+    groups = ssum.numel()
+    out = torch.empty(3, groups, dtype=torch.float32, device=ssum.device)
+    check(lib().rg_norm_finalize(ptr(ssum), ptr(ssq), C.c_int(groups), C.c_double(float(count)), C.c_float(eps),
+                                 ptr(out[0]), ptr(out[1]), ptr(out[2]), stream_ptr(ssum.device)), "rg_norm_finalize")
+    count_launch()
+    return out[0], out[1], out[2]  # mean, rstd, biased var
+
+
+def norm_apply(x, kind, mean, rstd, gamma, beta, residual, act, slope, out_dtype=None):
+    require_device(x)
+    y = empty5(x.shape, out_dtype or x.dtype, x.device)
+    rd = C.byref(t5(residual)) if residual is not None else None
+    check(lib().rg_norm_apply(C.byref(t5(x)), ptr(x), C.c_int(kind), ptr(mean), ptr(rstd), ptr(gamma), ptr(beta),
+                              rd, ptr(residual), C.c_int(act), C.c_float(slope), C.byref(t5(y)), ptr(y),
+                              stream_ptr(x.device)), "rg_norm_apply")
+    count_launch()
+    return y
+
+
+def norm_bwd(x, dy, y, kind, training, mean, rstd, gamma, act, slope, want_affine, need_dx=True):
+    """Returns dx, dgamma, dbeta (the latter two None unless want_affine)."""
+    if act != ACT_NONE and dy.dtype != y.dtype:
+        dy = convert(dy, y.dtype)
+    groups = mean.numel()
+    c = x.shape[1]
+    red = torch.zeros(2 * groups, dtype=torch.float32, device=x.device)
+    dg = torch.empty(2, c, dtype=torch.float32, device=x.device) if want_affine else None
+    dx = empty5(x.shape, x.dtype, x.device) if need_dx else None
+    yd = C.byref(t5(y)) if y is not None else None
+    check(lib().rg_norm_bwd(C.byref(t5(x)), ptr(x), C.byref(t5(dy)), ptr(dy), yd, ptr(y), C.c_int(kind),
+                            C.c_int(int(training)), ptr(mean), ptr(rstd), ptr(gamma), C.c_int(act), C.c_float(slope),
+                            ptr(red), ptr(dg[0]) if want_affine else None, ptr(dg[1]) if want_affine else None,
+                            C.byref(t5(dx)) if need_dx else None, ptr(dx), stream_ptr(x.device)), "rg_norm_bwd")
+    count_launch(2 if training or want_affine else 1)
+    return dx, (dg[0] if want_affine else None), (dg[1] if want_affine else None)
+
+
+# --------------------------------------------------------------------------------------------
+# losses / prediction arithmetic / optimiser
+# --------------------------------------------------------------------------------------------
+def loss_fwd_grad(kind, a, b=None, target=0.0, beta=1.0, want_grad=True):
+    """mean-reduced loss (fp32 scalar tensor) and d loss / d a (same storage as a)."""
+    require_device(a)
+    loss = torch.zeros(1, dtype=torch.float32, device=a.device)
+    grad = empty5(a.shape, a.dtype, a.device) if want_grad else None
+    check(lib().rg_loss_fwd_grad(C.c_int(kind), C.byref(t5(a)), ptr(a), C.byref(t5(b)) if b is not None else None,
+                                 ptr(b), C.c_float(target), C.c_float(beta), C.c_float(1.0), ptr(loss), C.c_float(1.0),
+                                 C.byref(t5(grad)) if want_grad else None, ptr(grad), stream_ptr(a.device)),
+          "rg_loss_fwd_grad")
+    count_launch()
+    return loss[0], grad
+
+
+def u8_normalise(u8: torch.Tensor, scale=2.0, shift=-1.0, dtype=None):
+    require_device(u8)
+    dtype = dtype or compute_dtype()
+    u8 = u8.contiguous()
+    y = torch.empty(u8.shape, dtype=dtype, device=u8.device)
+    check(lib().rg_u8_normalise(ptr(u8), C.c_int64(u8.numel()), C.c_float(scale), C.c_float(shift),
+                                C.c_int(_C.RG_BF16 if dtype == torch.bfloat16 else _C.RG_F32), ptr(y),
+                                stream_ptr(u8.device)), "rg_u8_normalise")
+    count_launch()
+    return y
+
+
+def denorm_clamp_u8(x: torch.Tensor):
+    """x: 5-D view (any strides, e.g. a cropped slice) -> contiguous uint8 of the same shape."""
+    require_device(x)
+    out = torch.empty(x.shape, dtype=torch.uint8, device=x.device)
+    check(lib().rg_denorm_clamp_u8(C.byref(t5(x)), ptr(x), ptr(out), stream_ptr(x.device)), "rg_denorm_clamp_u8")
+    count_launch()
+    return out
+
+
+def adam_step(p, g, m, v, lr, beta1, beta2, eps, step, grad_scale=1.0):
+    require_device(p)
+    check(lib().rg_adam_step(ptr(p), ptr(g), ptr(m), ptr(v), C.c_int64(p.numel()), C.c_float(lr), C.c_float(beta1),
+                             C.c_float(beta2), C.c_float(eps), C.c_int(step), C.c_float(grad_scale),
+                             stream_ptr(p.device)), "rg_adam_step")
+    count_launch()
