@@ -1,0 +1,360 @@
+"""Host-side mirror of the CycleGAN model / loss glue of the reference, driving the sm_100a kernels.
+
+Mirrors (same names, argument meaning, ordering of side effects):
+  * ``BaseSystem.get_network`` wrapper      systems/BaseSystem.py:163-242  -> ``make_generator`` / ``make_discriminator``
+  * ``GANLoss``                             losses/GANLoss.py:3-64
+  * ``CycleModel.forward``                  models/CycleModel.py:37-89
+  * ``LinkCycleLoss``                       losses/LinkCycleLoss.py:9-176 (+ BaseCompetentLoss.py:8-48)
+  * the gunpowder ``Train`` node's step     train/BaseTrain.py:63-75       -> ``CycleGANStep``
+The loss reductions run as fused forward+gradient warp-shuffle kernels; everything else is control flow.
+"""
+from __future__ import annotations
+
+import functools
+import itertools
+
+import torch
+import torch.nn as tnn
+
+from . import functional as F
+from . import networks as N
+from . import nn as L
+
+
+# ---------------------------------------------------------------------------------------------
+# get_network
+# ---------------------------------------------------------------------------------------------
+class Generator(tnn.Sequential):
+    """Sequential(net, Conv3d(ngf -> output_nc, 1x1x1, padding=padding_type), final_activation)
+    (BaseSystem.py:209-224) executed without leaving the compute dtype between the three stages."""
+
+    def forward(self, x):
+        net = self[0]
+        if getattr(net, "ndims", getattr(net, "_ndims", 3)) != 3:
+            return super().forward(x)
+        net._keep_compute_dtype = True
+        try:
+            y = net(x)
+        finally:
+            net._keep_compute_dtype = False
+        y = L.run_layers(list(self)[1:], y)
+        return F.cast(y, torch.float32)
+
+
+def _downsample_factors(kw, ndims):
+    # BaseSystem.get_downsample_factors (BaseSystem.py:145-161)
+    if "downsample_factors" not in kw:
+        f = kw.pop("down_factor", 2)
+        n = kw.pop("num_downs", 3)
+        kw["downsample_factors"] = [(f,) * ndims] * (n - 1)
+    return kw
+
+
+def make_generator(net_type, net_kwargs, output_nc=None, final_activation=None, ndims=3, init="kaiming"):
+    """What ``BaseSystem.get_network(net_type, net_kwargs)`` builds for a generator
+    (BaseSystem.py:163-242): pops ``final_activation`` / ``output_nc`` from the kwargs, builds the net,
+    appends Conv{n}d(ngf -> output_nc, 1x..x1, padding=padding_type) [+ activation], kaiming init."""
+    kw = dict(net_kwargs)
+    final_activation = kw.pop("final_activation", final_activation)
+    output_nc = kw.pop("output_nc", output_nc if output_nc is not None else kw.get("input_nc", 1))
+    t = net_type.lower()
+    if t == "unet":
+        net = N.UNet(**_downsample_factors(kw, ndims))
+    elif t == "residualunet":
+        net = N.ResidualUNet(**_downsample_factors(kw, ndims))
+    elif t == "resnet":
+        net = N.ResNet(ndims, **kw)
+    elif hasattr(N, net_type):
+        net = getattr(N, net_type)(**kw)
+    else:
+        raise ValueError(f"Unknown network type requested: {net_type}")
+    conv = L.Conv3d if ndims == 3 else tnn.Conv2d
+    layers = [net, conv(kw.get("ngf", 64), output_nc, (1,) * ndims, padding=kw.get("padding_type", "valid")
+                        if kw.get("padding_type", "valid") in ("same", "valid") else 0)]
+    if final_activation is not None:
+        layers.append(L.make_activation(final_activation) if ndims == 3 else
+                      (getattr(tnn, final_activation) if isinstance(final_activation, str) else final_activation)())
+    g = Generator(*layers)
+    if init:
+        N.init_weights(g, init, nonlinearity="relu")
+    return g
+
+
+def make_discriminator(net_kwargs, ndims=3, init="kaiming"):
+    """get_network for 'patchgan'/'nlayerdiscriminator': norm forced to InstanceNorm without affine or
+    running stats (BaseSystem.py:192-200)."""
+    norm = {3: tnn.InstanceNorm3d, 2: tnn.InstanceNorm2d}[ndims]
+    kw = dict(net_kwargs)
+    kw["norm_layer"] = functools.partial(norm, affine=False, track_running_stats=False)
+    d = N.NLayerDiscriminator(ndims, **kw)
+    if init:
+        N.init_weights(d, init, nonlinearity="leaky_relu")
+    return d
+
+
+# ---------------------------------------------------------------------------------------------
+# losses
+# ---------------------------------------------------------------------------------------------
+class GANLoss(tnn.Module):
+    """losses/GANLoss.py: lsgan = MSE against a constant label (one fused reduce+grad kernel, no label
+    tensor is ever materialised); wgangp = -/+ mean; vanilla = BCE-with-logits (stock torch op)."""
+
+    def __init__(self, gan_mode, target_real_label=1.0, target_fake_label=0.0):
+        super().__init__()
+        self.register_buffer("real_label", torch.tensor(target_real_label))
+        self.register_buffer("fake_label", torch.tensor(target_fake_label))
+        self._labels = (float(target_real_label), float(target_fake_label))
+        self.gan_mode = gan_mode
+        if gan_mode == "vanilla":
+            self.loss = tnn.BCEWithLogitsLoss()
+        elif gan_mode in ("lsgan", "wgangp"):
+            self.loss = None
+        else:
+            raise NotImplementedError("gan mode %s not implemented" % gan_mode)
+
+    def get_target_tensor(self, prediction, target_is_real):
+        return (self.real_label if target_is_real else self.fake_label).expand_as(prediction)
+
+    def __call__(self, prediction, target_is_real):
+        if self.gan_mode == "lsgan":
+            return F.mse_const_loss(prediction, self._labels[0] if target_is_real else self._labels[1])
+        if self.gan_mode == "wgangp":
+            m = F.mean_loss(prediction)
+            return -m if target_is_real else m
+        return self.loss(prediction, self.get_target_tensor(prediction, target_is_real))
+
+
+def _cycle_loss_fn(l1_loss):
+    """Map the reference's ``l1_loss`` module argument onto the fused kernels."""
+    if l1_loss is None or isinstance(l1_loss, tnn.SmoothL1Loss):
+        beta = 1.0 if l1_loss is None else float(l1_loss.beta)
+        if l1_loss is None or l1_loss.reduction == "mean":
+            return lambda real, pred: F.smooth_l1_loss(real, pred, beta)
+    if isinstance(l1_loss, tnn.L1Loss) and l1_loss.reduction == "mean":
+        return lambda real, pred: F.l1_loss(real, pred)
+    if isinstance(l1_loss, str):
+        return {"smoothl1": lambda r, p: F.smooth_l1_loss(r, p, 1.0), "l1": F.l1_loss}[l1_loss.lower()]
+    return l1_loss          # any other callable runs as given
+
+
+class CycleModel(tnn.Module):
+    """models/CycleModel.py:7-89 (sampling_bottleneck is delegated to torch's interpolate: off by default)."""
+
+    def __init__(self, netG1, netG2, scale_factor_A=None, scale_factor_B=None, split=False, freeze_norms_at=None,
+                 **kwargs):
+        super().__init__()
+        self.netG1, self.netG2 = netG1, netG2
+        self.nets = [netG1, netG2]
+        self.output_arrays = ["fake_B", "cycled_B", "fake_A", "cycled_A"]
+        self.scale_factor_A, self.scale_factor_B, self.split = scale_factor_A, scale_factor_B, split
+        self.freeze_norms_at = freeze_norms_at
+        self.cycle = True
+        self.crop_pad = None
+        for k, v in kwargs.items():
+            setattr(self, k, v)
+
+    def sampling_bottleneck(self, array, scale_factor):
+        size = array.shape[-len(scale_factor):]
+        mode = {2: "bilinear", 3: "trilinear"}[len(size)]
+        down = tnn.functional.interpolate(array, scale_factor=scale_factor, mode=mode, align_corners=True)
+        return tnn.functional.interpolate(down, size=size, mode=mode, align_corners=True)
+
+    def set_crop_pad(self, crop_pad, ndims):
+        self.crop_pad = (slice(None),) * 2 + (slice(crop_pad, -crop_pad),) * ndims
+
+    def set_norm_modes(self, mode="train"):
+        for net in self.nets:
+            N.set_norm_mode(net, mode)
+
+    def update_status(self, step):
+        if self.freeze_norms_at is not None and step >= self.freeze_norms_at:
+            self.set_norm_modes(mode="fix_norms")
+
+    def _half(self, first, second, real, scale):
+        fake = first(real)
+        if self.crop_pad is not None:
+            fake = fake[self.crop_pad]
+        if scale:
+            fake = self.sampling_bottleneck(fake, scale)
+        cycled = None
+        if self.cycle:
+            cycled = second(fake.detach() if self.split else fake)
+            if self.crop_pad is not None:
+                cycled = cycled[self.crop_pad]
+        return fake, cycled
+
+    def forward(self, real_A=None, real_B=None):
+        assert real_A is not None or real_B is not None, "Must have some real input to generate outputs)"
+        fake_B = cycled_A = fake_A = cycled_B = None
+        if real_A is not None:
+            fake_B, cycled_A = self._half(self.netG1, self.netG2, real_A, self.scale_factor_B)
+        if real_B is not None:
+            fake_A, cycled_B = self._half(self.netG2, self.netG1, real_B, self.scale_factor_A)
+        return fake_B, cycled_B, fake_A, cycled_A
+
+
+_DEFAULT_G_LAMBDA = {s: {"l1_loss": {"cycled": 10, "identity": 0}, "gan_loss": {"fake": 1, "cycled": 0}} for s in "AB"}
+_DEFAULT_D_LAMBDA = {s: {"real": 1, "fake": 1, "cycled": 0} for s in "AB"}
+
+
+class LinkCycleLoss(tnn.Module):
+    """losses/LinkCycleLoss.py.  ``forward`` performs the whole optimisation step, in the reference's
+    order: G losses -> backward (per side, retain_graph) -> optimizer_G.step -> D losses on the
+    PRE-step fakes (detached) -> backward -> optimizer_D.step; returns the total whose ``backward`` is a
+    no-op.  Extras: ``grad_sync(phase)`` is called right before each optimizer step (data-parallel
+    gradient all-reduce hooks in there); ``single_backward`` sums the two generator losses and
+    back-propagates once (same gradients, 4 instead of 6 generator traversals)."""
+
+    def __init__(self, netD1, netG1, netD2, netG2, optimizer_G, optimizer_D, dims, l1_loss=None, g_lambda_dict=None,
+                 d_lambda_dict=None, gan_mode="lsgan", grad_sync=None, single_backward=False, **kwargs):
+        super().__init__()
+        self.netD1, self.netG1, self.netD2, self.netG2 = netD1, netG1, netD2, netG2
+        self.optimizer_G, self.optimizer_D, self.dims = optimizer_G, optimizer_D, dims
+        self._l1_arg = l1_loss if l1_loss is not None else tnn.SmoothL1Loss()
+        self.l1_loss = _cycle_loss_fn(l1_loss)
+        self.g_lambda_dict = g_lambda_dict or _DEFAULT_G_LAMBDA
+        self.d_lambda_dict = d_lambda_dict or _DEFAULT_D_LAMBDA
+        self.gan_mode = gan_mode
+        self.gan_loss = GANLoss(gan_mode=gan_mode)
+        self.grad_sync, self.single_backward = grad_sync, single_backward
+        self.loss_dict, self.data_dict = {}, {}
+        for k, v in kwargs.items():
+            setattr(self, k, v)
+
+    # -- BaseCompetentLoss helpers ---------------------------------------------------------------
+    def set_requires_grad(self, nets, requires_grad=False):
+        for net in nets if isinstance(nets, list) else [nets]:
+            if net is not None:
+                for p in net.parameters():
+                    p.requires_grad = requires_grad
+
+    def crop(self, x, shape):
+        """Centre crop as a strided view (BaseCompetentLoss.py:33-42); the kernels are stride-generic."""
+        nd = len(shape)
+        sl = [slice(None)] * (x.dim() - nd)
+        for have, want in zip(x.shape[-nd:], shape):
+            o = (have - want) // 2
+            sl.append(slice(o, o + want))
+        return x[tuple(sl)]
+
+    def clamp_weights(self, net, min=-0.01, max=0.01):
+        for module in net.model:
+            if hasattr(module, "weight") and hasattr(module.weight, "data"):
+                module.weight.data = module.weight.data.clamp(min, max)
+
+    # -- the step ----------------------------------------------------------------------------------
+    def _d_loss(self, side, dnet, data):
+        loss = 0
+        for key, lam in self.d_lambda_dict[side].items():
+            if lam != 0:
+                this = self.gan_loss(dnet(data[key].detach()), key == "real")
+                self.loss_dict[f"Discriminator_{side}/{key}"] = this
+                loss = loss + lam * this
+        return loss
+
+    def backward_D(self, side, dnet, data_dict):
+        loss = self._d_loss(side, dnet, data_dict)
+        loss.backward()
+        return loss
+
+    def backward_Ds(self, data_dict, n_loop=5):
+        self.set_requires_grad([self.netG1, self.netG2], False)
+        self.optimizer_D.zero_grad(set_to_none=True)
+        loops = n_loop if self.gan_mode.lower() == "wgangp" else 1
+        for _ in range(loops):
+            loss_D1 = self.backward_D("B", self.netD1, data_dict["B"])
+            loss_D2 = self.backward_D("A", self.netD2, data_dict["A"])
+            if self.grad_sync is not None:
+                self.grad_sync("D")
+            self.optimizer_D.step()
+            if loops > 1:
+                self.clamp_weights(self.netD1)
+                self.clamp_weights(self.netD2)
+        self.set_requires_grad([self.netG1, self.netG2], True)
+        return loss_D1, loss_D2
+
+    def _g_loss(self, side, gnet, dnet, data):
+        loss = 0
+        real = data["real"]
+        for fcn_name, lambdas in self.g_lambda_dict[side].items():
+            for key, lam in lambdas.items():
+                if lam == 0:
+                    continue
+                if key == "identity" and key not in data:
+                    data["identity"] = gnet(real)
+                pred = data[key]
+                if fcn_name == "l1_loss":
+                    r = real
+                    if tuple(real.shape[-self.dims:]) != tuple(pred.shape[-self.dims:]):
+                        r = self.crop(real, pred.shape[-self.dims:])
+                    this = self.l1_loss(r, pred)
+                else:
+                    this = self.gan_loss(dnet(pred), True)
+                self.loss_dict[f"{fcn_name}/{key}_{side}"] = this
+                loss = loss + lam * this
+        return loss
+
+    def backward_G(self, side, gnet, dnet, data_dict):
+        loss = self._g_loss(side, gnet, dnet, data_dict)
+        loss.backward(retain_graph=True)
+        return loss
+
+    def backward_Gs(self, data_dict):
+        self.set_requires_grad([self.netD1, self.netD2], False)
+        self.optimizer_G.zero_grad(set_to_none=True)
+        if self.single_backward:
+            loss_G1 = self._g_loss("B", self.netG1, self.netD1, data_dict["B"])
+            loss_G2 = self._g_loss("A", self.netG2, self.netD2, data_dict["A"])
+            (loss_G1 + loss_G2).backward()
+        else:
+            loss_G1 = self.backward_G("B", self.netG1, self.netD1, data_dict["B"])
+            loss_G2 = self.backward_G("A", self.netG2, self.netD2, data_dict["A"])
+        if self.grad_sync is not None:
+            self.grad_sync("G")
+        self.optimizer_G.step()
+        self.set_requires_grad([self.netD1, self.netD2], True)
+        return loss_G1, loss_G2
+
+    def forward(self, real_A, fake_A, cycled_A, real_B, fake_B, cycled_B):
+        self.data_dict.update(real_A=real_A, fake_A=fake_A, cycled_A=cycled_A, real_B=real_B, fake_B=fake_B,
+                              cycled_B=cycled_B)
+        if tuple(real_A.shape[-self.dims:]) != tuple(fake_B.shape[-self.dims:]):
+            real_A = self.crop(real_A, fake_A.shape[-self.dims:])
+            real_B = self.crop(real_B, fake_B.shape[-self.dims:])
+        data = {"A": {"real": real_A, "fake": fake_A, "cycled": cycled_A},
+                "B": {"real": real_B, "fake": fake_B, "cycled": cycled_B}}
+        loss_G1, loss_G2 = self.backward_Gs(data)
+        loss_D1, loss_D2 = self.backward_Ds(data)
+        # one host sync for the four logged scalars (the reference does four float() calls)
+        vals = torch.stack([loss_D1.detach(), loss_D2.detach(), loss_G1.detach(), loss_G2.detach()]).tolist()
+        self.loss_dict.update({"Total_Loss/D1": vals[0], "Total_Loss/D2": vals[1], "Total_Loss/G1": vals[2],
+                               "Total_Loss/G2": vals[3]})
+        total = (loss_G1 + loss_G2 + loss_D1 + loss_D2).detach()
+        total.backward = lambda: None
+        return total
+
+
+# ---------------------------------------------------------------------------------------------
+# the training step harness (what gp.torch.Train does around model + loss)
+# ---------------------------------------------------------------------------------------------
+class CycleGANStep:
+    """model(real_A, real_B) -> loss(real_A, fake_A, cycled_A, real_B, fake_B, cycled_B); Adam for G1+G2 and
+    D1+D2 as wired by systems/CycleGAN.py:167-197 (lr 1e-5, betas (0.9, 0.999) from default_cycleGAN_conf.json)."""
+
+    def __init__(self, g1, g2, d1, d2, lr=1e-5, betas=(0.9, 0.999), l1_loss=None, g_lambda_dict=None,
+                 d_lambda_dict=None, gan_mode="lsgan", grad_sync=None, single_backward=False, dims=3,
+                 optimizer_cls=None):
+        opt = optimizer_cls or torch.optim.Adam
+        self.nets = (g1, g2, d1, d2)
+        self.optimizer_G = opt(itertools.chain(g1.parameters(), g2.parameters()), lr=lr, betas=betas)
+        self.optimizer_D = opt(itertools.chain(d1.parameters(), d2.parameters()), lr=lr, betas=betas)
+        self.model = CycleModel(g1, g2)
+        self.loss = LinkCycleLoss(d1, g1, d2, g2, self.optimizer_G, self.optimizer_D, dims, l1_loss=l1_loss,
+                                  g_lambda_dict=g_lambda_dict, d_lambda_dict=d_lambda_dict, gan_mode=gan_mode,
+                                  grad_sync=grad_sync, single_backward=single_backward)
+
+    def step(self, real_A, real_B):
+        fake_B, cycled_B, fake_A, cycled_A = self.model(real_A, real_B)
+        self.loss(real_A, fake_A, cycled_A, real_B, fake_B, cycled_B)
+        d = self.loss.loss_dict
+        return {"G1": d["Total_Loss/G1"], "G2": d["Total_Loss/G2"], "D1": d["Total_Loss/D1"], "D2": d["Total_Loss/D2"]}

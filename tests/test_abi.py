@@ -1,0 +1,105 @@
+"""CPU-side checks: the C-ABI library builds, loads and exports every symbol of include/raygun_b200.h;
+the drop-in classes reproduce the reference's module trees / state_dict keys; host logic that needs
+no GPU.  No compute call is made here."""
+import json
+import os
+import re
+
+import pytest
+import torch
+
+import raygun_b200 as rb
+from raygun_b200 import _C, _build
+from raygun_b200 import networks as N
+from tests._golden import GOLDEN, build_ours, case_names, load_case
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_builds_and_exports_every_declared_symbol():
+    _build.build()
+    lib = _C.lib()
+    with open(os.path.join(ROOT, "include", "raygun_b200.h")) as f:
+        header = f.read()
+    declared = set(re.findall(r"^(?:int|size_t|const char\*)\s+(rg_[a-z0-9_]+)\s*\(", header, flags=re.M))
+    assert declared == set(_C.SYMBOLS), declared ^ set(_C.SYMBOLS)
+    for s in declared:
+        assert hasattr(lib, s), s
+    assert lib.rg_version() == 100
+
+
+def test_sass_contains_blackwell_tensor_core_and_tma_instructions():
+    import shutil
+    import subprocess
+    if shutil.which("cuobjdump") is None:
+        pytest.skip("cuobjdump not on PATH")
+    out = subprocess.run(["cuobjdump", "-sass", _C.LIB_PATH], capture_output=True, text=True).stdout
+    for mnemonic in ("UTCHMMA", "UTMALDG", "UTMASTG", "LDTM"):
+        assert mnemonic in out, mnemonic
+    assert "HMMA." not in out.replace("UTCHMMA", "")   # no legacy mma.sync path
+
+
+@pytest.mark.parametrize("name", case_names())
+def test_state_dict_keys_and_shapes_match_reference_fixtures(name):
+    c = load_case(name)
+    net = build_ours(c["kind"], c["kw"])
+    ours = {k: tuple(v.shape) for k, v in net.state_dict().items()}
+    ref = {k: tuple(v.shape) for k, v in c["sd"].items()}
+    assert ours == ref
+    net.load_state_dict(c["sd"])     # strict
+
+
+def test_structural_constants_of_the_reference_tests():
+    with open(os.path.join(GOLDEN, "structural.json")) as f:
+        s = json.load(f)
+    d = N.NLayerDiscriminator(3)
+    assert sum(p.numel() for p in d.parameters()) == s["nld3d_default_params"] == 11048769
+    assert len(d.model) == s["nld3d_default_len"] == 12
+    assert len(N.ResNet(3).model) == s["resnet3d_default_len"]
+    assert len(N.ResNet(3, n_blocks=4, n_downsampling=3).model) == 28      # resnet_test.py:17-22
+    assert len(N.NLayerDiscriminator(2, n_layers=5).model) == 18            # nlayerdiscriminator_test.py:80
+    assert 30 <= N.NLayerDiscriminator(2).FOV <= 110                        # :24-37
+    with pytest.raises(ValueError):
+        N.ResNet(4)
+    with pytest.raises(ValueError):
+        N.NLayerDiscriminator(4)
+
+
+def test_unet_attributes():
+    u = N.UNet(input_nc=3, ngf=16, fmap_inc_factor=2, downsample_factors=[(2, 2, 2)] * 2, padding_type="same")
+    assert (u.ndims, u.num_levels, u.num_heads, u.input_nc, u.output_nc, u.dims) == (3, 3, 1, 3, 16, 3)
+    assert len(u.l_conv) == 3 and len(u.l_down) == 2 and len(u.r_up[0]) == 2 and len(u.r_conv[0]) == 2
+    md = N.MaxDownsample((2, 2, 2), flexible=False)
+    with pytest.raises(RuntimeError):
+        md(torch.zeros(1, 1, 5, 4, 4))
+
+
+def test_two_d_networks_are_delegated_to_stock_torch():
+    y = N.ResNet(2, ngf=4, n_blocks=1)(torch.randn(1, 1, 32, 32))
+    assert y.shape == (1, 4, 32, 32)
+    d = N.NLayerDiscriminator(2, ngf=4)(torch.randn(1, 1, 64, 64))
+    assert d.shape[:2] == (1, 1)
+
+
+def test_no_cpu_fallback_for_the_3d_path():
+    u = N.UNet(input_nc=1, ngf=4, fmap_inc_factor=2, downsample_factors=[(2, 2, 2)], padding_type="same")
+    with pytest.raises(_C.RaygunB200Error):
+        u(torch.zeros(1, 1, 8, 8, 8))
+
+
+def test_norm_helpers_work_on_the_kernel_backed_modules():
+    net = N.ResNet(3, ngf=4, n_blocks=1, norm_layer=torch.nn.BatchNorm3d)
+    assert len(N.get_norm_layers(net)) == 7
+    N.set_norm_mode(net, "fix_norms")
+    assert net.training and not any(m.training for m in N.get_norm_layers(net))
+    m, v = N.get_running_norm_stats(net)
+    assert m is not None and m.numel() == v.numel()
+    N.init_weights(net, "kaiming")
+
+
+def test_precision_switch():
+    assert rb.get_precision() in ("bf16", "fp32")
+    with rb.precision("fp32"):
+        assert rb.get_precision() == "fp32"
+    with pytest.raises(ValueError):
+        rb.set_precision("fp16")

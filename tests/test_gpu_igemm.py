@@ -1,0 +1,120 @@
+"""GPU parity of the tcgen05 / TMEM / TMA implicit-GEMM path (bf16 in, fp32 accumulate) vs the CPU
+oracle evaluated in fp32 on the SAME bf16-rounded operands: differences are accumulation order and the
+final bf16 rounding only (tolerance 1e-2 of the output scale; north_star allows 2e-2 relative)."""
+import pytest
+import torch
+import torch.nn.functional as TF
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def _q(t):
+    return t.bfloat16().float()
+
+
+def _rel(a, b):
+    a, b = a.detach().float().cpu(), b.detach().float().cpu()
+    assert a.shape == b.shape
+    return float((a - b).abs().max()) / max(1e-6, float(b.abs().max()))
+
+
+FPROP = [
+    # cin, cout, k, stride, pad, spatial, batch
+    (64, 64, 3, 1, 1, (8, 8, 8), 1),
+    (64, 128, 3, 1, 0, (10, 9, 12), 2),
+    (128, 256, 3, 2, 1, (9, 10, 11), 1),
+    (64, 64, 7, 1, 3, (9, 9, 9), 1),
+    (192, 64, 1, 1, 0, (5, 6, 7), 2),
+    (64, 512, 3, 1, 1, (9, 9, 9), 1),
+    (256, 256, 2, 2, 1, (17, 17, 17), 1),
+    (64, 192, (1, 3, 3), (1, 2, 1), (0, 1, 1), (4, 9, 8), 1),
+]
+
+
+@pytest.mark.parametrize("case", FPROP)
+def test_igemm_fprop_with_bias_activation_and_stats(case):
+    import raygun_b200 as rb
+    from raygun_b200 import conv as CV
+    cin, cout, k, s, p, sp, n = case
+    torch.manual_seed(11)
+    x = _q(torch.randn(n, cin, *sp))
+    conv = torch.nn.Conv3d(cin, cout, k, stride=s, padding=p)
+    w, b = _q(conv.weight.detach()), conv.bias.detach()
+    ref = TF.leaky_relu(TF.conv3d(x, w, b, stride=s, padding=p), 0.2)
+    before = CV.stats["igemm"]
+    with rb.precision("bf16"):
+        xg = x.to(DEV).bfloat16().contiguous(memory_format=torch.channels_last_3d)
+        st3 = lambda v: (v,) * 3 if isinstance(v, int) else tuple(v)
+        y, ssum, ssq = CV.conv_fprop(xg, w.to(DEV), b.to(DEV), st3(s), st3(p), 1, 2, 0.2, want_stats=True)
+    assert CV.stats["igemm"] == before + 1
+    assert y.dtype == torch.bfloat16
+    assert _rel(y, ref) <= 1e-2, _rel(y, ref)
+    yq = y.float().cpu()
+    assert _rel(ssum.view(n, cout), yq.sum(dim=(2, 3, 4))) <= 2e-3
+    assert _rel(ssq.view(n, cout), (yq * yq).sum(dim=(2, 3, 4))) <= 2e-3
+
+
+DGRAD = [
+    (64, 64, 3, 1, 1, (8, 8, 8), 0),
+    (128, 64, 3, 2, 1, (8, 9, 10), 1),
+    (64, 128, 2, 2, 0, (6, 6, 6), 0),
+    (64, 64, 7, 1, 3, (9, 9, 9), 0),
+    (256, 128, 3, 2, 1, (16, 16, 16), 1),
+    (128, 64, 2, 2, 1, (9, 9, 9), 0),
+    (64, 64, 4, 2, 1, (8, 8, 8), 0),
+]
+
+
+@pytest.mark.parametrize("case", DGRAD)
+def test_igemm_transposed_conv_forward_equals_dgrad(case):
+    """ConvTranspose3d(cin->cout) forward == data-gradient kernel; covers all 8 output parity classes."""
+    import raygun_b200 as rb
+    from raygun_b200 import conv as CV
+    cin, cout, k, s, p, sp, op = case
+    torch.manual_seed(12)
+    x = _q(torch.randn(2, cin, *sp))
+    ct = torch.nn.ConvTranspose3d(cin, cout, k, stride=s, padding=p, output_padding=op)
+    w, b = _q(ct.weight.detach()), ct.bias.detach()
+    ref = TF.conv_transpose3d(x, w, b, stride=s, padding=p, output_padding=op)
+    before = CV.stats["igemm"]
+    with rb.precision("bf16"):
+        xg = x.to(DEV).bfloat16().contiguous(memory_format=torch.channels_last_3d)
+        y, ssum, _ = CV.conv_dgrad(xg, w.to(DEV), (2, cout, *ref.shape[2:]), (s,) * 3, (p,) * 3, 1, bias=b.to(DEV),
+                                   want_stats=True)
+    assert CV.stats["igemm"] == before + 1
+    assert _rel(y, ref) <= 1e-2, _rel(y, ref)
+    assert _rel(ssum.view(2, cout), y.float().cpu().sum(dim=(2, 3, 4))) <= 2e-3
+
+
+def test_bf16_generator_forward_backward_close_to_fp32_oracle():
+    """End-to-end bf16 path on a 64-channel ResNet generator: outputs within 2e-2 relative of the fp32
+    oracle (north_star bf16 tolerance), gradients finite and close."""
+    import raygun_b200 as rb
+    from oracle import restate as O
+    from raygun_b200 import conv as CV
+    from raygun_b200 import networks as N
+    torch.manual_seed(13)
+    net = N.ResNet(3, input_nc=1, ngf=64, n_blocks=2, padding_type="same")
+    N.init_weights(net, "kaiming")
+    sd = {k: v.detach().clone() for k, v in net.state_dict().items()}
+    x = torch.randn(1, 1, 24, 24, 24).clamp(-1, 1)
+    spec = O.resnet_spec(input_nc=1, ngf=64, n_blocks=2, padding_type="same", norm=dict(kind="instance", affine=False))
+    xr = x.clone().requires_grad_(True)
+    sdr = {k: v.clone().requires_grad_(True) for k, v in sd.items()}
+    ref = O.resnet3d_forward(sdr, spec, xr)
+    r = torch.randn_like(ref)
+    (ref * r).sum().backward()
+    net = net.to(DEV)
+    before = CV.stats["igemm"]
+    with rb.precision("bf16"):
+        xg = x.to(DEV).requires_grad_(True)
+        y = net(xg)
+        (y * r.to(DEV)).sum().backward()
+    assert CV.stats["igemm"] - before >= 10
+    assert y.dtype == torch.float32
+    assert _rel(y, ref) <= 2e-2, _rel(y, ref)
+    assert torch.isfinite(xg.grad).all()
+    gk = "model.10.conv_block.1.weight"
+    g = dict(net.named_parameters())[gk].grad
+    assert _rel(g, sdr[gk].grad) <= 5e-2, _rel(g, sdr[gk].grad)

@@ -1,0 +1,96 @@
+"""GPU parity, network level: the drop-in classes (fp32 kernel path) vs the committed golden vectors
+generated from the reference modules (tests/golden, oracle/make_golden.py) -- outputs, input gradients and
+every parameter gradient -- and the reference's own shape tests (tests/torch/networks/*_test.py) run
+against the new classes."""
+import functools
+
+import pytest
+import torch
+
+from tests._golden import build_ours, case_names, load_case, load_cycle
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def _rel(a, b):
+    a, b = a.detach().float().cpu(), b.detach().float().cpu()
+    return float((a - b).abs().max()) / max(1.0, float(b.abs().max()))
+
+
+@pytest.mark.parametrize("name", case_names())
+def test_fp32_forward_and_all_gradients_match_reference_golden(name):
+    import raygun_b200 as rb
+    c = load_case(name)
+    net = build_ours(c["kind"], c["kw"])
+    net.load_state_dict(c["sd"])
+    net = net.to(DEV).train()
+    with rb.precision("fp32"):
+        x = c["x"].to(DEV).requires_grad_(True)
+        y = net(x)
+        ys = y if isinstance(y, (list, tuple)) else [y]
+        assert len(ys) == len(c["ys"])
+        for a, b in zip(ys, c["ys"]):
+            assert a.dtype == torch.float32 and tuple(a.shape) == tuple(b.shape)
+            assert _rel(a, b) <= 1e-4, ("forward", _rel(a, b))     # north_star: fp32 max-abs <= 1e-4 per layer
+        loss = sum((a * r.to(DEV)).sum() for a, r in zip(ys, c["rs"]))
+        loss.backward()
+    assert _rel(x.grad, c["dx"]) <= 2e-4, ("dx", _rel(x.grad, c["dx"]))
+    params = dict(net.named_parameters())
+    for k, ref in c["grads"].items():
+        g = params[k].grad
+        if g is None:
+            assert float(ref.abs().max()) < 1e-4, k
+            continue
+        # the bias in front of a norm layer has a mathematically zero gradient: rounding noise only
+        tol = 3e-3 if k.endswith("bias") else 3e-4
+        assert _rel(g, ref) <= tol, (k, _rel(g, ref))
+
+
+def test_reference_shape_tests_on_the_new_classes():
+    """tests/torch/networks/{unet,resnet,nlayerdiscriminator}_test.py shape assertions."""
+    import raygun_b200 as rb
+    from raygun_b200 import networks as N
+    with rb.precision("fp32"), torch.no_grad():
+        cp = N.ConvPass(1, 4, [(3, 3, 3)], "ReLU").to(DEV)                    # unet_test.py:11-27
+        assert cp(torch.randn(1, 1, 10, 10, 10, device=DEV)).shape == (1, 4, 8, 8, 8)
+        u = N.UNet(input_nc=3, ngf=16, fmap_inc_factor=2, downsample_factors=[(2, 2, 2)] * 2,
+                   padding_type="same").to(DEV)                                # unet_test.py:172-196
+        assert u(torch.randn(1, 3, 32, 32, 32, device=DEV)).shape == (1, 16, 32, 32, 32)
+        g = N.ResNet(3, ngf=8).to(DEV)                                         # resnet_test.py:73-78
+        assert g(torch.randn(1, 1, 32, 32, 32, device=DEV)).shape == (1, 8, 32, 32, 32)
+        gv = N.ResNet(3, ngf=4, padding_type="valid", n_blocks=2).to(DEV)      # resnet_test.py:80-87 (scaled)
+        out = gv(torch.randn(1, 1, 64, 64, 64, device=DEV))
+        assert out.shape[2] == out.shape[3] == out.shape[4] and out.shape[1] == 4
+        gn = N.ResNet(3, ngf=4, n_blocks=1, add_noise=True).to(DEV)            # resnet_test.py:98-106
+        xin = torch.randn(1, 1, 16, 16, 16, device=DEV)
+        assert not torch.equal(gn(xin), gn(xin))
+        d = N.NLayerDiscriminator(3, ngf=8).to(DEV)                            # nlayerdiscriminator_test.py:42-50
+        assert d(torch.randn(2, 1, 32, 32, 32, device=DEV)).shape == (2, 1, 2, 2, 2)
+        md = N.MaxDownsample((2, 2, 2))
+        assert md(torch.randn(1, 2, 8, 8, 8, device=DEV)).shape == (1, 2, 4, 4, 4)
+
+
+def test_cyclegan_training_steps_match_reference_losses():
+    """Three LinkCycleLoss steps (fp32 path) vs the losses the reference produced (golden cycle_step.npz)."""
+    import raygun_b200 as rb
+    from raygun_b200.cyclegan import CycleGANStep, make_generator
+    from raygun_b200 import networks as N
+    c = load_cycle()
+    IN = functools.partial(torch.nn.InstanceNorm3d, affine=False, track_running_stats=False)
+    g1 = make_generator("resnet", dict(c["spec"]["gkw"]), output_nc=1).to(DEV)
+    g2 = make_generator("resnet", dict(c["spec"]["gkw"]), output_nc=1).to(DEV)
+    d1 = N.NLayerDiscriminator(3, norm_layer=IN, **c["spec"]["dkw"]).to(DEV)
+    d2 = N.NLayerDiscriminator(3, norm_layer=IN, **c["spec"]["dkw"]).to(DEV)
+    for net, nm in ((g1, "g1"), (g2, "g2"), (d1, "d1"), (d2, "d2")):
+        net.load_state_dict(c["sds"][nm])
+    with rb.precision("fp32"):
+        step = CycleGANStep(g1, g2, d1, d2, lr=c["spec"]["lr"])
+        with torch.no_grad():
+            fb = g1(c["batches"][0][0].to(DEV))
+        assert _rel(fb, c["fake_B0"]) <= 1e-4
+        for it, (a, b) in enumerate(c["batches"]):
+            out = step.step(a.to(DEV), b.to(DEV))
+            got = [float(out[k]) for k in ("G1", "G2", "D1", "D2")]
+            for gv, rv in zip(got, c["losses"][it]):
+                assert abs(gv - rv) <= 1e-3 * max(1.0, abs(rv)), (it, got, c["losses"][it])

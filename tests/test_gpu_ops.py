@@ -1,0 +1,235 @@
+"""GPU parity, operator level: every C-ABI kernel vs the CPU oracle (plain torch.nn.functional
+fp32/fp64 on the same seeded inputs).  fp32 path tolerance: max-abs <= 1e-4 (north_star)."""
+import pytest
+import torch
+import torch.nn.functional as TF
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-4
+
+
+def _dev():
+    return torch.device("cuda:0")
+
+
+def _close(a, b, tol=TOL, what=""):
+    a, b = a.detach().float().cpu(), b.detach().float().cpu()
+    assert a.shape == b.shape, (what, a.shape, b.shape)
+    err = float((a - b).abs().max()) if a.numel() else 0.0
+    assert err <= tol * max(1.0, float(b.abs().max()) if b.numel() else 1.0), (what, err)
+
+
+CONV_CASES = [
+    # cin, cout, k, stride, pad, groups, spatial
+    (1, 8, 3, 1, 0, 1, (9, 10, 11)),
+    (5, 7, 3, 1, 1, 1, (8, 8, 8)),
+    (4, 6, 7, 1, 3, 1, (9, 9, 9)),
+    (3, 5, 3, 2, 1, 1, (9, 10, 8)),
+    (6, 4, 2, 2, 1, 1, (9, 9, 9)),
+    (4, 8, 4, 2, 1, 1, (10, 10, 10)),
+    (4, 12, 1, 1, 0, 4, (5, 6, 7)),
+    (8, 1, 4, 1, 1, 1, (6, 6, 6)),
+    (3, 70, (1, 3, 2), (1, 2, 1), (0, 1, 0), 1, (4, 9, 7)),
+]
+
+
+@pytest.mark.parametrize("case", CONV_CASES)
+def test_direct_conv3d_forward_backward_fp32(case):
+    import raygun_b200 as rb
+    from raygun_b200 import functional as F
+    cin, cout, k, s, p, g, sp = case
+    torch.manual_seed(1)
+    x = torch.randn(2, cin, *sp, requires_grad=True)
+    conv = torch.nn.Conv3d(cin, cout, k, stride=s, padding=p, groups=g)
+    y_ref = conv(x)
+    r = torch.randn_like(y_ref)
+    gx, gw, gb = torch.autograd.grad((y_ref * r).sum(), [x, conv.weight, conv.bias])
+    with rb.precision("fp32"):
+        xg = x.detach().to(_dev()).requires_grad_(True)
+        w = conv.weight.detach().to(_dev()).requires_grad_(True)
+        b = conv.bias.detach().to(_dev()).requires_grad_(True)
+        y = F.conv3d(xg, w, b, s, p, g)
+        y.backward(r.to(_dev()))
+    _close(y, y_ref, what="y")
+    _close(xg.grad, gx, what="dx")
+    _close(w.grad, gw, 2e-4, what="dw")
+    _close(b.grad, gb, 2e-4, what="db")
+
+
+@pytest.mark.parametrize("case", [(6, 4, 2, 2, 0, 0, (4, 5, 6)), (5, 3, 3, 2, 1, 1, (4, 4, 5)), (4, 4, 3, 1, 1, 0, (5, 5, 5)),
+                                  (3, 6, 4, 2, 1, 0, (4, 4, 4))])
+def test_direct_conv_transpose3d_forward_backward_fp32(case):
+    import raygun_b200 as rb
+    from raygun_b200 import functional as F
+    cin, cout, k, s, p, op, sp = case
+    torch.manual_seed(2)
+    x = torch.randn(2, cin, *sp, requires_grad=True)
+    ct = torch.nn.ConvTranspose3d(cin, cout, k, stride=s, padding=p, output_padding=op)
+    y_ref = ct(x)
+    r = torch.randn_like(y_ref)
+    gx, gw, gb = torch.autograd.grad((y_ref * r).sum(), [x, ct.weight, ct.bias])
+    with rb.precision("fp32"):
+        xg = x.detach().to(_dev()).requires_grad_(True)
+        w = ct.weight.detach().to(_dev()).requires_grad_(True)
+        b = ct.bias.detach().to(_dev()).requires_grad_(True)
+        y = F.conv_transpose3d(xg, w, b, s, p, op)
+        y.backward(r.to(_dev()))
+    _close(y, y_ref, what="y")
+    _close(xg.grad, gx, what="dx")
+    _close(w.grad, gw, 2e-4, what="dw")
+    _close(b.grad, gb, 2e-4, what="db")
+
+
+@pytest.mark.parametrize("mode", ["reflect", "replicate", "zeros"])
+@pytest.mark.parametrize("lo,hi", [((1, 1, 1), (1, 1, 1)), ((3, 3, 3), (3, 3, 3)), ((0, 1, 2), (1, 0, 2))])
+def test_pad3d_and_its_adjoint(mode, lo, hi):
+    from raygun_b200 import functional as F
+    torch.manual_seed(3)
+    x = torch.randn(2, 3, 5, 6, 7, requires_grad=True)
+    pads = (lo[2], hi[2], lo[1], hi[1], lo[0], hi[0])
+    y_ref = TF.pad(x, pads, mode={"zeros": "constant"}.get(mode, mode))
+    r = torch.randn_like(y_ref)
+    (gx,) = torch.autograd.grad((y_ref * r).sum(), [x])
+    xg = x.detach().to(_dev()).requires_grad_(True)
+    y = F.pad3d(xg, lo, hi, mode)
+    y.backward(r.to(_dev()))
+    _close(y, y_ref, 0.0, "pad")
+    _close(xg.grad, gx, 1e-6, "pad adjoint")
+
+
+@pytest.mark.parametrize("kind", ["instance", "batch"])
+@pytest.mark.parametrize("act", ["none", "relu", "leaky"])
+@pytest.mark.parametrize("layout", ["ncdhw", "ndhwc"])
+def test_norm_act_forward_backward(kind, act, layout):
+    from raygun_b200 import functional as F
+    from raygun_b200 import nn as L
+    torch.manual_seed(4)
+    x = (torch.randn(2, 6, 5, 6, 7) * 2 + 0.5).requires_grad_(True)
+    res = torch.randn(2, 6, 5, 6, 7, requires_grad=True)
+    ref_norm = torch.nn.InstanceNorm3d(6) if kind == "instance" else torch.nn.BatchNorm3d(6)
+    if kind == "batch":
+        with torch.no_grad():
+            ref_norm.weight.uniform_(0.5, 1.5)
+            ref_norm.bias.uniform_(-0.5, 0.5)
+    f = {"none": lambda t: t, "relu": torch.relu, "leaky": lambda t: TF.leaky_relu(t, 0.2)}[act]
+    y_ref = f(ref_norm(x) + res)
+    r = torch.randn_like(y_ref)
+    params = [x, res] + (list(ref_norm.parameters()) if kind == "batch" else [])
+    grads = torch.autograd.grad((y_ref * r).sum(), params)
+    ours = (L.InstanceNorm3d(6) if kind == "instance" else L.BatchNorm3d(6)).to(_dev())
+    if kind == "batch":
+        with torch.no_grad():
+            ours.weight.copy_(ref_norm.weight)
+            ours.bias.copy_(ref_norm.bias)
+    code = {"none": (0, 0.0), "relu": (1, 0.0), "leaky": (2, 0.2)}[act]
+    xg = x.detach().to(_dev())
+    rg = res.detach().to(_dev())
+    if layout == "ndhwc":
+        xg = xg.contiguous(memory_format=torch.channels_last_3d)
+    xg.requires_grad_(True)
+    rg.requires_grad_(True)
+    y = ours.fused(xg, None, code[0], code[1], residual=rg)
+    y.backward(r.to(_dev()))
+    _close(y, y_ref, what="y")
+    _close(xg.grad, grads[0], 2e-4, "dx")
+    _close(rg.grad, grads[1], what="dres")
+    if kind == "batch":
+        _close(ours.weight.grad, grads[2], 2e-4, "dgamma")
+        _close(ours.bias.grad, grads[3], 2e-4, "dbeta")
+        _close(ours.running_mean, ref_norm.running_mean, what="running_mean")
+        _close(ours.running_var, ref_norm.running_var, what="running_var")
+        ours.eval(), ref_norm.eval()
+        _close(ours(x.detach().to(_dev())), ref_norm(x.detach()), what="eval")
+
+
+def test_maxpool_upsample_activation_cropcat():
+    from raygun_b200 import functional as F
+    torch.manual_seed(5)
+    x = torch.randn(2, 3, 7, 8, 6, requires_grad=True)
+    for f in [(2, 2, 2), (1, 2, 3)]:
+        y_ref = TF.max_pool3d(x, f, stride=f)
+        r = torch.randn_like(y_ref)
+        (gx,) = torch.autograd.grad((y_ref * r).sum(), [x])
+        xg = x.detach().to(_dev()).requires_grad_(True)
+        y = F.max_pool3d(xg, f)
+        y.backward(r.to(_dev()))
+        _close(y, y_ref, 0.0, "pool")
+        _close(xg.grad, gx, 0.0, "pool bwd")
+        y_ref = TF.interpolate(x, scale_factor=tuple(float(v) for v in f), mode="nearest")
+        r = torch.randn_like(y_ref)
+        (gx,) = torch.autograd.grad((y_ref * r).sum(), [x])
+        xg = x.detach().to(_dev()).requires_grad_(True)
+        y = F.upsample_nearest(xg, f)
+        y.backward(r.to(_dev()))
+        _close(y, y_ref, 0.0, "up")
+        _close(xg.grad, gx, 1e-6, "up bwd")
+    for code, fn in [(1, torch.relu), (2, lambda t: TF.leaky_relu(t, 0.2)), (3, torch.tanh), (4, torch.sigmoid)]:
+        y_ref = fn(x)
+        r = torch.randn_like(y_ref)
+        (gx,) = torch.autograd.grad((y_ref * r).sum(), [x])
+        xg = x.detach().to(_dev()).requires_grad_(True)
+        y = F.activation(xg, code, 0.2)
+        y.backward(r.to(_dev()))
+        _close(y, y_ref, 1e-6, "act")
+        _close(xg.grad, gx, 1e-5, "act bwd")
+    a = torch.randn(2, 3, 9, 10, 8, requires_grad=True)
+    b = torch.randn(2, 2, 7, 6, 6, requires_grad=True)
+    from oracle.restate import center_crop
+    y_ref = torch.cat([center_crop(a, (5, 6, 4)), center_crop(b, (5, 6, 4))], 1)
+    r = torch.randn_like(y_ref)
+    ga, gb = torch.autograd.grad((y_ref * r).sum(), [a, b])
+    ag, bg = a.detach().to(_dev()).requires_grad_(True), b.detach().to(_dev()).requires_grad_(True)
+    y = F.crop_cat(ag, bg, (5, 6, 4))
+    y.backward(r.to(_dev()))
+    _close(y, y_ref, 0.0, "cropcat")
+    _close(ag.grad, ga, 0.0, "cropcat da")
+    _close(bg.grad, gb, 0.0, "cropcat db")
+
+
+def test_losses_match_oracle():
+    from oracle import restate as O
+    from raygun_b200 import functional as F
+    torch.manual_seed(6)
+    a = (torch.randn(2, 1, 9, 9, 9) * 1.5).requires_grad_(True)
+    b = torch.randn(2, 1, 9, 9, 9, requires_grad=True)
+    cases = [("mse1", lambda u, v: O.gan_loss(u, True), lambda u, v: F.mse_const_loss(u, 1.0)),
+             ("mse0", lambda u, v: O.gan_loss(u, False), lambda u, v: F.mse_const_loss(u, 0.0)),
+             ("smoothl1", O.smooth_l1, F.smooth_l1_loss), ("l1", O.l1, F.l1_loss)]
+    for name, ref_fn, our_fn in cases:
+        l_ref = ref_fn(a, b) * 3.0
+        ga, gb = torch.autograd.grad(l_ref, [a, b], allow_unused=True)
+        ag, bg = a.detach().to(_dev()).requires_grad_(True), b.detach().to(_dev()).requires_grad_(True)
+        l = our_fn(ag, bg) * 3.0
+        l.backward()
+        assert abs(float(l) - float(l_ref)) <= 1e-5 * max(1.0, abs(float(l_ref))), name
+        _close(ag.grad, ga, 1e-6, name + " da")
+        if gb is not None:
+            _close(bg.grad, gb, 1e-6, name + " db")
+
+
+def test_predict_arithmetic_bit_exact():
+    from oracle import restate as O
+    from raygun_b200 import kernels as K
+    u = torch.arange(256, dtype=torch.uint8).repeat(40)
+    x = K.u8_normalise(u.to(_dev()), dtype=torch.float32)
+    assert torch.equal(x.cpu(), O.u8_normalise(u))
+    v = torch.linspace(-0.2, 1.2, 30000).view(1, 1, 30, 20, 50)
+    out = K.denorm_clamp_u8(v.to(_dev())[:, :, 2:-2, 3:-3, 4:-4])
+    assert torch.equal(out.cpu(), O.denorm_clamp_u8(v[:, :, 2:-2, 3:-3, 4:-4]))
+
+
+def test_adam_matches_oracle_restatement():
+    from oracle.restate import AdamState
+    from raygun_b200 import kernels as K
+    torch.manual_seed(7)
+    p = torch.randn(10007)
+    ref = {"p": p.clone()}
+    st = AdamState(ref, lr=1e-3)
+    pg = p.to(_dev())
+    m, v = torch.zeros_like(pg), torch.zeros_like(pg)
+    for step in range(1, 4):
+        g = torch.randn(10007)
+        st.step({"p": g})
+        K.adam_step(pg, g.to(_dev()), m, v, 1e-3, 0.9, 0.999, 1e-8, step)
+    _close(pg, ref["p"], 1e-6, "adam")
