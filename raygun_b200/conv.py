@@ -191,6 +191,21 @@ def conv_dgrad(dy, w, x_shape, stride, pad, groups=1, bias=None, act=ACT_NONE, s
 def conv_wgrad(x, dy, w_shape, stride, pad, groups=1, want_bias=False):
     """dw (fp32, conv layout) and optionally dbias = sum(dy)."""
     require_device(x)
+    cout, cin_g = w_shape[0], w_shape[1]
+    kernel = tuple(w_shape[2:])
+    if _igemm_ok(cin_g, cout, kernel, stride, groups) and groups == 1:
+        xb, dyb = K.convert(x, torch.bfloat16), K.convert(dy, torch.bfloat16)
+        n = x.shape[0]
+        plan = _get_plan(2, n, cin_g, cout, tuple(x.shape[2:]), tuple(dy.shape[2:]), kernel, stride, pad,
+                         _sp_strides(xb), _sp_strides(dyb), ACT_NONE, 0.0)
+        if plan is not None:
+            dw = torch.zeros(tuple(w_shape), dtype=torch.float32, device=x.device)
+            check(lib().rg_igemm_wgrad(plan.handle, ptr(xb), ptr(dyb), ptr(dw), None, None, stream_ptr(x.device)),
+                  "rg_igemm_wgrad")
+            count_launch()
+            stats["igemm"] += 1
+            db = K.norm_stats(dyb, _C.NORM_BATCH)[0] if want_bias else None
+            return dw, db
     dw = torch.empty(tuple(w_shape), dtype=torch.float32, device=x.device)
     db = torch.empty(w_shape[0], dtype=torch.float32, device=x.device) if want_bias else None
     g = _geom(tuple(w_shape[2:]), stride, pad, groups)

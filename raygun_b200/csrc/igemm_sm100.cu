@@ -263,6 +263,190 @@ __global__ void __launch_bounds__(IGEMM_THREADS, 1) igemm_conv_kernel(const __gr
   }
 }
 
+
+// -------------------------------------------------------------------------------------------------
+// Weight gradient:  dW[co][ci][tap] += sum_vox X[vox (+) tap][ci] * dY[vox][co]
+// GEMM view (both operands MN-major, i.e. the voxel/K index selects the 128 B smem row):
+//   D[M = 2 slabs x 64 ci][N = Cout tile] += A[M][K = 128 voxels] * B[N][K]
+//   A slab = TMA box {64 ci, tw, th, td, 1} of X shifted by one tap   (one slab per (tap, ci-chunk))
+//   B      = TMA boxes {64 co, tw, th, td, 1} of dY (loaded once per voxel chunk, shared by all slabs)
+// A CTA owns one (slab group, voxel split): all 512 TMEM columns hold 512/N accumulators of 128 x N,
+// it streams its voxel range once and finally reduces into dW with fp32 atomics.
+// -------------------------------------------------------------------------------------------------
+struct alignas(64) WgradParams {
+  CUtensorMap x_maps[8];
+  CUtensorMap dy_map;
+  int ntap[3];
+  signed char tap_off[3][MAX_TAPS_DIM];
+  signed char tap_par[3][MAX_TAPS_DIM];
+  signed char tap_kidx[3][MAX_TAPS_DIM];
+  int kdims[3];
+  int cin, cout;
+  int tiles_w, tiles_h, tiles_d, batch;
+  int tw, th, td;
+  int n_co_tiles, n_groups, n_splits, chunks_per_split, total_chunks;
+  int n_slabs;        // ntaps * cin/64
+  float* dw;          // [cout][cin][taps] fp32
+};
+
+template <int BN> struct WgradCfg {
+  static constexpr int NACC = 512 / BN;                 // accumulators (slab pairs) per CTA
+  static constexpr int B_BYTES = (BN / 64) * A_BYTES;   // dY slabs of one voxel chunk
+  static constexpr int A_STAGE = 2 * A_BYTES;           // one slab pair
+  static constexpr int A_STAGES = (BN >= 256) ? 3 : (BN >= 128 ? 4 : 5);
+  static constexpr int SMEM_BYTES = 1024 + 2 * B_BYTES + A_STAGES * A_STAGE + 256;
+};
+
+template <int BN>
+__global__ void __launch_bounds__(IGEMM_THREADS, 1) igemm_wgrad_kernel(const __grid_constant__ WgradParams p) {
+  using Cfg = WgradCfg<BN>;
+  constexpr int NACC = Cfg::NACC, AST = Cfg::A_STAGES;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = ptx::smem_u32(smem_raw);
+  const uint32_t base = (raw + 1023u) & ~1023u;
+  uint8_t* base_ptr = smem_raw + (base - raw);
+  const uint32_t smem_b = base;                              // 2 x B_BYTES
+  const uint32_t smem_a = base + 2 * Cfg::B_BYTES;           // AST x 32 KB
+  uint8_t* tail = base_ptr + 2 * Cfg::B_BYTES + AST * Cfg::A_STAGE;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(tail);        // afull[AST], aempty[AST], bfull[2], bempty[2], done
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tail + 8 * (2 * AST + 5));
+  const uint32_t bar0 = ptx::smem_u32(bars);
+  auto afull = [&](int s) { return bar0 + 8u * s; };
+  auto aempty = [&](int s) { return bar0 + 8u * (AST + s); };
+  auto bfull = [&](int s) { return bar0 + 8u * (2 * AST + s); };
+  auto bempty = [&](int s) { return bar0 + 8u * (2 * AST + 2 + s); };
+  const uint32_t done_bar = bar0 + 8u * (2 * AST + 4);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // unit decode: blockIdx.x = ((split * n_groups) + group) * n_co_tiles + co_tile
+  int u = blockIdx.x;
+  const int co_tile = u % p.n_co_tiles; u /= p.n_co_tiles;
+  const int group = u % p.n_groups;
+  const int split = u / p.n_groups;
+  const int c_begin = split * p.chunks_per_split;
+  const int c_end = min(c_begin + p.chunks_per_split, p.total_chunks);
+  const int ci_chunks = p.cin / 64;
+  const int first_slab = group * 2 * NACC;
+
+  if (warp == 0 && lane == 0) {
+    for (int s = 0; s < AST; ++s) { ptx::mbar_init(afull(s), 1); ptx::mbar_init(aempty(s), 1); }
+    for (int s = 0; s < 2; ++s) { ptx::mbar_init(bfull(s), 1); ptx::mbar_init(bempty(s), 1); }
+    ptx::mbar_init(done_bar, 1);
+    ptx::fence_mbar_init();
+    ptx::prefetch_tmap(&p.dy_map);
+    ptx::prefetch_tmap(&p.x_maps[0]);
+  }
+  if (warp == 1) ptx::tmem_alloc<512>(ptx::smem_u32(tmem_slot));
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // ================= TMA producer =================
+      int stage = 0; uint32_t phase = 0;
+      int bb = 0; uint32_t bphase = 0;
+      for (int chunk = c_begin; chunk < c_end; ++chunk) {
+        int m = chunk;
+        const int iw = m % p.tiles_w; m /= p.tiles_w;
+        const int ih = m % p.tiles_h; m /= p.tiles_h;
+        const int id = m % p.tiles_d; const int n = m / p.tiles_d;
+        const int w0 = iw * p.tw, h0 = ih * p.th, d0 = id * p.td;
+        ptx::mbar_wait(bempty(bb), bphase ^ 1u);
+        ptx::mbar_arrive_expect_tx(bfull(bb), Cfg::B_BYTES);
+#pragma unroll
+        for (int s = 0; s < BN / 64; ++s)
+          ptx::tma_load_5d(smem_b + bb * Cfg::B_BYTES + s * A_BYTES, &p.dy_map, bfull(bb), co_tile * BN + s * 64, w0, h0, d0, n);
+        if (++bb == 2) { bb = 0; bphase ^= 1u; }
+        for (int j = 0; j < NACC; ++j) {
+          ptx::mbar_wait(aempty(stage), phase ^ 1u);
+          ptx::mbar_arrive_expect_tx(afull(stage), Cfg::A_STAGE);
+#pragma unroll
+          for (int half = 0; half < 2; ++half) {
+            int slab = first_slab + 2 * j + half;
+            if (slab >= p.n_slabs) slab = p.n_slabs - 1;      // duplicate; masked in the epilogue
+            const int q = slab % ci_chunks;
+            int t = slab / ci_chunks;
+            const int c = t % p.ntap[2]; t /= p.ntap[2];
+            const int b = t % p.ntap[1]; const int a = t / p.ntap[1];
+            const int mi = p.tap_par[0][a] * 4 + p.tap_par[1][b] * 2 + p.tap_par[2][c];
+            ptx::tma_load_5d(smem_a + stage * Cfg::A_STAGE + half * A_BYTES, &p.x_maps[mi], afull(stage), q * 64,
+                             w0 + p.tap_off[2][c], h0 + p.tap_off[1][b], d0 + p.tap_off[0][a], n);
+          }
+          if (++stage == AST) { stage = 0; phase ^= 1u; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      // ================= MMA issuer =================
+      constexpr uint32_t idesc = ptx::idesc_bf16(TILE_M, BN, 1, 1);    // both operands MN-major
+      int stage = 0; uint32_t phase = 0;
+      int bb = 0; uint32_t bphase = 0;
+      for (int chunk = c_begin; chunk < c_end; ++chunk) {
+        ptx::mbar_wait(bfull(bb), bphase);
+        const uint64_t bdesc = ptx::smem_desc_sw128(smem_b + bb * Cfg::B_BYTES, A_BYTES, 1024);
+        for (int j = 0; j < NACC; ++j) {
+          ptx::mbar_wait(afull(stage), phase);
+          ptx::tc_fence_after();
+          const uint64_t adesc = ptx::smem_desc_sw128(smem_a + stage * Cfg::A_STAGE, A_BYTES, 1024);
+#pragma unroll
+          for (int k = 0; k < TILE_M / UMMA_K; ++k) {
+            // 16 voxels (K) = two 8-row groups = 2048 B further down the slab
+            ptx::umma_bf16(tmem_base + (uint32_t)(j * BN), adesc + (uint64_t)(128 * k), bdesc + (uint64_t)(128 * k), idesc,
+                           (chunk > c_begin || k > 0) ? 1u : 0u);
+          }
+          ptx::umma_commit(aempty(stage));
+          if (++stage == AST) { stage = 0; phase ^= 1u; }
+        }
+        ptx::umma_commit(bempty(bb));
+        if (++bb == 2) { bb = 0; bphase ^= 1u; }
+      }
+      ptx::umma_commit(done_bar);
+    }
+    __syncwarp();
+  } else if (c_end > c_begin) {
+    // ================= epilogue: TMEM -> fp32 atomics into dW =================
+    const int quad = warp & 3;
+    const int taps_total = p.kdims[0] * p.kdims[1] * p.kdims[2];
+    ptx::mbar_wait(done_bar, 0);
+    ptx::tc_fence_after();
+    for (int j = 0; j < NACC; ++j) {
+      const int slab = first_slab + 2 * j + (quad >> 1);
+      const bool valid = slab < p.n_slabs;                    // warp-uniform
+      int widx = 0, ci = 0;
+      if (valid) {
+        const int q = slab % ci_chunks;
+        int t = slab / ci_chunks;
+        const int c = t % p.ntap[2]; t /= p.ntap[2];
+        const int b = t % p.ntap[1]; const int a = t / p.ntap[1];
+        widx = (p.tap_kidx[0][a] * p.kdims[1] + p.tap_kidx[1][b]) * p.kdims[2] + p.tap_kidx[2][c];
+        ci = q * 64 + (quad & 1) * 32 + lane;
+      }
+#pragma unroll 1
+      for (int cb = 0; cb < BN; cb += 32) {
+        uint32_t v[32];
+        ptx::tmem_ld_32x32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(j * BN + cb), v);
+        ptx::tmem_ld_wait();
+        if (valid) {
+#pragma unroll
+          for (int e = 0; e < 32; ++e) {
+            const int co = co_tile * BN + cb + e;
+            atomicAdd(p.dw + ((size_t)co * p.cin + ci) * taps_total + widx, __uint_as_float(v[e]));
+          }
+        }
+      }
+    }
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc<512>(tmem_base);
+  }
+}
+
 }  // namespace rg
 
 // =================================================================================================
@@ -371,6 +555,18 @@ struct rg_plan {
 
 using namespace rg;
 
+template <int BN> static int launch_wgrad(const WgradParams& p, int grid, cudaStream_t st) {
+  using Cfg = WgradCfg<BN>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(igemm_wgrad_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(wgrad)");
+    attr_set = true;
+  }
+  igemm_wgrad_kernel<BN><<<grid, IGEMM_THREADS, Cfg::SMEM_BYTES, st>>>(p);
+  return RG_OK;
+}
+
 template <int BN> static int launch_bn(const IgemmParams& p, int grid, cudaStream_t st) {
   using Cfg = IgemmCfg<BN>;
   static bool attr_set = false;
@@ -388,9 +584,8 @@ extern "C" {
 int rg_plan_create(const rg_igemm_desc* d, rg_plan** out) {
   RG_CHECK_ARG(d && out, "rg_plan_create: null argument");
   RG_CHECK_ARG(d->mode >= 0 && d->mode <= 2, "rg_plan_create: bad mode");
-  RG_UNSUPPORTED(d->mode == 2, "rg_plan_create: tcgen05 wgrad not available yet");
-  const int kc = d->mode == 0 ? d->cin : d->cout;      // reduction channels
-  const int rows = d->mode == 0 ? d->cout : d->cin;    // produced channels
+  const int kc = d->mode == 1 ? d->cout : d->cin;      // reduction channels (wgrad: the slab channels)
+  const int rows = d->mode == 1 ? d->cin : d->cout;    // produced channels  (wgrad: the N dimension)
   RG_UNSUPPORTED(kc % 64 != 0, "igemm: reduction channels (%d) must be a multiple of 64", kc);
   RG_UNSUPPORTED(rows % 64 != 0, "igemm: output channels (%d) must be a multiple of 64", rows);
   for (int i = 0; i < 3; ++i) {
@@ -407,7 +602,7 @@ int rg_plan_create(const rg_igemm_desc* d, rg_plan** out) {
   pl->taps = d->kernel[0] * d->kernel[1] * d->kernel[2];
   pl->bn = rows % 256 == 0 ? 256 : (rows % 128 == 0 ? 128 : 64);
 
-  const int nclass = d->mode == 0 ? 1 : d->stride[0] * d->stride[1] * d->stride[2];
+  const int nclass = d->mode != 1 ? 1 : d->stride[0] * d->stride[1] * d->stride[2];
   for (int cls = 0; cls < nclass; ++cls) {
     Launch L;
     memset(&L, 0, sizeof(L));
@@ -417,7 +612,7 @@ int rg_plan_create(const rg_igemm_desc* d, rg_plan** out) {
     for (int i = 0; i < 3; ++i) {
       int nt = 0;
       const int s = d->stride[i], pd = d->pad[i];
-      if (d->mode == 0) {
+      if (d->mode != 1) {
         for (int k = 0; k < d->kernel[i]; ++k) {
           int e = k - pd;
           int par = ((e % s) + s) % s;
@@ -476,6 +671,7 @@ int rg_igemm_run(const rg_plan* pl, const void* in, const void* w_packed, const 
                  float* stats_sum, float* stats_sqsum, void* workspace, void* stream) {
   (void)workspace;
   RG_CHECK_ARG(pl && in && w_packed && outp, "rg_igemm_run: null argument");
+  RG_CHECK_ARG(pl->d.mode != 2, "rg_igemm_run: plan was created for wgrad");
   RG_CHECK_ARG((stats_sum == nullptr) == (stats_sqsum == nullptr), "rg_igemm_run: stats pointers must come together");
   const rg_igemm_desc& d = pl->d;
   cudaStream_t st = (cudaStream_t)stream;
@@ -511,11 +707,56 @@ int rg_igemm_run(const rg_plan* pl, const void* in, const void* w_packed, const 
   return RG_OK;
 }
 
-int rg_igemm_wgrad(const rg_plan* plan, const void* x, const void* dy, float* dw, float* dbias, void* workspace,
+int rg_igemm_wgrad(const rg_plan* pl, const void* x, const void* dy, float* dw, float* dbias, void* workspace,
                    void* stream) {
-  (void)plan; (void)x; (void)dy; (void)dw; (void)dbias; (void)workspace; (void)stream;
-  set_error("rg_igemm_wgrad: not available yet");
-  return RG_E_UNSUPPORTED;
+  (void)workspace;
+  RG_CHECK_ARG(pl && x && dy && dw, "rg_igemm_wgrad: null argument");
+  RG_CHECK_ARG(pl->d.mode == 2, "rg_igemm_wgrad: plan was not created for wgrad");
+  RG_CHECK_ARG(dbias == nullptr, "rg_igemm_wgrad: dbias is produced by rg_norm_stats(kind=batch) on dy");
+  const rg_igemm_desc& d = pl->d;
+  cudaStream_t st = (cudaStream_t)stream;
+  const Launch& L = pl->launches[0];
+  WgradParams p;
+  memset(&p, 0, sizeof(p));
+  memcpy(p.ntap, L.p.ntap, sizeof(p.ntap));
+  memcpy(p.tap_off, L.p.tap_off, sizeof(p.tap_off));
+  memcpy(p.tap_par, L.p.tap_par, sizeof(p.tap_par));
+  memcpy(p.tap_kidx, L.p.tap_kidx, sizeof(p.tap_kidx));
+  memcpy(p.kdims, L.p.kdims, sizeof(p.kdims));
+  p.cin = d.cin; p.cout = d.cout;
+  p.tiles_w = L.p.tiles_w; p.tiles_h = L.p.tiles_h; p.tiles_d = L.p.tiles_d; p.batch = d.n;
+  p.tw = L.p.tw; p.th = L.p.th; p.td = L.p.td;
+  int rc;
+  for (int mi = 0; mi < 8; ++mi) {
+    if (!L.a_used[mi]) continue;
+    const int off[3] = {(mi >> 2) & 1, (mi >> 1) & 1, mi & 1};
+    rc = encode_act_map(&p.x_maps[mi], x, d.cin, d.in_dhw, d.n, d.x_strides, off, d.stride, L.box);
+    if (rc) return rc;
+  }
+  const int zero[3] = {0, 0, 0}, one[3] = {1, 1, 1};
+  rc = encode_act_map(&p.dy_map, dy, d.cout, d.out_dhw, d.n, d.y_strides, zero, one, L.box);
+  if (rc) return rc;
+  const int bn = pl->bn;
+  const int nacc = 512 / bn;
+  p.n_co_tiles = d.cout / bn;
+  p.n_slabs = pl->taps * (d.cin / 64);
+  p.n_groups = (p.n_slabs + 2 * nacc - 1) / (2 * nacc);
+  p.total_chunks = p.tiles_w * p.tiles_h * p.tiles_d * p.batch;
+  const long long base_units = (long long)p.n_groups * p.n_co_tiles;
+  long long splits = (2LL * num_sms() + base_units - 1) / base_units;     // ~2 waves of CTAs
+  const long long max_splits = (p.total_chunks + 3) / 4;                   // >= 4 chunks per CTA
+  if (splits > max_splits) splits = max_splits;
+  if (splits < 1) splits = 1;
+  p.chunks_per_split = (int)((p.total_chunks + splits - 1) / splits);
+  p.n_splits = (p.total_chunks + p.chunks_per_split - 1) / p.chunks_per_split;
+  p.dw = dw;
+  const int grid = (int)(base_units * p.n_splits);
+  if (bn == 256) rc = launch_wgrad<256>(p, grid, st);
+  else if (bn == 128) rc = launch_wgrad<128>(p, grid, st);
+  else rc = launch_wgrad<64>(p, grid, st);
+  if (rc) return rc;
+  RG_LAUNCH_CHECK("rg_igemm_wgrad");
+  return RG_OK;
 }
 
 }  // extern "C"

@@ -78,8 +78,8 @@ def test_cyclegan_training_steps_match_reference_losses():
     from raygun_b200 import networks as N
     c = load_cycle()
     IN = functools.partial(torch.nn.InstanceNorm3d, affine=False, track_running_stats=False)
-    g1 = make_generator("resnet", dict(c["spec"]["gkw"]), output_nc=1).to(DEV)
-    g2 = make_generator("resnet", dict(c["spec"]["gkw"]), output_nc=1).to(DEV)
+    g1 = make_generator("resnet", dict(c["spec"]["gkw"]), output_nc=1, final_activation="Tanh").to(DEV)
+    g2 = make_generator("resnet", dict(c["spec"]["gkw"]), output_nc=1, final_activation="Tanh").to(DEV)
     d1 = N.NLayerDiscriminator(3, norm_layer=IN, **c["spec"]["dkw"]).to(DEV)
     d2 = N.NLayerDiscriminator(3, norm_layer=IN, **c["spec"]["dkw"]).to(DEV)
     for net, nm in ((g1, "g1"), (g2, "g2"), (d1, "d1"), (d2, "d2")):
