@@ -1,0 +1,325 @@
+#!/usr/bin/env python
+"""bench.py -- the hot path of htem/raygun on B200: one step = one pass of the 3-D generator
+(forward + backward + loss) over one batch of synthetic EM-like uint8 volumes.
+
+Workload at N=1 (BASELINE.json configs[1], "cfg2"): G-ResNet9 = Sequential(ResNet(3, input_nc=1, ngf=64,
+n_blocks=9, InstanceNorm3d, padding 'same'), Conv3d(64,1,1), Tanh) forward+backward on a 2x1x128^3 patch,
+bf16 tensor-core path with fp32 accumulation / fp32 master weights, SmoothL1 loss against a synthetic target.
+N>1: the same per-GPU batch on every rank (weak scaling), gradients all-reduced with NCCL before they would
+be consumed by the optimizer.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload cfg2|cfg2-small]
+
+Prints ONE JSON line (rank 0).  `value` is device-timed with inputs resident in HBM; `e2e` goes through the
+public API from pinned HOST uint8 buffers (H2D + u8 normalise + step + D2H of the loss) every step.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+WORKLOADS = {
+    # name: (batch, side, n_blocks, ngf)
+    "cfg2": (2, 128, 9, 64),
+    "cfg2-small": (1, 64, 9, 64),
+}
+
+
+def conv_flops_resnet(batch, side, n_blocks, ngf, n_down=2):
+    """Algorithmic FLOPs (2 x MACs of Conv3d / ConvTranspose3d) of G-ResNet forward; SURVEY 8(d) convention."""
+    fl = 0.0
+    s = side
+    fl += 2.0 * batch * s ** 3 * ngf * 1 * 343                    # stem 7^3 1->ngf
+    c = ngf
+    for _ in range(n_down):
+        s //= 2
+        fl += 2.0 * batch * s ** 3 * (2 * c) * c * 27
+        c *= 2
+    fl += n_blocks * 2 * (2.0 * batch * s ** 3 * c * c * 27)
+    for _ in range(n_down):
+        fl += 2.0 * batch * s ** 3 * c * (c // 2) * 27               # ConvT k3 s2: MACs = in_voxels*cin*cout*27
+        s *= 2
+        c //= 2
+    fl += 2.0 * batch * s ** 3 * ngf * ngf * 343                    # head 7^3 ngf->ngf
+    fl += 2.0 * batch * s ** 3 * ngf * 1                           # 1x1x1 -> 1
+    return fl
+
+
+def load_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            p = json.load(f)
+        return dict(tf_burst=p["bf16_tflops"], tf_sustained=p.get("bf16_tflops_sustained", p["bf16_tflops"]),
+                    hbm=p["hbm_gbs"], source="measured")
+    return dict(tf_burst=1590.0, tf_sustained=1400.0, hbm=6650.0, source="fallback")
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return dict(sm_mhz=None, sm_max_mhz=None, reasons=["nvidia-smi unavailable"])
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx = float(r[1])
+                for nm, v in zip(names, r[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(nm)
+            except Exception:
+                pass
+        sm.sort()
+        return dict(sm_mhz=sm[len(sm) // 2] if sm else None, sm_max_mhz=mx, samples=len(sm), reasons=sorted(reasons))
+
+
+def synth_batch(batch, side, seed):
+    from raygun_b200.synth import em_like_u8
+    import numpy as np
+    return torch.from_numpy(np.stack([em_like_u8((side, side, side), seed=seed + i)[None] for i in range(batch)]))
+
+
+# ---------------------------------------------------------------------------------------------
+# reference arm / CPU baseline: the oracle port (the reference's algorithm restated over plain
+# torch.nn.functional, oracle/restate.py) on the host cores
+# ---------------------------------------------------------------------------------------------
+def cpu_step_fn(n_blocks, ngf, side, batch=1):
+    from oracle import restate as O
+    import raygun_b200.networks as N  # constructors only (parameter shapes / init); arithmetic is the oracle's
+    torch.manual_seed(42)
+    g = torch.nn.Sequential(N.ResNet(3, input_nc=1, ngf=ngf, n_blocks=n_blocks, padding_type="same"),
+                            torch.nn.Conv3d(ngf, 1, 1), torch.nn.Tanh())
+    N.init_weights(g, "kaiming")
+    sd = {k: v.detach().clone().requires_grad_(v.is_floating_point()) for k, v in g.state_dict().items()}
+    spec = O.resnet_spec(input_nc=1, ngf=ngf, n_blocks=n_blocks, padding_type="same",
+                         norm=dict(kind="instance", affine=False))
+    x = O.u8_normalise(synth_batch(batch, side, 42))
+    tgt = O.u8_normalise(synth_batch(batch, side, 43))
+    leaves = [v for v in sd.values() if v.requires_grad]
+
+    def step():
+        y = O.generator_forward(sd, "resnet", spec, x, final_activation="Tanh")
+        loss = O.smooth_l1(tgt, y)
+        torch.autograd.grad(loss, leaves, allow_unused=True)
+        return float(loss)
+
+    return step, batch * side ** 3
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    batch, side, n_blocks, ngf = WORKLOADS[args.workload]
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    sample_side = 48 if side >= 128 else 32
+    step, vox = cpu_step_fn(n_blocks, ngf, sample_side)
+    for _ in range(max(1, min(args.warmup, 1))):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step()
+    dt = (time.perf_counter() - t0) / args.steps
+    val = vox / dt
+    sample = f"1x1x{sample_side}^3 patch per step (network is fully convolutional; full workload {batch}x1x{side}^3)"
+    out = dict(metric="generator_train_voxels_per_sec", value=val, unit="voxels/s", impl="reference", n_gpus=args.gpus,
+               steps=args.steps, warmup=args.warmup, ms_per_step=dt * 1e3, higher_is_better=True, scaling="weak",
+               vs_baseline=None, dtype="f32", data="synthetic",
+               config=dict(workload=f"{args.workload}: G-ResNet{n_blocks} fwd+bwd+SmoothL1, CPU oracle port", sample=sample),
+               cpu_baseline=dict(value=val, unit="voxels/s", cores=cores, kind="port", sample=sample),
+               e2e=dict(value=val, unit="voxels/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0))
+    print(json.dumps(out))
+
+
+# ---------------------------------------------------------------------------------------------
+# our arm
+# ---------------------------------------------------------------------------------------------
+def run_ours(args):
+    import torch.distributed as dist
+
+    import raygun_b200 as rb
+    from raygun_b200 import _C
+    from raygun_b200 import conv as CV
+    from raygun_b200 import functional as F
+    from raygun_b200 import kernels as K
+    from raygun_b200.cyclegan import make_generator
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (raygun_b200 has no CPU path; use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    rb.set_precision("bf16")
+    batch, side, n_blocks, ngf = WORKLOADS[args.workload]
+
+    torch.manual_seed(42)
+    g = make_generator("resnet", dict(input_nc=1, output_nc=1, ngf=ngf, n_blocks=n_blocks, padding_type="same",
+                                      final_activation="Tanh")).to(dev)
+    params = [p for p in g.parameters()]
+    host_x = synth_batch(batch, side, 42 + 10 * rank).pin_memory()
+    host_t = synth_batch(batch, side, 43 + 10 * rank).pin_memory()
+    x_dev = K.u8_normalise(host_x.to(dev), dtype=torch.float32)
+    t_dev = K.u8_normalise(host_t.to(dev), dtype=torch.float32)
+
+    def step(x, t):
+        for p in params:
+            p.grad = None
+        y = g(x)
+        loss = F.smooth_l1_loss(t, y)
+        loss.backward()
+        if world > 1:   # data-parallel: average gradients over ranks (flat bucket, NCCL over NVLink)
+            flat = torch.cat([p.grad.reshape(-1) for p in params])
+            dist.all_reduce(flat)
+            flat.div_(world)
+        return loss
+
+    def e2e_step():
+        xu = host_x.to(dev, non_blocking=True)
+        tu = host_t.to(dev, non_blocking=True)
+        loss = step(K.u8_normalise(xu, dtype=torch.float32), K.u8_normalise(tu, dtype=torch.float32))
+        return float(loss)     # D2H of the step's result
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1) / steps
+        if world > 1:
+            t = torch.tensor([ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t)
+        return ms
+
+    for _ in range(max(args.warmup, 3)):
+        step(x_dev, t_dev)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = _C.launch_count
+    ms = timed(lambda: step(x_dev, t_dev), args.steps)
+    launches = (_C.launch_count - l0) // args.steps
+    clocks = sampler.stop() if rank == 0 else None
+    ms_e2e = timed(e2e_step, args.steps)
+
+    # roofline of the dominant kernel family (tcgen05 implicit-GEMM convolutions), timed per launch with
+    # CUDA events on the launching stream over one extra step
+    CV.profile = []
+    step(x_dev, t_dev)
+    torch.cuda.synchronize()
+    prof, CV.profile = CV.profile, None
+    by_kind = {}
+    for kind, fl, a, b in prof:
+        d = by_kind.setdefault(kind, [0.0, 0.0, 0])
+        d[0] += fl
+        d[1] += a.elapsed_time(b)
+        d[2] += 1
+    peaks = load_peaks()
+    tot_fl = sum(v[0] for v in by_kind.values())
+    tot_ms = sum(v[1] for v in by_kind.values())
+    achieved = tot_fl / (tot_ms * 1e-3) / 1e12 if tot_ms > 0 else 0.0
+    peak = peaks["tf_sustained"]
+    roofline = dict(bound="tensor", kernel="igemm_conv_kernel / igemm_wgrad_kernel (tcgen05, all conv launches of one step)",
+                    achieved=achieved, peak=peak, unit="TFLOP/s", frac=achieved / peak,
+                    peak_kind=f"{peaks['source']} sustained bf16 (burst {peaks['tf_burst']})", traffic=None,
+                    launches=sum(v[2] for v in by_kind.values()), share_of_step=tot_ms / ms,
+                    by_kind={k: dict(tflops=v[0] / (v[1] * 1e-3) / 1e12, ms=v[1], launches=v[2]) for k, v in by_kind.items()})
+
+    if rank == 0:
+        vox = batch * side ** 3 * world
+        fwd = conv_flops_resnet(batch, side, n_blocks, ngf)
+        cores = os.cpu_count() or 1
+        torch.set_num_threads(cores)
+        cstep, cvox = cpu_step_fn(n_blocks, ngf, 48 if side >= 128 else 32)
+        cstep()
+        t0 = time.perf_counter()
+        cstep()
+        cdt = time.perf_counter() - t0
+        out = dict(metric="generator_train_voxels_per_sec", value=vox / (ms * 1e-3), unit="voxels/s", n_gpus=world,
+                   steps=args.steps, warmup=max(args.warmup, 3), ms_per_step=ms, higher_is_better=True, scaling="weak",
+                   vs_baseline=None, dtype="bf16", data="synthetic",
+                   config=dict(workload=f"{args.workload}: G-ResNet{n_blocks} (ngf {ngf}, InstanceNorm, reflect 'same') "
+                                        f"fwd+bwd+SmoothL1 on {batch}x1x{side}^3 per GPU",
+                               l2="activation working set (GBs) >> 126 MB L2; no explicit flush",
+                               parallelism=f"dp{world}" if world > 1 else "single", algorithmic_tflop_per_step=3 * fwd / 1e12),
+                   step_tflops=3 * fwd * world / (ms * 1e-3) / 1e12,
+                   e2e=dict(value=vox / (ms_e2e * 1e-3), unit="voxels/s", ms_per_step=ms_e2e,
+                            h2d_bytes_per_step=int(host_x.numel() + host_t.numel()), d2h_bytes_per_step=4),
+                   gpu_launches=int(launches), roofline=roofline,
+                   cpu_baseline=dict(value=cvox / cdt, unit="voxels/s", cores=cores, kind="port",
+                                     sample=f"1x1x{48 if side >= 128 else 32}^3 fwd+bwd, oracle/restate.py, 1 warm-up + 1 timed"),
+                   clocks=clocks, conv_paths=dict(CV.stats))
+        print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS))
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -17,6 +17,32 @@ from ._C import ACT_NONE, ConvGeom, IgemmDesc, check, count_launch, i3, lib, ptr
 
 stats = {"igemm": 0, "direct": 0}     # which path convolutions took (tests / bench inspect this)
 
+# Optional per-launch device timing of the tensor-core kernels (bench.py's roofline): when `profile`
+# is a list, every igemm launch appends (kind, flops, start_event, end_event) recorded on the
+# launching stream.
+profile = None
+
+
+class _Timed:
+    def __init__(self, kind, flops, device):
+        self.on = profile is not None
+        if self.on:
+            self.kind, self.flops = kind, flops
+            self.e0 = torch.cuda.Event(enable_timing=True)
+            self.e1 = torch.cuda.Event(enable_timing=True)
+            self.stream = torch.cuda.current_stream(device)
+
+    def __enter__(self):
+        if self.on:
+            self.e0.record(self.stream)
+        return self
+
+    def __exit__(self, *exc):
+        if self.on:
+            self.e1.record(self.stream)
+            profile.append((self.kind, self.flops, self.e0, self.e1))
+        return False
+
 
 def _geom(kernel, stride, pad, groups=1, act=ACT_NONE, slope=0.0):
     g = ConvGeom()
@@ -134,9 +160,10 @@ def conv_fprop(x, w, bias, stride, pad, groups=1, act=ACT_NONE, slope=0.0, want_
         if plan is not None:
             wf, _ = packed_weights(w)
             st = torch.zeros(2, n * cout, dtype=torch.float32, device=x.device) if want_stats else None
-            check(lib().rg_igemm_run(plan.handle, ptr(xb), ptr(wf), ptr(bias_f), ptr(y),
-                                     ptr(st[0]) if want_stats else None, ptr(st[1]) if want_stats else None, None,
-                                     stream_ptr(x.device)), "rg_igemm_run(fprop)")
+            with _Timed("fprop", 2.0 * y.numel() * cin_t * kernel[0] * kernel[1] * kernel[2], x.device):
+                check(lib().rg_igemm_run(plan.handle, ptr(xb), ptr(wf), ptr(bias_f), ptr(y),
+                                         ptr(st[0]) if want_stats else None, ptr(st[1]) if want_stats else None, None,
+                                         stream_ptr(x.device)), "rg_igemm_run(fprop)")
             count_launch()
             stats["igemm"] += 1
             return (y, st[0], st[1]) if want_stats else (y, None, None)
@@ -170,9 +197,10 @@ def conv_dgrad(dy, w, x_shape, stride, pad, groups=1, bias=None, act=ACT_NONE, s
         if plan is not None:
             _, wdp = packed_weights(w)
             st = torch.zeros(2, n * cin_t, dtype=torch.float32, device=dy.device) if want_stats else None
-            check(lib().rg_igemm_run(plan.handle, ptr(dyb), ptr(wdp), ptr(bias_f), ptr(dx),
-                                     ptr(st[0]) if want_stats else None, ptr(st[1]) if want_stats else None, None,
-                                     stream_ptr(dy.device)), "rg_igemm_run(dgrad)")
+            with _Timed("dgrad", 2.0 * dyb.numel() * cin_t * kernel[0] * kernel[1] * kernel[2], dy.device):
+                check(lib().rg_igemm_run(plan.handle, ptr(dyb), ptr(wdp), ptr(bias_f), ptr(dx),
+                                         ptr(st[0]) if want_stats else None, ptr(st[1]) if want_stats else None, None,
+                                         stream_ptr(dy.device)), "rg_igemm_run(dgrad)")
             count_launch(stride[0] * stride[1] * stride[2])
             stats["igemm"] += 1
             return (dx, st[0], st[1]) if want_stats else (dx, None, None)
@@ -200,8 +228,9 @@ def conv_wgrad(x, dy, w_shape, stride, pad, groups=1, want_bias=False):
                          _sp_strides(xb), _sp_strides(dyb), ACT_NONE, 0.0)
         if plan is not None:
             dw = torch.zeros(tuple(w_shape), dtype=torch.float32, device=x.device)
-            check(lib().rg_igemm_wgrad(plan.handle, ptr(xb), ptr(dyb), ptr(dw), None, None, stream_ptr(x.device)),
-                  "rg_igemm_wgrad")
+            with _Timed("wgrad", 2.0 * dyb.numel() * cin_g * kernel[0] * kernel[1] * kernel[2], x.device):
+                check(lib().rg_igemm_wgrad(plan.handle, ptr(xb), ptr(dyb), ptr(dw), None, None,
+                                           stream_ptr(x.device)), "rg_igemm_wgrad")
             count_launch()
             stats["igemm"] += 1
             db = K.norm_stats(dyb, _C.NORM_BATCH)[0] if want_bias else None
