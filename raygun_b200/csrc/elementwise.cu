@@ -3,6 +3,7 @@
 // All kernels are grid-stride loops sized to a multiple of the 148 SMs; the loop order follows the
 // innermost storage dimension of the destination so that stores (and usually loads) coalesce.
 #include "common.cuh"
+#include "vec_ndhwc.cuh"
 
 namespace rg {
 
@@ -138,6 +139,117 @@ __global__ void act_bwd_kernel(T5 yd, const TY* __restrict__ y, T5 gd, const TG*
   }
 }
 
+
+// ------------------------------------------------------------------------------------------
+// vectorised NDHWC bf16 fast paths (8 channels / thread)
+// ------------------------------------------------------------------------------------------
+__global__ void vec_copy_kernel(T5 dd, __nv_bfloat16* __restrict__ dst, T5 sd, const __nv_bfloat16* __restrict__ src,
+                                bool accumulate) {
+  const long long total = dd.numel() >> 3;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    VIdx p = vunravel(i, dd);
+    float v[8];
+    ld8(src + voff(sd, p.n, p.d, p.h, p.w, p.c), v);
+    __nv_bfloat16* q = dst + voff(dd, p.n, p.d, p.h, p.w, p.c);
+    if (accumulate) {
+      float o[8];
+      ld8(q, o);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) v[k] += o[k];
+    }
+    st8(q, v);
+  }
+}
+
+__global__ void vec_pad_fwd_kernel(T5 xd, const __nv_bfloat16* __restrict__ x, T5 yd, __nv_bfloat16* __restrict__ y,
+                                   int lo_d, int lo_h, int lo_w, int mode) {
+  const long long total = yd.numel() >> 3;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    VIdx p = vunravel(i, yd);
+    bool vd, vh, vw;
+    const long long id = pad_src(p.d, lo_d, xd.d, mode, vd);
+    const long long ih = pad_src(p.h, lo_h, xd.h, mode, vh);
+    const long long iw = pad_src(p.w, lo_w, xd.w, mode, vw);
+    float v[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    if (vd && vh && vw) ld8(x + voff(xd, p.n, id, ih, iw, p.c), v);
+    st8(y + voff(yd, p.n, p.d, p.h, p.w, p.c), v);
+  }
+}
+
+// k-th padded-output index that reads input index i (k = 0 is always the interior image i + lo).
+__device__ __forceinline__ int pad_npre(long long i, long long lo, long long hi, long long size, int mode) {
+  if (mode == RG_PAD_REFLECT) return 1 + (i >= 1 && i <= lo ? 1 : 0) + (i <= size - 2 && i >= size - 1 - hi ? 1 : 0);
+  if (mode == RG_PAD_REPLICATE) return 1 + (i == 0 ? (int)lo : 0) + (i == size - 1 ? (int)hi : 0);
+  return 1;
+}
+__device__ __forceinline__ long long pad_pre(long long i, int k, long long lo, long long hi, long long size, int mode) {
+  if (k == 0) return i + lo;
+  if (mode == RG_PAD_REFLECT) {
+    const bool low = (i >= 1 && i <= lo);
+    if (low && k == 1) return lo - i;
+    return lo + 2 * (size - 1) - i;
+  }
+  // replicate: border voxels absorb the shell
+  if (i == 0 && k <= lo) return k - 1;
+  const int kk = k - 1 - (i == 0 ? (int)lo : 0);
+  return lo + size + kk;
+}
+
+__global__ void vec_pad_bwd_kernel(T5 gd, const __nv_bfloat16* __restrict__ dy, T5 dxd, __nv_bfloat16* __restrict__ dx,
+                                   int lo_d, int lo_h, int lo_w, int mode) {
+  const long long total = dxd.numel() >> 3;
+  const long long hi_d = gd.d - dxd.d - lo_d, hi_h = gd.h - dxd.h - lo_h, hi_w = gd.w - dxd.w - lo_w;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    VIdx p = vunravel(i, dxd);
+    const int nd = pad_npre(p.d, lo_d, hi_d, dxd.d, mode), nh = pad_npre(p.h, lo_h, hi_h, dxd.h, mode),
+              nw = pad_npre(p.w, lo_w, hi_w, dxd.w, mode);
+    float acc[8];
+    __nv_bfloat16* q = dx + voff(dxd, p.n, p.d, p.h, p.w, p.c);
+    ld8(q, acc);
+    for (int a = 0; a < nd; ++a) {
+      const long long od = pad_pre(p.d, a, lo_d, hi_d, dxd.d, mode);
+      for (int b = 0; b < nh; ++b) {
+        const long long oh = pad_pre(p.h, b, lo_h, hi_h, dxd.h, mode);
+        for (int c = 0; c < nw; ++c) {
+          const long long ow = pad_pre(p.w, c, lo_w, hi_w, dxd.w, mode);
+          float v[8];
+          ld8(dy + voff(gd, p.n, od, oh, ow, p.c), v);
+#pragma unroll
+          for (int k = 0; k < 8; ++k) acc[k] += v[k];
+        }
+      }
+    }
+    st8(q, acc);
+  }
+}
+
+__global__ void vec_act_fwd_kernel(T5 xd, const __nv_bfloat16* __restrict__ x, T5 yd, __nv_bfloat16* __restrict__ y,
+                                   int act, float slope) {
+  const long long total = yd.numel() >> 3;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    VIdx p = vunravel(i, yd);
+    float v[8];
+    ld8(x + voff(xd, p.n, p.d, p.h, p.w, p.c), v);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) v[k] = act_apply(v[k], act, slope);
+    st8(y + voff(yd, p.n, p.d, p.h, p.w, p.c), v);
+  }
+}
+
+__global__ void vec_act_bwd_kernel(T5 yd, const __nv_bfloat16* __restrict__ y, T5 gd, const __nv_bfloat16* __restrict__ dy,
+                                   T5 dxd, __nv_bfloat16* __restrict__ dx, int act, float slope) {
+  const long long total = dxd.numel() >> 3;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    VIdx p = vunravel(i, dxd);
+    float yy[8], g[8];
+    ld8(y + voff(yd, p.n, p.d, p.h, p.w, p.c), yy);
+    ld8(dy + voff(gd, p.n, p.d, p.h, p.w, p.c), g);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) g[k] *= act_grad_from_y(yy[k], act, slope);
+    st8(dx + voff(dxd, p.n, p.d, p.h, p.w, p.c), g);
+  }
+}
+
 }  // namespace rg
 
 using namespace rg;
@@ -152,6 +264,11 @@ int rg_copy5(const rg_tensor5* dd, void* dst, const rg_tensor5* sd, const void* 
   if (total == 0) return RG_OK;
   bool ci = channels_inner(dd);
   cudaStream_t st = (cudaStream_t)stream;
+  if (vec_ok(dd, dst) && vec_ok(sd, src)) {
+    vec_copy_kernel<<<grid_for(total >> 3, 256), 256, 0, st>>>(view(dd), (__nv_bfloat16*)dst, view(sd), (const __nv_bfloat16*)src, accumulate != 0);
+    RG_LAUNCH_CHECK("rg_copy5(vec)");
+    return RG_OK;
+  }
   int grid = grid_for(total, 256);
   RG_DISPATCH_FLOAT(sd->dtype, TS, RG_DISPATCH_FLOAT(dd->dtype, TD, {
     copy5_kernel<TS, TD><<<grid, 256, 0, st>>>(view(dd), (TD*)dst, view(sd), (const TS*)src, ci, accumulate != 0);
@@ -174,6 +291,11 @@ int rg_pad3d_fwd(const rg_tensor5* xd, const void* x, const rg_tensor5* yd, void
   long long total = view(yd).numel();
   if (total == 0) return RG_OK;
   cudaStream_t st = (cudaStream_t)stream;
+  if (vec_ok(xd, x) && vec_ok(yd, y)) {
+    vec_pad_fwd_kernel<<<grid_for(total >> 3, 256), 256, 0, st>>>(view(xd), (const __nv_bfloat16*)x, view(yd), (__nv_bfloat16*)y, lo[0], lo[1], lo[2], mode);
+    RG_LAUNCH_CHECK("rg_pad3d_fwd(vec)");
+    return RG_OK;
+  }
   int grid = grid_for(total, 256);
   bool ci = channels_inner(yd);
   RG_DISPATCH_FLOAT(xd->dtype, TS, RG_DISPATCH_FLOAT(yd->dtype, TD, {
@@ -191,6 +313,11 @@ int rg_pad3d_bwd(const rg_tensor5* dyd, const void* dy, const rg_tensor5* dxd, v
   long long total = view(dxd).numel();
   if (total == 0) return RG_OK;
   cudaStream_t st = (cudaStream_t)stream;
+  if (vec_ok(dyd, dy) && vec_ok(dxd, dx)) {
+    vec_pad_bwd_kernel<<<grid_for(total >> 3, 256), 256, 0, st>>>(view(dyd), (const __nv_bfloat16*)dy, view(dxd), (__nv_bfloat16*)dx, lo[0], lo[1], lo[2], mode);
+    RG_LAUNCH_CHECK("rg_pad3d_bwd(vec)");
+    return RG_OK;
+  }
   int grid = grid_for(total, 128);
   bool ci = channels_inner(dxd);
   RG_DISPATCH_FLOAT(dyd->dtype, TS, RG_DISPATCH_FLOAT(dxd->dtype, TD, {
@@ -207,6 +334,11 @@ int rg_act_fwd(const rg_tensor5* xd, const void* x, int act, float slope, const 
   long long total = view(yd).numel();
   if (total == 0) return RG_OK;
   cudaStream_t st = (cudaStream_t)stream;
+  if (vec_ok(xd, x) && vec_ok(yd, y)) {
+    vec_act_fwd_kernel<<<grid_for(total >> 3, 256), 256, 0, st>>>(view(xd), (const __nv_bfloat16*)x, view(yd), (__nv_bfloat16*)y, act, slope);
+    RG_LAUNCH_CHECK("rg_act_fwd(vec)");
+    return RG_OK;
+  }
   int grid = grid_for(total, 256);
   bool ci = channels_inner(yd);
   RG_DISPATCH_FLOAT(xd->dtype, TS, RG_DISPATCH_FLOAT(yd->dtype, TD, {
@@ -224,6 +356,11 @@ int rg_act_bwd(const rg_tensor5* yd, const void* y, const rg_tensor5* dyd, const
   long long total = view(dxd).numel();
   if (total == 0) return RG_OK;
   cudaStream_t st = (cudaStream_t)stream;
+  if (vec_ok(yd, y) && vec_ok(dyd, dy) && vec_ok(dxd, dx)) {
+    vec_act_bwd_kernel<<<grid_for(total >> 3, 256), 256, 0, st>>>(view(yd), (const __nv_bfloat16*)y, view(dyd), (const __nv_bfloat16*)dy, view(dxd), (__nv_bfloat16*)dx, act, slope);
+    RG_LAUNCH_CHECK("rg_act_bwd(vec)");
+    return RG_OK;
+  }
   int grid = grid_for(total, 256);
   bool ci = channels_inner(dxd);
   RG_DISPATCH_FLOAT(yd->dtype, TS, RG_DISPATCH_FLOAT(dxd->dtype, TD, {

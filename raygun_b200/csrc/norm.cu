@@ -1,6 +1,7 @@
 // InstanceNorm3d / BatchNorm3d: statistics, apply (fused activation + residual), backward.
 // HBM-bound: stats 1 read; apply 1 read + 1 write; backward = 1 reduction pass (x, dy, y) + 1 pass.
 #include "common.cuh"
+#include "vec_ndhwc.cuh"
 
 namespace rg {
 
@@ -96,6 +97,145 @@ __global__ void reduce2_c_inner(NormCtx cx, T5 xd, const TX* __restrict__ x, T5 
   }
 }
 
+// ------------------------------------------------------------------------------------------
+// vectorised NDHWC bf16 fast paths (8 channels / thread)
+// ------------------------------------------------------------------------------------------
+__global__ void vec_norm_apply_kernel(NormCtx cx, const float* __restrict__ beta, T5 xd, const __nv_bfloat16* __restrict__ x,
+                                      T5 rd, const __nv_bfloat16* __restrict__ res, T5 yd, __nv_bfloat16* __restrict__ y) {
+  const long long total = yd.numel() >> 3;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    VIdx p = vunravel(i, yd);
+    float v[8];
+    ld8(x + voff(xd, p.n, p.d, p.h, p.w, p.c), v);
+    if (cx.mean) {
+      const int g0 = group_of(cx.kind, p.n, p.c, xd.c);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) v[k] = (v[k] - __ldg(cx.mean + g0 + k)) * __ldg(cx.rstd + g0 + k);
+    }
+    if (cx.gamma) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) v[k] *= __ldg(cx.gamma + p.c + k);
+    }
+    if (beta) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) v[k] += __ldg(beta + p.c + k);
+    }
+    if (res) {
+      float r[8];
+      ld8(res + voff(rd, p.n, p.d, p.h, p.w, p.c), r);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) v[k] += r[k];
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) v[k] = act_apply(v[k], cx.act, cx.slope);
+    st8(y + voff(yd, p.n, p.d, p.h, p.w, p.c), v);
+  }
+}
+
+__global__ void vec_norm_bwd_dx_kernel(NormCtx cx, int training, const float* __restrict__ red, float inv_count, T5 xd,
+                                       const __nv_bfloat16* __restrict__ x, T5 gd, const __nv_bfloat16* __restrict__ dy,
+                                       T5 yd, const __nv_bfloat16* __restrict__ y, T5 dxd, __nv_bfloat16* __restrict__ dx,
+                                       int groups) {
+  const long long total = dxd.numel() >> 3;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    VIdx p = vunravel(i, dxd);
+    const int g0 = group_of(cx.kind, p.n, p.c, xd.c);
+    float g[8], out[8];
+    ld8(dy + voff(gd, p.n, p.d, p.h, p.w, p.c), g);
+    if (cx.act != RG_ACT_NONE) {
+      float yy[8];
+      ld8(y + voff(yd, p.n, p.d, p.h, p.w, p.c), yy);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) g[k] *= act_grad_from_y(yy[k], cx.act, cx.slope);
+    }
+    if (training) {
+      float xv[8];
+      ld8(x + voff(xd, p.n, p.d, p.h, p.w, p.c), xv);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const float r = __ldg(cx.rstd + g0 + k);
+        const float gam = cx.gamma ? __ldg(cx.gamma + p.c + k) : 1.f;
+        const float xhat = (xv[k] - __ldg(cx.mean + g0 + k)) * r;
+        out[k] = gam * r * (g[k] - __ldg(red + g0 + k) * inv_count - xhat * __ldg(red + groups + g0 + k) * inv_count);
+      }
+    } else {
+#pragma unroll
+      for (int k = 0; k < 8; ++k)
+        out[k] = (cx.gamma ? __ldg(cx.gamma + p.c + k) : 1.f) * __ldg(cx.rstd + g0 + k) * g[k];
+    }
+    st8(dx + voff(dxd, p.n, p.d, p.h, p.w, p.c), out);
+  }
+}
+
+// blockIdx.y = n, blockIdx.x = voxel chunk.  Thread = (channel group of 8, voxel lane); the block walks
+// its voxel range with 16-byte loads, reduces across voxel lanes in smem, one atomic per (block, channel).
+template <int MODE>
+__global__ void __launch_bounds__(256) vec_reduce2_kernel(NormCtx cx, T5 xd, const __nv_bfloat16* __restrict__ x, T5 gd,
+                                                          const __nv_bfloat16* __restrict__ dy, T5 yd,
+                                                          const __nv_bfloat16* __restrict__ y, float* __restrict__ out0,
+                                                          float* __restrict__ out1, long long vox_per_block) {
+  const long long n = blockIdx.y;
+  const long long vox = xd.d * xd.h * xd.w;
+  const long long v0 = blockIdx.x * vox_per_block;
+  const long long v1 = v0 + vox_per_block < vox ? v0 + vox_per_block : vox;
+  const int cgroups = (int)(xd.c >> 3);
+  __shared__ float red0[256], red1[256];
+  // process channel groups in tiles of up to 32 groups (256 channels) so that 256 threads = 32 cg x 8 voxel lanes
+  for (int cg0 = 0; cg0 < cgroups; cg0 += 32) {
+    const int ncg = min(32, cgroups - cg0);
+    const int lanes_v = 256 / ncg;                 // voxel lanes (>= 8)
+    const int cgi = threadIdx.x % ncg, lv = threadIdx.x / ncg;
+    float s0[8], s1[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) { s0[k] = 0.f; s1[k] = 0.f; }
+    if (lv < lanes_v) {
+      const int c = (cg0 + cgi) << 3;
+      const int g0 = group_of(cx.kind, n, c, xd.c);
+      for (long long i = v0 + lv; i < v1; i += lanes_v) {
+        const long long w = i % xd.w, t = i / xd.w;
+        const long long h = t % xd.h, d = t / xd.h;
+        float xv[8];
+        ld8(x + voff(xd, n, d, h, w, c), xv);
+        if (MODE == 0) {
+#pragma unroll
+          for (int k = 0; k < 8; ++k) { s0[k] += xv[k]; s1[k] += xv[k] * xv[k]; }
+        } else {
+          float g[8];
+          ld8(dy + voff(gd, n, d, h, w, c), g);
+          if (cx.act != RG_ACT_NONE) {
+            float yy[8];
+            ld8(y + voff(yd, n, d, h, w, c), yy);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) g[k] *= act_grad_from_y(yy[k], cx.act, cx.slope);
+          }
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            const float xhat = (xv[k] - __ldg(cx.mean + g0 + k)) * __ldg(cx.rstd + g0 + k);
+            s0[k] += g[k]; s1[k] += g[k] * xhat;
+          }
+        }
+      }
+    }
+    // reduce over voxel lanes: lanes with the same cgi are threadIdx.x = cgi + ncg*lv
+    // 8 rounds (one per channel of the group) through a 256-entry staging array
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      red0[threadIdx.x] = s0[k];
+      red1[threadIdx.x] = s1[k];
+      __syncthreads();
+      if (threadIdx.x < ncg) {
+        float a = 0.f, b = 0.f;
+        for (int l = 0; l < lanes_v; ++l) { a += red0[threadIdx.x + ncg * l]; b += red1[threadIdx.x + ncg * l]; }
+        const int c = ((cg0 + threadIdx.x) << 3) + k;
+        const int grp = group_of(cx.kind, n, c, xd.c);
+        atomicAdd(out0 + grp, a);
+        atomicAdd(out1 + grp, b);
+      }
+      __syncthreads();
+    }
+  }
+}
+
 __global__ void finalize_kernel(const float* __restrict__ sum, const float* __restrict__ sq, int groups, double count,
                                 float eps, float* __restrict__ mean, float* __restrict__ rstd, float* __restrict__ var_out) {
   int g = blockIdx.x * blockDim.x + threadIdx.x;
@@ -171,6 +311,16 @@ static int launch_reduce2(const NormCtx& cx, const rg_tensor5* xd, const TX* x, 
                           const rg_tensor5* yd, const TG* y, float* out0, float* out1, cudaStream_t st) {
   T5 xv = view(xd), gv = gd ? view(gd) : xv, yv = yd ? view(yd) : xv;
   long long vox = xv.d * xv.h * xv.w;
+  if (vec_ok(xd, x) && (MODE == 0 || (vec_ok(gd, dy) && (cx.act == RG_ACT_NONE || vec_ok(yd, y))))) {
+    long long blocks_x = (148LL * 4 + xv.n - 1) / xv.n;
+    long long vpb = (vox + blocks_x - 1) / blocks_x;
+    if (vpb < 256) vpb = 256;
+    blocks_x = (vox + vpb - 1) / vpb;
+    dim3 grid((unsigned)blocks_x, (unsigned)xv.n);
+    vec_reduce2_kernel<MODE><<<grid, 256, 0, st>>>(cx, xv, (const __nv_bfloat16*)x, gv, (const __nv_bfloat16*)dy, yv,
+                                                   (const __nv_bfloat16*)y, out0, out1, vpb);
+    return RG_OK;
+  }
   if (channels_inner(xd)) {
     long long blocks_x = (148LL * 8 + xv.n - 1) / xv.n;
     long long vpb = (vox + blocks_x - 1) / blocks_x;
@@ -235,6 +385,12 @@ int rg_norm_apply(const rg_tensor5* xd, const void* x, int kind, const float* me
   bool ci = channels_inner(yd);
   int rdt = residual ? rd->dtype : xd->dtype;
   T5 rv = residual ? view(rd) : view(xd);
+  if (vec_ok(xd, x) && vec_ok(yd, y) && (!residual || vec_ok(rd, residual))) {
+    vec_norm_apply_kernel<<<grid_for(total >> 3, 256), 256, 0, st>>>(cx, beta, view(xd), (const __nv_bfloat16*)x, rv,
+                                                                     (const __nv_bfloat16*)residual, view(yd), (__nv_bfloat16*)y);
+    RG_LAUNCH_CHECK("rg_norm_apply(vec)");
+    return RG_OK;
+  }
   RG_DISPATCH_FLOAT(xd->dtype, TX, RG_DISPATCH_FLOAT(rdt, TR, RG_DISPATCH_FLOAT(yd->dtype, TY, {
     norm_apply_kernel<TX, TR, TY><<<grid, 256, 0, st>>>(cx, beta, view(xd), (const TX*)x, rv, (const TR*)residual, view(yd), (TY*)y, ci);
   })))
@@ -274,6 +430,13 @@ int rg_norm_bwd(const rg_tensor5* xd, const void* x, const rg_tensor5* dyd, cons
     int grid = grid_for(total, 256);
     bool ci = channels_inner(dxd);
     T5 yv = (yd && y) ? view(yd) : xv;
+    if (vec_ok(xd, x) && vec_ok(dyd, dy) && vec_ok(dxd, dx) && (act == RG_ACT_NONE || vec_ok(yd, y))) {
+      vec_norm_bwd_dx_kernel<<<grid_for(total >> 3, 256), 256, 0, st>>>(
+          cx, training, red, (float)(1.0 / count), xv, (const __nv_bfloat16*)x, view(dyd), (const __nv_bfloat16*)dy, yv,
+          (const __nv_bfloat16*)y, view(dxd), (__nv_bfloat16*)dx, groups);
+      RG_LAUNCH_CHECK("rg_norm_bwd dx(vec)");
+      return RG_OK;
+    }
     RG_DISPATCH_FLOAT(xd->dtype, TX, RG_DISPATCH_FLOAT(dyd->dtype, TG, RG_DISPATCH_FLOAT(dxd->dtype, TD, {
       norm_bwd_dx_kernel<TX, TG, TD><<<grid, 256, 0, st>>>(cx, training, red, (float)(1.0 / count), xv, (const TX*)x, view(dyd), (const TG*)dy, yv, (const TG*)y, view(dxd), (TD*)dx, groups, ci);
     })))

@@ -233,3 +233,76 @@ def test_adam_matches_oracle_restatement():
         st.step({"p": g})
         K.adam_step(pg, g.to(_dev()), m, v, 1e-3, 0.9, 0.999, 1e-8, step)
     _close(pg, ref["p"], 1e-6, "adam")
+
+
+# ---- vectorised bf16 NDHWC fast paths (8 channels / thread) vs the oracle on bf16-rounded operands ----
+def _bf(t):
+    return t.bfloat16().float()
+
+
+def _ndhwc(t):
+    return t.to(_dev()).bfloat16().contiguous(memory_format=torch.channels_last_3d)
+
+
+@pytest.mark.parametrize("mode", ["reflect", "replicate", "zeros"])
+@pytest.mark.parametrize("lo,hi", [((1, 1, 1), (1, 1, 1)), ((3, 3, 3), (3, 3, 3)), ((0, 2, 1), (2, 0, 1))])
+def test_vec_pad_and_adjoint_bf16_ndhwc(mode, lo, hi):
+    from raygun_b200 import functional as F
+    torch.manual_seed(21)
+    x = _bf(torch.randn(2, 16, 5, 6, 7)).requires_grad_(True)
+    pads = (lo[2], hi[2], lo[1], hi[1], lo[0], hi[0])
+    y_ref = TF.pad(x, pads, mode={"zeros": "constant"}.get(mode, mode))
+    r = _bf(torch.randn_like(y_ref))
+    (gx,) = torch.autograd.grad((y_ref * r).sum(), [x])
+    xg = _ndhwc(x.detach()).requires_grad_(True)
+    y = F.pad3d(xg, lo, hi, mode)
+    y.backward(_ndhwc(r))
+    assert y.dtype == torch.bfloat16
+    _close(y, y_ref, 0.0, "vec pad")
+    _close(xg.grad, gx, 1e-2, "vec pad adjoint")
+
+
+@pytest.mark.parametrize("kind", ["instance", "batch"])
+@pytest.mark.parametrize("c", [16, 192, 320])
+def test_vec_norm_act_bf16_ndhwc(kind, c):
+    from raygun_b200 import nn as L
+    torch.manual_seed(22)
+    x = _bf(torch.randn(2, c, 5, 6, 7) * 2 + 0.5).requires_grad_(True)
+    res = _bf(torch.randn(2, c, 5, 6, 7)).requires_grad_(True)
+    ref_norm = torch.nn.InstanceNorm3d(c) if kind == "instance" else torch.nn.BatchNorm3d(c)
+    y_ref = TF.leaky_relu(ref_norm(x) + res, 0.2)
+    r = _bf(torch.randn_like(y_ref))
+    gx, gr = torch.autograd.grad((y_ref * r).sum(), [x, res])
+    ours = (L.InstanceNorm3d(c) if kind == "instance" else L.BatchNorm3d(c)).to(_dev())
+    xg, rg = _ndhwc(x.detach()).requires_grad_(True), _ndhwc(res.detach()).requires_grad_(True)
+    y = ours.fused(xg, None, 2, 0.2, residual=rg)
+    y.backward(_ndhwc(r))
+    _close(y, y_ref, 1e-2, "vec norm y")
+    _close(xg.grad, gx, 2e-2, "vec norm dx")
+    _close(rg.grad, gr, 1e-2, "vec norm dres")
+
+
+def test_vec_act_copy_cropcat_bf16_ndhwc():
+    from oracle.restate import center_crop
+    from raygun_b200 import functional as F
+    torch.manual_seed(23)
+    x = _bf(torch.randn(2, 24, 6, 5, 7)).requires_grad_(True)
+    y_ref = torch.tanh(x)
+    r = _bf(torch.randn_like(y_ref))
+    (gx,) = torch.autograd.grad((y_ref * r).sum(), [x])
+    xg = _ndhwc(x.detach()).requires_grad_(True)
+    y = F.activation(xg, 3)
+    y.backward(_ndhwc(r))
+    _close(y, y_ref, 1e-2, "vec act")
+    _close(xg.grad, gx, 1e-2, "vec act bwd")
+    a = _bf(torch.randn(2, 16, 9, 10, 8)).requires_grad_(True)
+    b = _bf(torch.randn(2, 8, 7, 6, 6)).requires_grad_(True)
+    y_ref = torch.cat([center_crop(a, (5, 6, 4)), center_crop(b, (5, 6, 4))], 1)
+    r = _bf(torch.randn_like(y_ref))
+    ga, gb = torch.autograd.grad((y_ref * r).sum(), [a, b])
+    ag, bg = _ndhwc(a.detach()).requires_grad_(True), _ndhwc(b.detach()).requires_grad_(True)
+    y = F.crop_cat(ag, bg, (5, 6, 4))
+    y.backward(_ndhwc(r))
+    _close(y, y_ref, 0.0, "vec cropcat")
+    _close(ag.grad, ga, 0.0, "vec cropcat da")
+    _close(bg.grad, gb, 0.0, "vec cropcat db")
