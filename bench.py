@@ -16,6 +16,7 @@ public API from pinned HOST uint8 buffers (H2D + u8 normalise + step + D2H of th
 from __future__ import annotations
 
 import argparse
+import contextlib
 import json
 import os
 import subprocess
@@ -129,7 +130,8 @@ def cpu_step_fn(n_blocks, ngf, side, batch=1):
     torch.manual_seed(42)
     g = torch.nn.Sequential(N.ResNet(3, input_nc=1, ngf=ngf, n_blocks=n_blocks, padding_type="same"),
                             torch.nn.Conv3d(ngf, 1, 1), torch.nn.Tanh())
-    N.init_weights(g, "kaiming")
+    with contextlib.redirect_stdout(sys.stderr):      # init_weights prints, as the reference's does
+        N.init_weights(g, "kaiming")
     sd = {k: v.detach().clone().requires_grad_(v.is_floating_point()) for k, v in g.state_dict().items()}
     spec = O.resnet_spec(input_nc=1, ngf=ngf, n_blocks=n_blocks, padding_type="same",
                          norm=dict(kind="instance", affine=False))
@@ -141,7 +143,7 @@ def cpu_step_fn(n_blocks, ngf, side, batch=1):
         y = O.generator_forward(sd, "resnet", spec, x, final_activation="Tanh")
         loss = O.smooth_l1(tgt, y)
         torch.autograd.grad(loss, leaves, allow_unused=True)
-        return float(loss)
+        return float(loss.detach())
 
     return step, batch * side ** 3
 
@@ -198,8 +200,9 @@ def run_ours(args):
     batch, side, n_blocks, ngf = WORKLOADS[args.workload]
 
     torch.manual_seed(42)
-    g = make_generator("resnet", dict(input_nc=1, output_nc=1, ngf=ngf, n_blocks=n_blocks, padding_type="same",
-                                      final_activation="Tanh")).to(dev)
+    with contextlib.redirect_stdout(sys.stderr):
+        g = make_generator("resnet", dict(input_nc=1, output_nc=1, ngf=ngf, n_blocks=n_blocks, padding_type="same",
+                                          final_activation="Tanh")).to(dev)
     params = [p for p in g.parameters()]
     host_x = synth_batch(batch, side, 42 + 10 * rank).pin_memory()
     host_t = synth_batch(batch, side, 43 + 10 * rank).pin_memory()
@@ -222,7 +225,7 @@ def run_ours(args):
         xu = host_x.to(dev, non_blocking=True)
         tu = host_t.to(dev, non_blocking=True)
         loss = step(K.u8_normalise(xu, dtype=torch.float32), K.u8_normalise(tu, dtype=torch.float32))
-        return float(loss)     # D2H of the step's result
+        return float(loss.detach())     # D2H of the step's result
 
     def barrier():
         if world > 1:

@@ -109,12 +109,28 @@ int rg_igemm_run(const rg_plan* plan, const void* in, const void* w_packed, cons
 int rg_igemm_wgrad(const rg_plan* plan, const void* x, const void* dy, float* dw, float* dbias,
                    void* workspace, void* stream);
 
+/* ---- 1x1x1 convolutions onto <= 4 channels (BaseSystem.py:209-224: Conv3d(ngf, output_nc, 1) + Tanh) -------
+ * HBM-bound streaming kernels over a bf16 NDHWC x (Cin/8 a power of two <= 32); w fp32 [Cout][Cin].
+ * fprop fuses bias + activation; wgrad accumulates into dw / dbias (caller zeroes).                     */
+int rg_pw_conv_fprop(const rg_tensor5* xd, const void* x, const float* w, const float* bias, int act, float slope,
+                     const rg_tensor5* yd, void* y, void* stream);
+int rg_pw_conv_dgrad(const rg_tensor5* dyd, const void* dy, const float* w, const rg_tensor5* dxd, void* dx, void* stream);
+int rg_pw_conv_wgrad(const rg_tensor5* xd, const void* x, const rg_tensor5* dyd, const void* dy, float* dw, float* dbias,
+                     void* stream);
+
 /* ---- data movement: strided copy / cast / crop / concat-slice ------------------------
  * Replaces the reference's center `crop` + torch.cat (UNet.py:327-351), ResNet crop
  * (ResNet.py:436-443), dtype/layout casts and .float() (predict/worker.py:101-107).
  * dst[i] (+)= src[i] over the logical shape of dst (src must have the same shape).  */
 int rg_copy5(const rg_tensor5* dd, void* dst, const rg_tensor5* sd, const void* src, int accumulate,
              void* stream);
+
+/* Small-Cin stems (ResNet.py:283 Conv3d(input_nc=1, ngf, 7); UNet.py:61-69 first ConvPass conv):
+ * y[n][(ci*KH+kh)*KW+kw][d][h][w] = x[n][ci][d][h+kh-ph][w+kw-pw] (0 outside), channels zero-filled up to
+ * yd->c.  Folding the H/W taps into >= 64 channels turns the layer into a (KD,1,1) convolution that the
+ * tcgen05 implicit-GEMM kernels run at tensor-core speed.  y must be bf16.                                */
+int rg_im2col_hw(const rg_tensor5* xd, const void* x, int kh, int kw, int ph, int pw, const rg_tensor5* yd, void* y,
+                 void* stream);
 
 /* ---- padding (nn.ReflectionPad3d / ReplicationPad3d / F.pad; ResNet.py:270-279,392-401,
  *      UNet.py:61-69 padding_mode="reflect") and its adjoint ----------------------------*/

@@ -132,6 +132,13 @@ def _sp_strides(t):
     return (s[0], s[2], s[3], s[4])
 
 
+def _pw_ok(cin, cout, kernel, stride, pad, groups):
+    cg = cin // 8
+    return (K.get_precision() == "bf16" and K.use_tensor_cores() and groups == 1 and tuple(kernel) == (1, 1, 1)
+            and tuple(stride) == (1, 1, 1) and tuple(pad) == (0, 0, 0) and 1 <= cout <= 4 and cin % 8 == 0
+            and 1 <= cg <= 32 and (cg & (cg - 1)) == 0)
+
+
 def _igemm_ok(cin, cout, kernel, stride, groups):
     return (K.get_precision() == "bf16" and K.use_tensor_cores() and groups == 1 and cin % 64 == 0
             and cout % 64 == 0 and all(s in (1, 2) for s in stride) and all(1 <= k <= 8 for k in kernel))
@@ -167,6 +174,14 @@ def conv_fprop(x, w, bias, stride, pad, groups=1, act=ACT_NONE, slope=0.0, want_
             count_launch()
             stats["igemm"] += 1
             return (y, st[0], st[1]) if want_stats else (y, None, None)
+    if _pw_ok(cin_t, cout, kernel, stride, pad, groups):
+        xb = K.convert(x, torch.bfloat16)
+        y = K.empty5((n, cout, *od), cdt, x.device)
+        check(lib().rg_pw_conv_fprop(C.byref(t5(xb)), ptr(xb), ptr(w.detach().contiguous()), ptr(bias_f), C.c_int(act),
+                                     C.c_float(slope), C.byref(t5(y)), ptr(y), stream_ptr(x.device)), "rg_pw_conv_fprop")
+        count_launch()
+        stats["pointwise"] = stats.get("pointwise", 0) + 1
+        return y, None, None
     y = K.empty5((n, cout, *od), cdt, x.device)
     g = _geom(kernel, stride, pad, groups, act, slope)
     wc = w.detach()
@@ -204,6 +219,14 @@ def conv_dgrad(dy, w, x_shape, stride, pad, groups=1, bias=None, act=ACT_NONE, s
             count_launch(stride[0] * stride[1] * stride[2])
             stats["igemm"] += 1
             return (dx, st[0], st[1]) if want_stats else (dx, None, None)
+    if (_pw_ok(cin_t, cout_t, kernel, stride, pad, groups) and bias is None and act == ACT_NONE
+            and cdt == torch.bfloat16):
+        dx = K.empty5(tuple(x_shape), torch.bfloat16, dy.device)
+        check(lib().rg_pw_conv_dgrad(C.byref(t5(dy)), ptr(dy), ptr(w.detach().contiguous()), C.byref(t5(dx)), ptr(dx),
+                                     stream_ptr(dy.device)), "rg_pw_conv_dgrad")
+        count_launch()
+        stats["pointwise"] = stats.get("pointwise", 0) + 1
+        return dx, None, None
     dx = K.empty5(tuple(x_shape), cdt, dy.device)
     g = _geom(kernel, stride, pad, groups, act, slope)
     wc = w.detach()
@@ -235,6 +258,15 @@ def conv_wgrad(x, dy, w_shape, stride, pad, groups=1, want_bias=False):
             stats["igemm"] += 1
             db = K.norm_stats(dyb, _C.NORM_BATCH)[0] if want_bias else None
             return dw, db
+    if _pw_ok(cin_g, cout, kernel, stride, pad, groups):
+        xb = K.convert(x, torch.bfloat16)
+        dw = torch.zeros(tuple(w_shape), dtype=torch.float32, device=x.device)
+        db = torch.zeros(cout, dtype=torch.float32, device=x.device) if want_bias else None
+        check(lib().rg_pw_conv_wgrad(C.byref(t5(xb)), ptr(xb), C.byref(t5(dy)), ptr(dy), ptr(dw), ptr(db),
+                                     stream_ptr(x.device)), "rg_pw_conv_wgrad")
+        count_launch()
+        stats["pointwise"] = stats.get("pointwise", 0) + 1
+        return dw, db
     dw = torch.empty(tuple(w_shape), dtype=torch.float32, device=x.device)
     db = torch.empty(w_shape[0], dtype=torch.float32, device=x.device) if want_bias else None
     g = _geom(tuple(w_shape[2:]), stride, pad, groups)

@@ -250,6 +250,30 @@ __global__ void vec_act_bwd_kernel(T5 yd, const __nv_bfloat16* __restrict__ y, T
   }
 }
 
+
+template <typename TS>
+__global__ void im2col_hw_kernel(T5 xd, const TS* __restrict__ x, int kh, int kw, int ph, int pw, T5 yd,
+                                 __nv_bfloat16* __restrict__ y) {
+  const long long total = yd.numel() >> 3;
+  const int cvalid = (int)xd.c * kh * kw;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    VIdx p = vunravel(i, yd);
+    float v[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const int c = p.c + k;
+      float val = 0.f;
+      if (c < cvalid) {
+        const int kw_ = c % kw; int t = c / kw; const int kh_ = t % kh; const int ci = t / kh;
+        const long long ih = p.h + kh_ - ph, iw = p.w + kw_ - pw;
+        if (ih >= 0 && ih < xd.h && iw >= 0 && iw < xd.w) val = ldf(x + xd.off(p.n, ci, p.d, ih, iw));
+      }
+      v[k] = val;
+    }
+    st8(y + voff(yd, p.n, p.d, p.h, p.w, p.c), v);
+  }
+}
+
 }  // namespace rg
 
 using namespace rg;
@@ -367,6 +391,23 @@ int rg_act_bwd(const rg_tensor5* yd, const void* y, const rg_tensor5* dyd, const
     act_bwd_kernel<TS, TS, TD><<<grid, 256, 0, st>>>(view(yd), (const TS*)y, view(dyd), (const TS*)dy, view(dxd), (TD*)dx, act, slope, ci);
   }))
   RG_LAUNCH_CHECK("rg_act_bwd");
+  return RG_OK;
+}
+
+int rg_im2col_hw(const rg_tensor5* xd, const void* x, int kh, int kw, int ph, int pw, const rg_tensor5* yd, void* y,
+                 void* stream) {
+  RG_CHECK_ARG(xd && x && yd && y && kh >= 1 && kw >= 1 && ph >= 0 && pw >= 0, "rg_im2col_hw: bad argument");
+  RG_CHECK_ARG(vec_ok(yd, y), "rg_im2col_hw: output must be bf16 NDHWC with C %% 8 == 0");
+  RG_CHECK_ARG(yd->c >= xd->c * kh * kw, "rg_im2col_hw: output has too few channels");
+  RG_CHECK_ARG(yd->n == xd->n && yd->d == xd->d && yd->h == xd->h + 2 * ph - kh + 1 && yd->w == xd->w + 2 * pw - kw + 1,
+               "rg_im2col_hw: shape mismatch");
+  long long total = view(yd).numel() >> 3;
+  if (total == 0) return RG_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  RG_DISPATCH_FLOAT(xd->dtype, TS, {
+    im2col_hw_kernel<TS><<<grid_for(total, 256), 256, 0, st>>>(view(xd), (const TS*)x, kh, kw, ph, pw, view(yd), (__nv_bfloat16*)y);
+  })
+  RG_LAUNCH_CHECK("rg_im2col_hw");
   return RG_OK;
 }
 

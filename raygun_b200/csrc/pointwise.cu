@@ -1,0 +1,180 @@
+// 1x1x1 convolutions onto a handful of output channels (the generator's final Conv3d(ngf, output_nc, 1)
+// of systems/BaseSystem.py:209-224, with its Tanh fused): pure HBM-bound streaming over a bf16 NDHWC
+// tensor, 8 channels (16 bytes) per thread.  fprop = per-voxel dot products reduced with warp shuffles;
+// dgrad = rank-Cout outer product; wgrad = reduction over all voxels (block partials + fp32 atomics).
+#include "common.cuh"
+#include "vec_ndhwc.cuh"
+
+namespace rg {
+
+constexpr int PW_MAX_COUT = 4;
+
+struct PwW { const float* w; const float* bias; int cin, cout; };
+
+// threads t*cg .. t*cg+cg-1 (cg = Cin/8, a power of two <= 32) share one voxel
+template <typename TY>
+__global__ void pw_fprop_kernel(PwW pw, T5 xd, const __nv_bfloat16* __restrict__ x, T5 yd, TY* __restrict__ y, int act,
+                                float slope) {
+  const int cg = pw.cin >> 3;
+  const long long vox_total = xd.n * xd.d * xd.h * xd.w;
+  const long long total = vox_total * cg;
+  const long long stride = (long long)gridDim.x * blockDim.x;     // multiple of 32 -> multiple of cg
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; (i & ~31LL) < total; i += stride) {   // warp-uniform trip count
+    const bool live = i < total;
+    float acc[PW_MAX_COUT] = {0.f, 0.f, 0.f, 0.f};
+    VIdx p;
+    if (live) {
+      p = vunravel(i, xd);
+      float v[8];
+      ld8(x + voff(xd, p.n, p.d, p.h, p.w, p.c), v);
+      for (int co = 0; co < pw.cout; ++co) {
+        float a = 0.f;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) a = fmaf(v[k], __ldg(pw.w + co * pw.cin + p.c + k), a);
+        acc[co] = a;
+      }
+    }
+    for (int o = cg >> 1; o > 0; o >>= 1)
+      for (int co = 0; co < pw.cout; ++co) acc[co] += __shfl_xor_sync(0xffffffffu, acc[co], o);
+    if (live && p.c == 0) {
+      for (int co = 0; co < pw.cout; ++co) {
+        float v = acc[co] + (pw.bias ? __ldg(pw.bias + co) : 0.f);
+        stf(y + yd.off(p.n, co, p.d, p.h, p.w), act_apply(v, act, slope));
+      }
+    }
+  }
+}
+
+template <typename TG>
+__global__ void pw_dgrad_kernel(PwW pw, T5 gd, const TG* __restrict__ dy, T5 dxd, __nv_bfloat16* __restrict__ dx) {
+  const long long total = dxd.numel() >> 3;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    VIdx p = vunravel(i, dxd);
+    float out[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int co = 0; co < pw.cout; ++co) {
+      const float g = ldf(dy + gd.off(p.n, co, p.d, p.h, p.w));
+#pragma unroll
+      for (int k = 0; k < 8; ++k) out[k] = fmaf(g, __ldg(pw.w + co * pw.cin + p.c + k), out[k]);
+    }
+    st8(dx + voff(dxd, p.n, p.d, p.h, p.w, p.c), out);
+  }
+}
+
+// dw[co][c] += sum_vox dy[vox][co] * x[vox][c];  dbias[co] += sum_vox dy[vox][co]
+template <typename TG>
+__global__ void __launch_bounds__(256) pw_wgrad_kernel(int cin, int cout, T5 xd, const __nv_bfloat16* __restrict__ x, T5 gd,
+                                                       const TG* __restrict__ dy, float* __restrict__ dw,
+                                                       float* __restrict__ dbias, long long vox_per_block) {
+  const int cg = cin >> 3;                       // <= 32
+  const int lanes_v = 256 / cg;
+  const int cgi = threadIdx.x % cg, lv = threadIdx.x / cg;
+  const long long vox_total = xd.n * xd.d * xd.h * xd.w;
+  const long long v0 = blockIdx.x * vox_per_block;
+  const long long v1 = v0 + vox_per_block < vox_total ? v0 + vox_per_block : vox_total;
+  float acc[PW_MAX_COUT][8];
+  float bsum[PW_MAX_COUT];
+#pragma unroll
+  for (int co = 0; co < PW_MAX_COUT; ++co) {
+    bsum[co] = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) acc[co][k] = 0.f;
+  }
+  if (lv < lanes_v) {
+    for (long long i = v0 + lv; i < v1; i += lanes_v) {
+      long long t = i;
+      const long long w = t % xd.w; t /= xd.w;
+      const long long h = t % xd.h; t /= xd.h;
+      const long long d = t % xd.d; const long long n = t / xd.d;
+      float v[8];
+      ld8(x + voff(xd, n, d, h, w, cgi << 3), v);
+#pragma unroll
+      for (int co = 0; co < PW_MAX_COUT; ++co) {
+        if (co < cout) {
+          const float g = ldf(dy + gd.off(n, co, d, h, w));
+          bsum[co] += g;
+#pragma unroll
+          for (int k = 0; k < 8; ++k) acc[co][k] = fmaf(g, v[k], acc[co][k]);
+        }
+      }
+    }
+  }
+  __shared__ float red[256];
+  for (int co = 0; co < cout; ++co) {
+#pragma unroll
+    for (int k = 0; k <= 8; ++k) {          // k == 8: the bias partial
+      red[threadIdx.x] = (lv < lanes_v) ? (k < 8 ? acc[co][k] : bsum[co]) : 0.f;
+      __syncthreads();
+      if (threadIdx.x < cg) {
+        float a = 0.f;
+        for (int l = 0; l < lanes_v; ++l) a += red[threadIdx.x + cg * l];
+        if (k < 8) atomicAdd(dw + co * cin + (threadIdx.x << 3) + k, a);
+        else if (threadIdx.x == 0 && dbias) atomicAdd(dbias + co, a);
+      }
+      __syncthreads();
+    }
+  }
+}
+
+static bool pw_shape_ok(int cin, int cout) {
+  const int cg = cin >> 3;
+  return cin % 8 == 0 && cg >= 1 && cg <= 32 && (cg & (cg - 1)) == 0 && cout >= 1 && cout <= PW_MAX_COUT;
+}
+
+}  // namespace rg
+
+using namespace rg;
+
+extern "C" {
+
+int rg_pw_conv_fprop(const rg_tensor5* xd, const void* x, const float* w, const float* bias, int act, float slope,
+                     const rg_tensor5* yd, void* y, void* stream) {
+  RG_CHECK_ARG(xd && x && w && yd && y, "rg_pw_conv_fprop: null argument");
+  RG_UNSUPPORTED(!vec_ok(xd, x) || !pw_shape_ok((int)xd->c, (int)yd->c), "rg_pw_conv_fprop: unsupported layout / channel counts");
+  RG_CHECK_ARG(xd->n == yd->n && xd->d == yd->d && xd->h == yd->h && xd->w == yd->w, "rg_pw_conv_fprop: shape mismatch");
+  PwW pw{w, bias, (int)xd->c, (int)yd->c};
+  long long total = (view(xd).numel() >> 3);
+  if (total == 0) return RG_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  RG_DISPATCH_FLOAT(yd->dtype, TY, {
+    pw_fprop_kernel<TY><<<grid_for(total, 256), 256, 0, st>>>(pw, view(xd), (const __nv_bfloat16*)x, view(yd), (TY*)y, act, slope);
+  })
+  RG_LAUNCH_CHECK("rg_pw_conv_fprop");
+  return RG_OK;
+}
+
+int rg_pw_conv_dgrad(const rg_tensor5* dyd, const void* dy, const float* w, const rg_tensor5* dxd, void* dx, void* stream) {
+  RG_CHECK_ARG(dyd && dy && w && dxd && dx, "rg_pw_conv_dgrad: null argument");
+  RG_UNSUPPORTED(!vec_ok(dxd, dx) || !pw_shape_ok((int)dxd->c, (int)dyd->c), "rg_pw_conv_dgrad: unsupported layout / channel counts");
+  RG_CHECK_ARG(dxd->n == dyd->n && dxd->d == dyd->d && dxd->h == dyd->h && dxd->w == dyd->w, "rg_pw_conv_dgrad: shape mismatch");
+  PwW pw{w, nullptr, (int)dxd->c, (int)dyd->c};
+  long long total = (view(dxd).numel() >> 3);
+  if (total == 0) return RG_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  RG_DISPATCH_FLOAT(dyd->dtype, TG, {
+    pw_dgrad_kernel<TG><<<grid_for(total, 256), 256, 0, st>>>(pw, view(dyd), (const TG*)dy, view(dxd), (__nv_bfloat16*)dx);
+  })
+  RG_LAUNCH_CHECK("rg_pw_conv_dgrad");
+  return RG_OK;
+}
+
+int rg_pw_conv_wgrad(const rg_tensor5* xd, const void* x, const rg_tensor5* dyd, const void* dy, float* dw, float* dbias,
+                     void* stream) {
+  RG_CHECK_ARG(xd && x && dyd && dy && dw, "rg_pw_conv_wgrad: null argument");
+  RG_UNSUPPORTED(!vec_ok(xd, x) || !pw_shape_ok((int)xd->c, (int)dyd->c), "rg_pw_conv_wgrad: unsupported layout / channel counts");
+  RG_CHECK_ARG(xd->n == dyd->n && xd->d == dyd->d && xd->h == dyd->h && xd->w == dyd->w, "rg_pw_conv_wgrad: shape mismatch");
+  long long vox = xd->n * xd->d * xd->h * xd->w;
+  if (vox == 0) return RG_OK;
+  long long blocks = 148 * 4;
+  long long vpb = (vox + blocks - 1) / blocks;
+  if (vpb < 256) vpb = 256;
+  blocks = (vox + vpb - 1) / vpb;
+  cudaStream_t st = (cudaStream_t)stream;
+  RG_DISPATCH_FLOAT(dyd->dtype, TG, {
+    pw_wgrad_kernel<TG><<<(unsigned)blocks, 256, 0, st>>>((int)xd->c, (int)dyd->c, view(xd), (const __nv_bfloat16*)x, view(dyd),
+                                                          (const TG*)dy, dw, dbias, vpb);
+  })
+  RG_LAUNCH_CHECK("rg_pw_conv_wgrad");
+  return RG_OK;
+}
+
+}  // extern "C"

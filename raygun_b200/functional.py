@@ -81,8 +81,58 @@ class _Conv3d(torch.autograd.Function):
         return dx, dw, db, None, None, None, None, None, None
 
 
+
+class _StemConv3d(torch.autograd.Function):
+    """Small-Cin convolution (the 7^3 1->64 ResNet stem, ResNet.py:283; the first U-Net ConvPass conv,
+    UNet.py:61-69) on the tensor cores: the H/W taps are folded into 64 bf16 channels by an im2col kernel,
+    leaving a (KD,1,1) convolution with Cin = 64 for the implicit-GEMM kernels (fprop and wgrad).
+    The folded input is recomputed in backward instead of being saved."""
+
+    @staticmethod
+    def forward(ctx, x, w, bias, pad, act, slope, want_stats):
+        cout, cin, kd, kh, kw = w.shape
+        cf = cin * kh * kw
+        xc = K.im2col_hw(x, kh, kw, pad[1], pad[2], 64)
+        w2 = w.detach().permute(0, 2, 1, 3, 4).reshape(cout, kd, cf)          # [co][kd][(ci,kh,kw)]
+        w2 = torch.nn.functional.pad(w2, (0, 64 - cf)).permute(0, 2, 1).reshape(cout, 64, kd, 1, 1).contiguous()
+        y, s, q = CV.conv_fprop(xc, w2, bias, (1, 1, 1), (pad[0], 0, 0), 1, act, slope, want_stats)
+        ctx.cfg = (pad, act, slope, tuple(w.shape), tuple(w2.shape))
+        ctx.has_bias = bias is not None
+        ctx.save_for_backward(x, w, y if act != ACT_NONE else None)
+        if s is None:
+            s = q = x.new_empty(0, dtype=torch.float32)
+        ctx.mark_non_differentiable(s, q)
+        return y, s, q
+
+    @staticmethod
+    def backward(ctx, dy, _ds, _dq):
+        x, w, y = ctx.saved_tensors
+        pad, act, slope, wshape, w2shape = ctx.cfg
+        cout, cin, kd, kh, kw = wshape
+        if act != ACT_NONE:
+            dy = K.act_bwd(y, dy, act, slope)
+        dx = dw = db = None
+        if ctx.needs_input_grad[0]:
+            dx, _, _ = CV.conv_dgrad(dy, w, x.shape, (1, 1, 1), pad, 1, out_dtype=x.dtype)
+        if ctx.needs_input_grad[1] or (ctx.has_bias and ctx.needs_input_grad[2]):
+            xc = K.im2col_hw(x, kh, kw, pad[1], pad[2], 64)
+            dw2, db = CV.conv_wgrad(xc, dy, w2shape, (1, 1, 1), (pad[0], 0, 0), 1, want_bias=ctx.has_bias)
+            dw = dw2.reshape(cout, 64, kd)[:, : cin * kh * kw].reshape(cout, cin, kh, kw, kd).permute(0, 1, 4, 2, 3)
+            dw = dw.contiguous() if ctx.needs_input_grad[1] else None
+        return dx, dw, db, None, None, None, None
+
+
+def _stem_eligible(x, w, stride, groups):
+    cout, cin, kd, kh, kw = w.shape
+    return (K.get_precision() == "bf16" and K.use_tensor_cores() and groups == 1 and stride == (1, 1, 1)
+            and cin % 64 != 0 and cin * kh * kw <= 64 and cout % 64 == 0 and kd <= 8)
+
+
 def conv3d(x, w, bias=None, stride=1, padding=0, groups=1, act=ACT_NONE, slope=0.0, want_stats=False):
-    y, s, q = _Conv3d.apply(x, w, bias, _t3(stride), _t3(padding), int(groups), act, float(slope), bool(want_stats))
+    if _stem_eligible(x, w, _t3(stride), int(groups)):
+        y, s, q = _StemConv3d.apply(x, w, bias, _t3(padding), act, float(slope), bool(want_stats))
+    else:
+        y, s, q = _Conv3d.apply(x, w, bias, _t3(stride), _t3(padding), int(groups), act, float(slope), bool(want_stats))
     if want_stats:
         return y, (s, q) if s.numel() else None
     return y

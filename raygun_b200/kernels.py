@@ -82,6 +82,17 @@ def convert(x: torch.Tensor, dtype) -> torch.Tensor:
     return copy_into(empty5(x.shape, dtype, x.device), x)
 
 
+def im2col_hw(x, kh, kw, ph, pw, channels=64):
+    """Fold the H/W taps of a small-Cin convolution into `channels` bf16 NDHWC channels."""
+    require_device(x)
+    n, c, d, h, w = x.shape
+    y = empty5((n, channels, d, h + 2 * ph - kh + 1, w + 2 * pw - kw + 1), torch.bfloat16, x.device)
+    check(lib().rg_im2col_hw(C.byref(t5(x)), ptr(x), C.c_int(kh), C.c_int(kw), C.c_int(ph), C.c_int(pw),
+                             C.byref(t5(y)), ptr(y), stream_ptr(x.device)), "rg_im2col_hw")
+    count_launch()
+    return y
+
+
 def pad3d(x, lo, hi, mode):
     require_device(x)
     n, c, d, h, w = x.shape

@@ -160,3 +160,57 @@ def test_bf16_generator_forward_backward_close_to_fp32_oracle():
     # (stock torch autocast(bf16) on the same net shows the same 0.28, scripts/diag_bf16.py): check direction
     assert _cos(g, sdr[gk].grad) >= 0.98, _cos(g, sdr[gk].grad)
     assert _rel(g, sdr[gk].grad) <= 0.5
+
+
+@pytest.mark.parametrize("case", [(1, 64, 7, 3, (12, 13, 14)), (1, 64, 3, 1, (9, 9, 9)), (2, 128, 3, 0, (8, 8, 8)),
+                                  (1, 64, (3, 5, 5), (1, 2, 2), (6, 9, 9))])
+def test_small_cin_stem_runs_on_tensor_cores(case):
+    """Cin*KH*KW <= 64: H/W taps folded into channels (rg_im2col_hw) + (KD,1,1) implicit GEMM, fwd + wgrad."""
+    import raygun_b200 as rb
+    from raygun_b200 import conv as CV
+    from raygun_b200 import functional as F
+    cin, cout, k, p, sp = case
+    torch.manual_seed(15)
+    x = _q(torch.randn(2, cin, *sp))
+    conv = torch.nn.Conv3d(cin, cout, k, padding=p)
+    with torch.no_grad():
+        conv.weight.copy_(_q(conv.weight))
+    y_ref = conv(x)
+    r = _q(torch.randn_like(y_ref))
+    gw, gb = torch.autograd.grad((y_ref * r).sum(), [conv.weight, conv.bias])
+    before = CV.stats["igemm"]
+    with rb.precision("bf16"):
+        w = conv.weight.detach().to(DEV).requires_grad_(True)
+        b = conv.bias.detach().to(DEV).requires_grad_(True)
+        y = F.conv3d(x.to(DEV), w, b, 1, p)
+        y.backward(r.to(DEV).bfloat16())
+    assert CV.stats["igemm"] == before + 2
+    assert _rel(y, y_ref) <= 1e-2
+    assert _rel(w.grad, gw) <= 5e-3
+    assert _rel(b.grad, gb) <= 5e-3
+
+
+@pytest.mark.parametrize("cin,cout", [(64, 1), (16, 3), (256, 2)])
+def test_pointwise_small_cout_conv_forward_backward(cin, cout):
+    """Conv3d(ngf, output_nc, 1) + Tanh head (BaseSystem.py:209-224): streaming fprop / dgrad / wgrad kernels."""
+    import raygun_b200 as rb
+    from raygun_b200 import conv as CV
+    from raygun_b200 import functional as F
+    torch.manual_seed(16)
+    x = _q(torch.randn(2, cin, 5, 6, 7)).requires_grad_(True)
+    conv = torch.nn.Conv3d(cin, cout, 1)
+    y_ref = torch.tanh(conv(x))
+    r = torch.randn_like(y_ref)
+    gx, gw, gb = torch.autograd.grad((y_ref * r).sum(), [x, conv.weight, conv.bias])
+    before = CV.stats.get("pointwise", 0)
+    with rb.precision("bf16"):
+        xg = x.detach().to(DEV).bfloat16().contiguous(memory_format=torch.channels_last_3d).requires_grad_(True)
+        w = conv.weight.detach().to(DEV).requires_grad_(True)
+        b = conv.bias.detach().to(DEV).requires_grad_(True)
+        y = F.cast(F.conv3d(xg, w, b, 1, 0, act=3), torch.float32)
+        y.backward(r.to(DEV))
+    assert CV.stats.get("pointwise", 0) == before + 3
+    assert _rel(y, y_ref) <= 1e-2
+    assert _rel(xg.grad, gx) <= 2e-2
+    assert _rel(w.grad, gw) <= 2e-2
+    assert _rel(b.grad, gb) <= 2e-2
