@@ -1,0 +1,86 @@
+"""Blockwise volume prediction on the sm_100a path.
+
+Restates the Daisy task geometry of the reference (``predict.py:73-108,154-164``: write blocks tile the volume from
+its origin, read block = write block grown by ``context = (read - write) // 2``) and the worker arithmetic
+(``torch/predict/worker.py:100-147``: uint8 -> float, ``/255``, ``*scale + shift``, model, centre crop, ``*255``, clamp,
+TRUNCATING cast to uint8) over an in-memory volume.  Daisy / zarr are I/O and stay the reference's.
+
+Blocks are independent given their halo, so ranks take a static round-robin share of the block list and never
+communicate.  Volume faces are reflect-padded, i.e. exactly what the whole-volume 'same'/reflect network would see.
+Unlike the reference worker (which builds an autograd graph per block, worker.py:116), inference runs under no_grad
+and the block crosses PCIe as uint8, not float32.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import functional as F
+from . import kernels as K
+
+
+def block_origins(vol_shape, write_shape):
+    """Origins of the write blocks, z-major (the order Daisy hands them out for a dependency-free task)."""
+    return [(z, y, x) for z in range(0, vol_shape[0], write_shape[0]) for y in range(0, vol_shape[1], write_shape[1])
+            for x in range(0, vol_shape[2], write_shape[2])]
+
+
+def rank_blocks(origins, rank=0, world=1):
+    return origins[rank::world]
+
+
+def read_block(volume_u8: torch.Tensor, origin, read_shape, context, device, scale=2.0, shift=-1.0, dtype=None):
+    """Fetch one read block as a normalised (1,1,d,h,w) device tensor; parts outside the volume are mirrored."""
+    lo_pad, hi_pad, sl = [], [], []
+    for o, r, c, v in zip(origin, read_shape, context, volume_u8.shape):
+        a, b = o - c, o - c + r
+        lo, hi = max(0, -a), max(0, b - v)
+        lo_pad.append(lo)
+        hi_pad.append(hi)
+        sl.append(slice(a + lo, b - hi))
+    sub = volume_u8[tuple(sl)]
+    if not sub.is_cuda:
+        sub = sub.contiguous().to(device, non_blocking=True)
+    x = K.u8_normalise(sub.contiguous(), scale, shift, dtype or torch.float32)[None, None]
+    if any(lo_pad) or any(hi_pad):
+        ok = all(p < s for p, s in zip(lo_pad, x.shape[2:])) and all(p < s for p, s in zip(hi_pad, x.shape[2:]))
+        x = F.pad3d(x, tuple(lo_pad), tuple(hi_pad), "reflect" if ok else "replicate")
+    return x
+
+
+@torch.no_grad()
+def predict_volume(model, volume_u8: torch.Tensor, read_shape, write_shape, out: torch.Tensor | None = None, rank=0,
+                   world=1, scale_shift=(2.0, -1.0), device=None):
+    """Run `model` blockwise over a (D,H,W) uint8 volume; returns (out, n_blocks_done, voxels_written).
+
+    `out` (uint8, same shape as the volume, CPU or CUDA) receives this rank's blocks; other voxels are untouched."""
+    if volume_u8.dim() != 3 or volume_u8.dtype != torch.uint8:
+        raise ValueError("volume must be a (D,H,W) uint8 tensor")
+    read_shape, write_shape = tuple(read_shape), tuple(write_shape)
+    if any((r - w) % 2 or r < w for r, w in zip(read_shape, write_shape)):
+        raise ValueError("read_shape - write_shape must be even and non-negative in every dimension")
+    context = tuple((r - w) // 2 for r, w in zip(read_shape, write_shape))
+    device = device or torch.device("cuda", torch.cuda.current_device())
+    if out is None:
+        out = torch.zeros(volume_u8.shape, dtype=torch.uint8, device="cpu").pin_memory()
+    was_training = model.training
+    model.eval()
+    done = vox = 0
+    for origin in rank_blocks(block_origins(volume_u8.shape, write_shape), rank, world):
+        x = read_block(volume_u8, origin, read_shape, context, device, *scale_shift)
+        y = model(x)
+        y = y[0] if isinstance(y, (list, tuple)) else y
+        if tuple(y.shape[2:]) == read_shape:          # 'same' network: crop the halo (worker.py:124-129)
+            y = y[:, :, context[0]: read_shape[0] - context[0], context[1]: read_shape[1] - context[1],
+                  context[2]: read_shape[2] - context[2]]
+        elif tuple(y.shape[2:]) != write_shape:
+            raise RuntimeError(f"model output {tuple(y.shape[2:])} matches neither read {read_shape} nor write {write_shape}")
+        ext = tuple(min(w, v - o) for w, v, o in zip(write_shape, volume_u8.shape, origin))
+        y = y[:, :1, : ext[0], : ext[1], : ext[2]]
+        blk = K.denorm_clamp_u8(y)[0, 0]               # *255, clamp, truncating cast -- on the device
+        dst = out[origin[0]: origin[0] + ext[0], origin[1]: origin[1] + ext[1], origin[2]: origin[2] + ext[2]]
+        dst.copy_(blk, non_blocking=True)
+        done += 1
+        vox += ext[0] * ext[1] * ext[2]
+    torch.cuda.synchronize(device)
+    model.train(was_training)
+    return out, done, vox

@@ -94,3 +94,33 @@ def test_cyclegan_training_steps_match_reference_losses():
             got = [float(out[k]) for k in ("G1", "G2", "D1", "D2")]
             for gv, rv in zip(got, c["losses"][it]):
                 assert abs(gv - rv) <= 1e-3 * max(1.0, abs(rv)), (it, got, c["losses"][it])
+
+
+def test_blockwise_prediction_equals_whole_volume_and_oracle_arithmetic():
+    """cfg4 in miniature: G-UNet ('same', 2 downsamplings) over a uint8 volume in halo-24 blocks with origins = 0 mod 4
+    reproduces the whole-volume forward (exact iff crop >= 22 and aligned origins), and the worker's
+    normalise / denormalise arithmetic (truncating cast) matches the oracle restatement."""
+    import raygun_b200 as rb
+    from oracle import restate as O
+    from raygun_b200 import kernels as K
+    from raygun_b200 import predict as P
+    from raygun_b200.cyclegan import make_generator
+    from raygun_b200.synth import em_like_u8
+    torch.manual_seed(3)
+    g = make_generator("unet", dict(input_nc=1, output_nc=1, ngf=4, fmap_inc_factor=2, num_downs=3, padding_type="same",
+                                    final_activation="Tanh")).to(DEV).eval()
+    vol = torch.from_numpy(em_like_u8((40, 48, 36), seed=42))
+    with rb.precision("fp32"), torch.no_grad():
+        whole = g(K.u8_normalise(vol.to(DEV), dtype=torch.float32)[None, None])
+        ref_u8 = K.denorm_clamp_u8(whole)[0, 0].cpu()
+        outs = []
+        for rank in range(2):       # two "ranks" fill disjoint block sets of one output volume
+            out, n, vox = P.predict_volume(g, vol, (64, 64, 64), (16, 16, 16), out=outs[0] if outs else None,
+                                           rank=rank, world=2)
+            outs.append(out)
+    out = outs[0]
+    diff = (out.int() - ref_u8.int()).abs()
+    assert int(diff.max()) <= 1 and float((diff > 0).float().mean()) < 1e-3      # fp32 rounding at truncation edges only
+    # oracle arithmetic on the same fp32 network output
+    assert torch.equal(ref_u8, O.denorm_clamp_u8(whole.cpu())[0, 0])
+    assert torch.equal(K.u8_normalise(vol.to(DEV), dtype=torch.float32).cpu(), O.u8_normalise(vol))
