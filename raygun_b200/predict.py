@@ -1,12 +1,13 @@
 """Blockwise volume prediction on the sm_100a path.
 
-Restates the Daisy task geometry of the reference (``predict.py:73-108,154-164``: write blocks tile the volume from
-its origin, read block = write block grown by ``context = (read - write) // 2``) and the worker arithmetic
+Restates the Daisy task geometry of the reference (``predict.py:73-108,154-164``: read roi at the origin, write roi
+= read roi shrunk by ``context = (read - write) // 2``, blocks shifted by the write size while the read roi stays
+inside the volume) and the worker arithmetic
 (``torch/predict/worker.py:100-147``: uint8 -> float, ``/255``, ``*scale + shift``, model, centre crop, ``*255``, clamp,
 TRUNCATING cast to uint8) over an in-memory volume.  Daisy / zarr are I/O and stay the reference's.
 
 Blocks are independent given their halo, so ranks take a static round-robin share of the block list and never
-communicate.  Volume faces are reflect-padded, i.e. exactly what the whole-volume 'same'/reflect network would see.
+communicate.  With fit="mirror" the blocks also cover the outer shell, the input being mirrored at the volume faces.
 Unlike the reference worker (which builds an autograd graph per block, worker.py:116), inference runs under no_grad
 and the block crosses PCIe as uint8, not float32.
 """
@@ -18,10 +19,21 @@ from . import functional as F
 from . import kernels as K
 
 
-def block_origins(vol_shape, write_shape):
-    """Origins of the write blocks, z-major (the order Daisy hands them out for a dependency-free task)."""
-    return [(z, y, x) for z in range(0, vol_shape[0], write_shape[0]) for y in range(0, vol_shape[1], write_shape[1])
-            for x in range(0, vol_shape[2], write_shape[2])]
+def block_origins(vol_shape, write_shape, read_shape=None, fit="valid"):
+    """Origins of the write blocks, z-major (the order Daisy hands them out for a dependency-free task).
+
+    fit="valid" is the reference's behaviour (`predict.py:154-164` leaves daisy's default fit): the first write block sits
+    at `context`, and only blocks whose READ roi lies inside the volume are processed -- the outer `context` shell of
+    the output stays unwritten.  fit="mirror" (an extension) tiles the whole volume from the origin and mirrors the
+    input at the volume faces; voxels nearer than the network's field of view to a face are then approximate."""
+    if fit == "mirror" or read_shape is None:
+        return [(z, y, x) for z in range(0, vol_shape[0], write_shape[0]) for y in range(0, vol_shape[1], write_shape[1])
+                for x in range(0, vol_shape[2], write_shape[2])]
+    if fit != "valid":
+        raise NotImplementedError(f"fit [{fit}] is not implemented")
+    ctx = [(r - w) // 2 for r, w in zip(read_shape, write_shape)]
+    axes = [range(c, v - r + c + 1, w) for c, v, r, w in zip(ctx, vol_shape, read_shape, write_shape)]
+    return [(z, y, x) for z in axes[0] for y in axes[1] for x in axes[2]]
 
 
 def rank_blocks(origins, rank=0, world=1):
@@ -49,7 +61,7 @@ def read_block(volume_u8: torch.Tensor, origin, read_shape, context, device, sca
 
 @torch.no_grad()
 def predict_volume(model, volume_u8: torch.Tensor, read_shape, write_shape, out: torch.Tensor | None = None, rank=0,
-                   world=1, scale_shift=(2.0, -1.0), device=None):
+                   world=1, scale_shift=(2.0, -1.0), device=None, fit="valid", dtype=None):
     """Run `model` blockwise over a (D,H,W) uint8 volume; returns (out, n_blocks_done, voxels_written).
 
     `out` (uint8, same shape as the volume, CPU or CUDA) receives this rank's blocks; other voxels are untouched."""
@@ -65,8 +77,8 @@ def predict_volume(model, volume_u8: torch.Tensor, read_shape, write_shape, out:
     was_training = model.training
     model.eval()
     done = vox = 0
-    for origin in rank_blocks(block_origins(volume_u8.shape, write_shape), rank, world):
-        x = read_block(volume_u8, origin, read_shape, context, device, *scale_shift)
+    for origin in rank_blocks(block_origins(volume_u8.shape, write_shape, read_shape, fit), rank, world):
+        x = read_block(volume_u8, origin, read_shape, context, device, *scale_shift, dtype=dtype)
         y = model(x)
         y = y[0] if isinstance(y, (list, tuple)) else y
         if tuple(y.shape[2:]) == read_shape:          # 'same' network: crop the halo (worker.py:124-129)

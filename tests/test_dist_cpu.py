@@ -59,3 +59,10 @@ def test_block_partition_is_a_disjoint_cover():
     parts = [P.rank_blocks(origins, r, 3) for r in range(3)]
     assert sorted(sum(parts, [])) == sorted(origins)
     assert max(len(p) for p in parts) - min(len(p) for p in parts) <= 1
+
+
+def test_valid_fit_matches_daisy_geometry():
+    """predict.py:154-164: read roi at the origin, shifted by the write size while it stays inside the volume."""
+    o = P.block_origins((100, 64, 70), (16, 16, 16), (64, 64, 64), fit="valid")
+    assert o[0] == (24, 24, 24) and len(o) == 3 * 1 * 1 and o[-1] == (56, 24, 24)
+    assert P.block_origins((63, 64, 64), (16,) * 3, (64,) * 3) == []

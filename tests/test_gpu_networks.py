@@ -109,18 +109,32 @@ def test_blockwise_prediction_equals_whole_volume_and_oracle_arithmetic():
     torch.manual_seed(3)
     g = make_generator("unet", dict(input_nc=1, output_nc=1, ngf=4, fmap_inc_factor=2, num_downs=3, padding_type="same",
                                     final_activation="Tanh")).to(DEV).eval()
-    vol = torch.from_numpy(em_like_u8((40, 48, 36), seed=42))
+    vol = torch.from_numpy(em_like_u8((80, 72, 76), seed=42))
     with rb.precision("fp32"), torch.no_grad():
         whole = g(K.u8_normalise(vol.to(DEV), dtype=torch.float32)[None, None])
         ref_u8 = K.denorm_clamp_u8(whole)[0, 0].cpu()
-        outs = []
+        outs, outs_m = [], []
         for rank in range(2):       # two "ranks" fill disjoint block sets of one output volume
             out, n, vox = P.predict_volume(g, vol, (64, 64, 64), (16, 16, 16), out=outs[0] if outs else None,
                                            rank=rank, world=2)
             outs.append(out)
-    out = outs[0]
-    diff = (out.int() - ref_u8.int()).abs()
+            outm, nm, voxm = P.predict_volume(g, vol, (64, 64, 64), (16, 16, 16), out=outs_m[0] if outs_m else None,
+                                              rank=rank, world=2, fit="mirror")
+            outs_m.append(outm)
+    out, outm = outs[0], outs_m[0]
+    # reference geometry (daisy fit="valid"): blocks cover [24, 24 + 16k) per axis, the context shell stays unwritten
+    inner = (slice(24, 56), slice(24, 40), slice(24, 40))
+    assert len(P.block_origins(vol.shape, (16,) * 3, (64,) * 3)) == 2 * 1 * 1
+    diff = (out[inner].int() - ref_u8[inner].int()).abs()
     assert int(diff.max()) <= 1 and float((diff > 0).float().mean()) < 1e-3      # fp32 rounding at truncation edges only
+    mask = torch.ones_like(out, dtype=torch.bool)
+    mask[inner] = False
+    assert int(out[mask].max()) == 0
+    # mirror fit covers everything; farther than the halo from every face it equals the whole-volume forward
+    core = (slice(24, 56), slice(24, 48), slice(24, 52))
+    diffm = (outm[core].int() - ref_u8[core].int()).abs()
+    assert int(diffm.max()) <= 1 and float((diffm > 0).float().mean()) < 1e-3
+    assert float((outm.int() - ref_u8.int()).abs().float().mean()) < 8.0          # shell: approximate, not garbage
     # oracle arithmetic on the same fp32 network output
     assert torch.equal(ref_u8, O.denorm_clamp_u8(whole.cpu())[0, 0])
     assert torch.equal(K.u8_normalise(vol.to(DEV), dtype=torch.float32).cpu(), O.u8_normalise(vol))
