@@ -109,6 +109,19 @@ int rg_igemm_run(const rg_plan* plan, const void* in, const void* w_packed, cons
 int rg_igemm_wgrad(const rg_plan* plan, const void* x, const void* dy, float* dw, float* dbias,
                    void* workspace, void* stream);
 
+/* ---- slice-ring convolution (stride 1; 64-channel produced blocks; ring_conv_sm100.cu) -------------------
+ * Same role as rg_igemm_run for fprop (ConvPass / ResnetGenerator3D head, UNet.py:52-87, ResNet.py:324-327) and
+ * stride-1 dgrad, for layers where the plain implicit GEMM is L2-feed bound.  The weights are packed per
+ * (n-tile, k-chunk, kh, kw) as [kd reversed][64 produced][64 reduction] bf16 by rg_ring_pack_weights
+ * (mode 0 = fprop, 1 = dgrad: taps flipped, channel roles swapped); same element count as the fp32 weights.
+ * rg_ring_supported: 1 when rg_ring_run accepts `desc`.  rg_ring_config: {S, lag, slice buffers, weight stages,
+ * segment length, segments, smem bytes, slice pitch} the host picks (introspection for tests / docs).        */
+int rg_ring_supported(const rg_igemm_desc* desc);
+int rg_ring_config(const rg_igemm_desc* desc, int* out8);
+int rg_ring_pack_weights(const float* w, int cout, int cin, const int* kernel3, int mode, void* out_bf16, void* stream);
+int rg_ring_run(const rg_igemm_desc* desc, const void* in, const void* w_ring, const float* bias, void* out,
+                float* stats_sum, float* stats_sqsum, void* stream);
+
 /* ---- 1x1x1 convolutions onto <= 4 channels (BaseSystem.py:209-224: Conv3d(ngf, output_nc, 1) + Tanh) -------
  * HBM-bound streaming kernels over a bf16 NDHWC x (Cin/8 a power of two <= 32); w fp32 [Cout][Cin].
  * fprop fuses bias + activation; wgrad accumulates into dw / dbias (caller zeroes).                     */

@@ -26,7 +26,8 @@ SYMBOLS = [
     "rg_version", "rg_last_error", "rg_device_check",
     "rg_conv3d_direct_fprop", "rg_conv3d_direct_dgrad", "rg_conv3d_direct_wgrad",
     "rg_plan_create", "rg_plan_destroy", "rg_plan_workspace_bytes", "rg_pack_weights",
-    "rg_igemm_run", "rg_igemm_wgrad", "rg_pw_conv_fprop", "rg_pw_conv_dgrad", "rg_pw_conv_wgrad",
+    "rg_igemm_run", "rg_igemm_wgrad", "rg_ring_supported", "rg_ring_config", "rg_ring_pack_weights", "rg_ring_run",
+    "rg_pw_conv_fprop", "rg_pw_conv_dgrad", "rg_pw_conv_wgrad",
     "rg_copy5", "rg_im2col_hw", "rg_pad3d_fwd", "rg_pad3d_bwd",
     "rg_norm_stats", "rg_norm_finalize", "rg_norm_apply", "rg_norm_bwd",
     "rg_act_fwd", "rg_act_bwd",

@@ -127,6 +127,60 @@ def _get_plan(mode, n, cin, cout, in_dhw, out_dhw, kernel, stride, pad, xs, ys, 
     return _plans[key]
 
 
+# --------------------------------------------------------------------------------------------
+# slice-ring kernel (stride-1 layers producing 64-channel blocks): descriptor, support cache, weight packs
+# --------------------------------------------------------------------------------------------
+import os
+
+_ring_descs: "dict[tuple, IgemmDesc | None]" = {}
+_ring_packs: "dict[tuple, tuple]" = {}
+RING_MAX_PRODUCED = int(os.environ.get("RAYGUN_B200_RING_MAX_PRODUCED", "64"))   # 0 disables the ring kernel
+
+
+def _ring_desc(mode, n, cin, cout, in_dhw, out_dhw, kernel, stride, pad, xs, ys, act, slope):
+    """IgemmDesc when the slice-ring kernel should run this layer, else None."""
+    produced = cout if mode == 0 else cin
+    if tuple(stride) != (1, 1, 1) or produced > RING_MAX_PRODUCED or produced % 64 or (cin if mode == 0 else cout) % 64:
+        return None
+    key = (mode, n, cin, cout, tuple(in_dhw), tuple(out_dhw), tuple(kernel), tuple(pad), tuple(xs), tuple(ys), act, slope)
+    if key in _ring_descs:
+        return _ring_descs[key]
+    d = IgemmDesc()
+    d.mode, d.n, d.cin, d.cout = mode, n, cin, cout
+    d.in_dhw[:] = list(in_dhw)
+    d.out_dhw[:] = list(out_dhw)
+    d.kernel[:] = list(kernel)
+    d.stride[:] = [1, 1, 1]
+    d.pad[:] = list(pad)
+    d.x_strides[:] = list(xs)
+    d.y_strides[:] = list(ys)
+    d.act, d.slope = act, slope
+    ok = lib().rg_ring_supported(C.byref(d)) == 1
+    _ring_descs[key] = d if ok else None
+    return _ring_descs[key]
+
+
+def ring_packed_weights(w: torch.Tensor, mode: int):
+    """bf16 slice-ring pack of a conv-layout weight for fprop (mode 0) or dgrad (mode 1); cached per version."""
+    key = (id(w), mode)
+    ent = _ring_packs.get(key)
+    ver = w._version
+    if ent is not None and ent[0]() is w and ent[1] == ver and ent[2] == w.data_ptr():
+        return ent[3]
+    wsrc = w.detach()
+    if not wsrc.is_contiguous():
+        wsrc = wsrc.contiguous()
+    out = torch.empty(w.numel(), dtype=torch.bfloat16, device=w.device)
+    check(lib().rg_ring_pack_weights(ptr(wsrc), C.c_int(w.shape[0]), C.c_int(w.shape[1]), i3(w.shape[2:]), C.c_int(mode),
+                                     ptr(out), stream_ptr(w.device)), "rg_ring_pack_weights")
+    count_launch()
+    if len(_ring_packs) > 4096:
+        for k in [k for k, e in _ring_packs.items() if e[0]() is None]:
+            del _ring_packs[k]
+    _ring_packs[key] = (weakref.ref(w), ver, w.data_ptr(), out)
+    return out
+
+
 def _sp_strides(t):
     s = t.stride()
     return (s[0], s[2], s[3], s[4])
@@ -162,6 +216,19 @@ def conv_fprop(x, w, bias, stride, pad, groups=1, act=ACT_NONE, slope=0.0, want_
     if _igemm_ok(cin_t, cout, kernel, stride, groups) and cdt == torch.bfloat16:
         xb = K.convert(x, torch.bfloat16)
         y = K.empty5((n, cout, *od), torch.bfloat16, x.device)
+        rd = _ring_desc(0, n, cin_t, cout, (d, h, wd_), od, kernel, stride, pad, _sp_strides(xb), _sp_strides(y),
+                        act, float(slope))
+        if rd is not None:
+            wr = ring_packed_weights(w, 0)
+            st = torch.zeros(2, n * cout, dtype=torch.float32, device=x.device) if want_stats else None
+            with _Timed("fprop", 2.0 * y.numel() * cin_t * kernel[0] * kernel[1] * kernel[2], x.device):
+                check(lib().rg_ring_run(C.byref(rd), ptr(xb), ptr(wr), ptr(bias_f), ptr(y),
+                                        ptr(st[0]) if want_stats else None, ptr(st[1]) if want_stats else None,
+                                        stream_ptr(x.device)), "rg_ring_run(fprop)")
+            count_launch()
+            stats["igemm"] += 1
+            stats["ring"] = stats.get("ring", 0) + 1
+            return (y, st[0], st[1]) if want_stats else (y, None, None)
         plan = _get_plan(0, n, cin_t, cout, (d, h, wd_), od, kernel, stride, pad, _sp_strides(xb), _sp_strides(y),
                          act, float(slope))
         if plan is not None:
@@ -207,6 +274,19 @@ def conv_dgrad(dy, w, x_shape, stride, pad, groups=1, bias=None, act=ACT_NONE, s
     if _igemm_ok(cin_t, cout_t, kernel, stride, groups) and cdt == torch.bfloat16:
         dyb = K.convert(dy, torch.bfloat16)
         dx = K.empty5(tuple(x_shape), torch.bfloat16, dy.device)
+        rd = _ring_desc(1, n, cin_t, cout_t, tuple(x_shape[2:]), (od, oh, ow), kernel, stride, pad, _sp_strides(dx),
+                        _sp_strides(dyb), act, float(slope))
+        if rd is not None:
+            wr = ring_packed_weights(w, 1)
+            st = torch.zeros(2, n * cin_t, dtype=torch.float32, device=dy.device) if want_stats else None
+            with _Timed("dgrad", 2.0 * dyb.numel() * cin_t * kernel[0] * kernel[1] * kernel[2], dy.device):
+                check(lib().rg_ring_run(C.byref(rd), ptr(dyb), ptr(wr), ptr(bias_f), ptr(dx),
+                                        ptr(st[0]) if want_stats else None, ptr(st[1]) if want_stats else None,
+                                        stream_ptr(dy.device)), "rg_ring_run(dgrad)")
+            count_launch()
+            stats["igemm"] += 1
+            stats["ring"] = stats.get("ring", 0) + 1
+            return (dx, st[0], st[1]) if want_stats else (dx, None, None)
         plan = _get_plan(1, n, cin_t, cout_t, tuple(x_shape[2:]), (od, oh, ow), kernel, stride, pad, _sp_strides(dx),
                          _sp_strides(dyb), act, float(slope))
         if plan is not None:

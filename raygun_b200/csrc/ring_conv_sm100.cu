@@ -1,0 +1,585 @@
+// Slice-ring implicit-GEMM Conv3d (stride 1) on tcgen05 tensor cores: the kernel for layers that produce 64-channel
+// blocks with many taps (the 7^3 64->64 ResNet head, ResNet.py:324-327, is 70 % of the generator's FLOPs; the 3^3
+// 64-channel U-Net levels, UNet.py:52-87).  The plain implicit GEMM (igemm_sm100.cu) is L2-feed bound there: it pulls
+// a fresh 16 KB activation tile and an 8 KB weight tile per 128x64x64 MMA block (192 B/clk/SM at tensor rate), and a
+// 128 x 64 x 16 SS-mode MMA is itself shared-memory-read bound (48 clk instead of 32; profiles/r01_exp_umma_*.txt).
+//
+// Formulation (input-stationary along depth):
+//   * a CTA owns an output column: a 16(h) x 8(w) tile, a depth segment [d0, d0+L);
+//   * input slice z (one depth plane of the tile WITH its (kh,kw) halo, 64 channels) is loaded ONCE by TMA into
+//     128B-swizzled smem; the A operand of tap (kh,kw) is the same buffer addressed through a UMMA descriptor whose
+//     start is shifted by (kh*WB+kw) rows and whose 8-row-group stride is WB*128 B (swizzle is anchored on absolute
+//     smem address bits, so row-shifted descriptors are exact -- verified by scripts/exp_umma.cu);
+//   * slice z contributes to the KD output planes d = z+pd-kd, so one MMA multiplies the A tile with the weights of
+//     ALL kd at once: N = 64*KD columns (split in <= 256-column pieces) -> full-rate MMAs, A read once per KD taps;
+//   * TMEM holds a ring of eight 128x64 fp32 accumulators, one per output plane in flight; plane d lives in block
+//     (d-d0) mod 8.  S consecutive input slices share every weight stage (S + KD - 1 <= 8), which divides the weight
+//     traffic by S.  When a plane has received its last slice, the epilogue warps drain it (bias, activation, bf16,
+//     Instance/BatchNorm sum / sum-of-squares), re-zero the block and hand it back.
+// Warp roles: warp 0 = TMA producer, warp 1 = MMA issuer + TMEM owner, warps 2-5 = epilogue.
+#include <cuda.h>
+#include <cuda_bf16.h>
+
+#include "common.cuh"
+#include "sm100_ptx.cuh"
+
+namespace rg {
+
+constexpr int RING_THREADS = 192;
+constexpr int RING_BLOCKS = 8;            // accumulator blocks of 64 TMEM columns
+constexpr int WBLK_BYTES = 64 * 128;      // weights of one (tap, kd): 64 produced channels x 64 reduction channels bf16
+constexpr int STAGE_KD = 4;               // kd blocks per weight stage (<= 256 MMA columns)
+constexpr int RING_TH = 16, RING_TW = 8;  // output tile (h, w); 8 = one swizzle-atom row group
+constexpr int MAX_S = 8, MAX_NA = 12, MAX_NB = 4;
+constexpr int PTAB_N = 2 * MAX_S;                                   // pieces per weight-stage part (<= 2 per slice)
+constexpr int RING_PTAB_OFF = 8 * (2 * MAX_NA + 2 * MAX_NB + 4) + 32;
+constexpr int RING_TAIL_BYTES = RING_PTAB_OFF + 2 * PTAB_N * 16 + 64;
+
+struct alignas(64) RingParams {
+  CUtensorMap a_map;      // 5-D {C, W, H, D, N}; box {64, WB, HB, 1, 1}
+  CUtensorMap b_map;      // 2-D {64, rows};      box {64, 64}
+  int kd, kh, kw;
+  int pd, ph, pw;         // coordinate offsets (zero padding through TMA out-of-bounds fill)
+  int q_chunks;           // reduction channels / 64
+  int n_tiles_n;          // produced channels / 64
+  int S, lag, na, nb;
+  int slice_bytes;        // smem pitch of a slice buffer (multiple of 1024)
+  int slice_tx;           // bytes one slice TMA delivers: HB * WB * 128
+  int stage_bytes;        // smem pitch of a weight stage
+  int wb;                 // slice row pitch in voxels: RING_TW + kw - 1
+  int tiles_h, tiles_w, segs, seg_len, batch;
+  int in_d;               // depth extent of the input (fully out-of-range slices are skipped)
+  int out_d, out_h, out_w;
+  long long ys_n, ys_d, ys_h, ys_w;
+  __nv_bfloat16* y;
+  int cout_total;
+  int act; float slope;
+  const float* bias;
+  float* stats_sum; float* stats_sq;
+};
+
+struct RingUnit { int nt, n, h0, w0, d0, len, z_begin, z_end; };
+
+__device__ __forceinline__ RingUnit ring_decode(const RingParams& p, int u) {
+  RingUnit r;
+  r.nt = u % p.n_tiles_n; u /= p.n_tiles_n;
+  const int iw = u % p.tiles_w; u /= p.tiles_w;
+  const int ih = u % p.tiles_h; u /= p.tiles_h;
+  const int sg = u % p.segs; r.n = u / p.segs;
+  r.h0 = ih * RING_TH; r.w0 = iw * RING_TW; r.d0 = sg * p.seg_len;
+  r.len = min(p.seg_len, p.out_d - r.d0);
+  r.z_begin = r.d0 - p.pd;
+  r.z_end = r.d0 + r.len - 1 - p.pd + p.kd - 1;
+  return r;
+}
+
+__global__ void __launch_bounds__(RING_THREADS, 1) ring_conv_kernel(const __grid_constant__ RingParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = ptx::smem_u32(smem_raw);
+  const uint32_t base = (raw + 1023u) & ~1023u;
+  uint8_t* base_ptr = smem_raw + (base - raw);
+  const uint32_t smem_a = base;
+  const uint32_t smem_b = base + (uint32_t)(p.na * p.slice_bytes);
+  uint8_t* tail = base_ptr + (size_t)p.na * p.slice_bytes + (size_t)p.nb * p.stage_bytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(tail);     // afull[na] aempty[na] bfull[nb] bempty[nb] tfull[2] tempty[2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tail + 8 * (2 * MAX_NA + 2 * MAX_NB + 4));
+  uint4* ptab = reinterpret_cast<uint4*>(tail + RING_PTAB_OFF);          // [2 parts][PTAB_N] piece table of the MMA warp
+  int* pcnt = reinterpret_cast<int*>(tail + RING_PTAB_OFF + 2 * PTAB_N * 16);
+  const uint32_t bar0 = ptx::smem_u32(bars);
+  auto afull = [&](int s) { return bar0 + 8u * s; };
+  auto aempty = [&](int s) { return bar0 + 8u * (MAX_NA + s); };
+  auto bfull = [&](int s) { return bar0 + 8u * (2 * MAX_NA + s); };
+  auto bempty = [&](int s) { return bar0 + 8u * (2 * MAX_NA + MAX_NB + s); };
+  auto tfull = [&](int s) { return bar0 + 8u * (2 * MAX_NA + 2 * MAX_NB + s); };
+  auto tempty = [&](int s) { return bar0 + 8u * (2 * MAX_NA + 2 * MAX_NB + 2 + s); };
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int total_units = p.batch * p.segs * p.tiles_h * p.tiles_w * p.n_tiles_n;
+  const int ntaps_hw = p.kh * p.kw;
+  const int parts = (p.kd + STAGE_KD - 1) / STAGE_KD;
+
+  if (warp == 0 && lane == 0) {
+    for (int s = 0; s < p.na; ++s) { ptx::mbar_init(afull(s), 1); ptx::mbar_init(aempty(s), 1); }
+    for (int s = 0; s < p.nb; ++s) { ptx::mbar_init(bfull(s), 1); ptx::mbar_init(bempty(s), 1); }
+    for (int s = 0; s < 2; ++s) { ptx::mbar_init(tfull(s), 1); ptx::mbar_init(tempty(s), 128); }
+    ptx::fence_mbar_init();
+    ptx::prefetch_tmap(&p.a_map);
+    ptx::prefetch_tmap(&p.b_map);
+  }
+  if (warp == 1) ptx::tmem_alloc<512>(ptx::smem_u32(tmem_slot));
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  if (warp >= 2) {   // all accumulator blocks start at zero: every MMA accumulates
+    const uint32_t t = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
+#pragma unroll 1
+    for (int c = 0; c < 512; c += 32) ptx::tmem_st_32x32_fill(t + c, 0u);
+    ptx::tmem_st_wait();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // ================= TMA producer =================
+      int a_i = 0; uint32_t a_ph = 0;
+      int b_i = 0; uint32_t b_ph = 0;
+      for (int u = blockIdx.x; u < total_units; u += gridDim.x) {
+        const RingUnit r = ring_decode(p, u);
+        for (int zg = r.z_begin; zg <= r.z_end; zg += p.S) {
+          for (int q = 0; q < p.q_chunks; ++q) {
+            auto load_slice = [&](int s) {
+              const int z = zg + s;
+              if (z > r.z_end || z < 0 || z >= p.in_d) return;
+              ptx::mbar_wait_backoff(aempty(a_i), a_ph ^ 1u);
+              ptx::mbar_arrive_expect_tx(afull(a_i), (uint32_t)p.slice_tx);
+              ptx::tma_load_5d(smem_a + (uint32_t)(a_i * p.slice_bytes), &p.a_map, afull(a_i), q * 64, r.w0 - p.pw,
+                               r.h0 - p.ph, z, r.n);
+              if (++a_i == p.na) { a_i = 0; a_ph ^= 1u; }
+            };
+            // consumer order: slice 0, first weight stage, remaining slices, remaining weight stages
+            load_slice(0);
+            bool rest_done = false;
+            for (int t = 0; t < ntaps_hw; ++t)
+              for (int part = 0; part < parts; ++part) {
+                const int nblk = min(STAGE_KD, p.kd - part * STAGE_KD);
+                ptx::mbar_wait_backoff(bempty(b_i), b_ph ^ 1u);
+                ptx::mbar_arrive_expect_tx(bfull(b_i), (uint32_t)(nblk * WBLK_BYTES));
+                const int row0 = ((((r.nt * p.q_chunks + q) * ntaps_hw + t) * p.kd) + part * STAGE_KD) * 64;
+                for (int j = 0; j < nblk; ++j)
+                  ptx::tma_load_2d(smem_b + (uint32_t)(b_i * p.stage_bytes + j * WBLK_BYTES), &p.b_map, bfull(b_i), 0,
+                                   row0 + j * 64);
+                if (++b_i == p.nb) { b_i = 0; b_ph ^= 1u; }
+                if (!rest_done) {
+                  for (int s = 1; s < p.S; ++s) load_slice(s);
+                  rest_done = true;
+                }
+              }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================= MMA issuer =================
+    // The whole warp runs this loop convergently (so addresses / descriptors stay in the uniform datapath and the
+    // tcgen05.mma operands need no per-instruction lane election loop); one elected lane issues.
+    const bool leader = ptx::elect_one_sync();
+    const uint32_t idesc_base = ptx::idesc_bf16(128, 0, 0, 0);
+    const uint32_t a_hi = (((uint32_t)(p.wb * 128) >> 4) & 0x3FFFu) | (1u << 14) | (2u << 29);   // SBO | version | SW128
+    const uint32_t b_hi = ((1024u >> 4) & 0x3FFFu) | (1u << 14) | (2u << 29);
+    const uint32_t lbo_lo = 1u << 16;
+    int a_i = 0; uint32_t a_ph = 0;
+    int b_i = 0; uint32_t b_ph = 0;
+    int g = 0, waited = -1;
+    for (int u = blockIdx.x; u < total_units; u += gridDim.x) {
+      const RingUnit r = ring_decode(p, u);
+      bool first = true;
+      for (int zg = r.z_begin; zg <= r.z_end; zg += p.S) {
+        // piece table of this group: which accumulator blocks each (slice, weight-stage part) feeds.  It is the same
+        // for every (kh, kw) tap and reduction chunk, so it is built once (lane 0) and replayed from smem.
+        __syncwarp();
+        int nvalid = 0;
+        if (lane == 0) {
+          int cnt[2] = {0, 0};
+          for (int s = 0; s < p.S; ++s) {
+            const int z = zg + s;
+            if (z > r.z_end || z < 0 || z >= p.in_d) continue;
+            // weight block i (kd = KD-1-i) of slice z feeds output plane d = z + pd - KD + 1 + i
+            const int dbase = z + p.pd - p.kd + 1;
+            for (int part = 0; part < parts; ++part) {
+              const int nblk = min(STAGE_KD, p.kd - part * STAGE_KD);
+              int i_lo = max(part * STAGE_KD, r.d0 - dbase);
+              const int i_hi = min(part * STAGE_KD + nblk, r.d0 + r.len - dbase);      // exclusive
+              while (i_lo < i_hi) {
+                const int blk = (dbase + i_lo - r.d0) & (RING_BLOCKS - 1);
+                const int c = min(i_hi - i_lo, RING_BLOCKS - blk);
+                ptab[part * PTAB_N + cnt[part]] = make_uint4(tmem_base + (uint32_t)(blk * 64), idesc_base | ((uint32_t)(c * 8) << 17),
+                                                              (uint32_t)nvalid, (uint32_t)((i_lo - part * STAGE_KD) * (WBLK_BYTES >> 4)));
+                ++cnt[part];
+                i_lo += c;
+              }
+            }
+            ++nvalid;
+          }
+          pcnt[0] = cnt[0]; pcnt[1] = cnt[1]; pcnt[2] = nvalid;
+        }
+        __syncwarp();
+        nvalid = pcnt[2];
+        const int need = first ? g - 1 : g - p.lag;
+        while (waited < need) { ++waited; ptx::mbar_wait(tempty(waited & 1), (uint32_t)((waited >> 1) & 1)); }
+        ptx::tc_fence_after();
+        for (int q = 0; q < p.q_chunks; ++q) {
+          uint32_t ready = 0;       // slices of this chunk whose TMA has been waited for
+          for (int t = 0; t < ntaps_hw; ++t) {
+            const int tkh = t / p.kw, tkw = t - tkh * p.kw;
+            const uint32_t a_shift = (uint32_t)((tkh * p.wb + tkw) * 8);        // rows * 128 B >> 4
+            for (int part = 0; part < parts; ++part) {
+              ptx::mbar_wait(bfull(b_i), b_ph);
+              ptx::tc_fence_after();
+              const uint32_t b_lo = (((smem_b + (uint32_t)(b_i * p.stage_bytes)) >> 4) & 0x3FFFu) | lbo_lo;
+              const int n = pcnt[part];
+              for (int j = 0; j < n; ++j) {
+                const uint4 e = ptab[part * PTAB_N + j];
+                int slot = a_i + (int)e.z; uint32_t sph = a_ph;
+                if (slot >= p.na) { slot -= p.na; sph ^= 1u; }
+                if (t == 0 && !((ready >> e.z) & 1u)) {
+                  ptx::mbar_wait(afull(slot), sph);
+                  ptx::tc_fence_after();
+                  ready |= 1u << e.z;
+                }
+                const uint32_t a_lo = ((((smem_a + (uint32_t)(slot * p.slice_bytes)) >> 4) + a_shift) & 0x3FFFu) | lbo_lo;
+                if (leader) {
+#pragma unroll
+                  for (int k = 0; k < 4; ++k)
+                    ptx::umma_bf16(e.x, ((uint64_t)a_hi << 32) | (uint64_t)(a_lo + 2 * k),
+                                   ((uint64_t)b_hi << 32) | (uint64_t)(b_lo + e.w + 2 * k), e.y, 1u);
+                }
+              }
+              if (leader) ptx::umma_commit(bempty(b_i));
+              if (++b_i == p.nb) { b_i = 0; b_ph ^= 1u; }
+            }
+          }
+          for (int j = 0; j < nvalid; ++j) {
+            if (leader) ptx::umma_commit(aempty(a_i));
+            if (++a_i == p.na) { a_i = 0; a_ph ^= 1u; }
+          }
+        }
+        if (leader) ptx::umma_commit(tfull(g & 1));
+        ++g;
+        first = false;
+      }
+    }
+    __syncwarp();
+  } else {
+    // ================= epilogue (warps 2..5) =================
+    const int quad = warp & 3;
+    const int row = quad * 32 + lane;
+    const int rh = row >> 3, rw = row & 7;
+    const uint32_t t_lane = tmem_base + ((uint32_t)(quad * 32) << 16);
+    const bool want_stats = p.stats_sum != nullptr;
+    float st_acc[4] = {0.f, 0.f, 0.f, 0.f};
+    int st_n = -1, st_nt = -1;
+    auto flush_stats = [&]() {
+      if (!want_stats || st_n < 0) return;
+      const int c = st_nt * 64 + 2 * lane;
+      float* ps = p.stats_sum + (size_t)st_n * p.cout_total + c;
+      float* pq = p.stats_sq + (size_t)st_n * p.cout_total + c;
+      atomicAdd(ps, st_acc[0]); atomicAdd(ps + 1, st_acc[1]);
+      atomicAdd(pq, st_acc[2]); atomicAdd(pq + 1, st_acc[3]);
+      st_acc[0] = st_acc[1] = st_acc[2] = st_acc[3] = 0.f;
+    };
+    int g = 0;
+    for (int u = blockIdx.x; u < total_units; u += gridDim.x) {
+      const RingUnit r = ring_decode(p, u);
+      if (r.n != st_n || r.nt != st_nt) { flush_stats(); st_n = r.n; st_nt = r.nt; }
+      const int oh = r.h0 + rh, ow = r.w0 + rw;
+      const bool valid = oh < p.out_h && ow < p.out_w;
+      float bias_r[64];
+#pragma unroll
+      for (int c = 0; c < 64; ++c) bias_r[c] = 0.f;
+      if (p.bias) {
+#pragma unroll
+        for (int c = 0; c < 64; c += 4) {
+          const float4 b4 = *reinterpret_cast<const float4*>(p.bias + r.nt * 64 + c);
+          bias_r[c] = b4.x; bias_r[c + 1] = b4.y; bias_r[c + 2] = b4.z; bias_r[c + 3] = b4.w;
+        }
+      }
+      __nv_bfloat16* ybase = p.y + (size_t)r.n * p.ys_n + (size_t)oh * p.ys_h + (size_t)ow * p.ys_w + r.nt * 64;
+      for (int zg = r.z_begin; zg <= r.z_end; zg += p.S) {
+        ptx::mbar_wait_backoff(tfull(g & 1), (uint32_t)((g >> 1) & 1));
+        ptx::tc_fence_after();
+        // planes whose last contributing slice is in this group: d = z + pd - KD + 1
+        const int d_first = max(r.d0, zg + p.pd - p.kd + 1);
+        const int d_last = min(r.d0 + r.len - 1, min(zg + p.S - 1, r.z_end) + p.pd - p.kd + 1);
+        if (d_last < d_first) {
+          ptx::tc_fence_before();
+          ptx::mbar_arrive(tempty(g & 1));
+        }
+        for (int d = d_first; d <= d_last; ++d) {
+          const uint32_t taddr = t_lane + (uint32_t)(((d - r.d0) & (RING_BLOCKS - 1)) * 64);
+          uint32_t v[64];
+          ptx::tmem_ld_32x32(taddr, v);
+          ptx::tmem_ld_32x32(taddr + 32, v + 32);
+          ptx::tmem_ld_wait();
+          ptx::tmem_st_32x32_fill(taddr, 0u);
+          ptx::tmem_st_32x32_fill(taddr + 32, 0u);
+          if (d == d_last) {      // accumulators drained and re-zeroed: hand the blocks back before the arithmetic
+            ptx::tmem_st_wait();
+            ptx::tc_fence_before();
+            ptx::mbar_arrive(tempty(g & 1));
+          }
+          uint32_t pk[32];
+#pragma unroll
+          for (int c = 0; c < 64; c += 2) {
+            float f0 = act_apply(__uint_as_float(v[c]) + bias_r[c], p.act, p.slope);
+            float f1 = act_apply(__uint_as_float(v[c + 1]) + bias_r[c + 1], p.act, p.slope);
+            if (!valid) { f0 = 0.f; f1 = 0.f; }
+            __nv_bfloat162 h2 = __floats2bfloat162_rn(f0, f1);
+            pk[c >> 1] = *reinterpret_cast<uint32_t*>(&h2);
+          }
+          if (valid) {
+            uint4* dst = reinterpret_cast<uint4*>(ybase + (size_t)d * p.ys_d);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) dst[j] = make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+          }
+          if (want_stats) {
+            // transpose-reduce over the warp's 32 rows: after 5 halving steps lane l holds channels 2l, 2l+1
+#pragma unroll
+            for (int pass = 0; pass < 2; ++pass) {
+              float w[64];
+#pragma unroll
+              for (int c = 0; c < 64; c += 2) {
+                const float2 f = __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&pk[c >> 1]));
+                w[c] = pass ? f.x * f.x : f.x; w[c + 1] = pass ? f.y * f.y : f.y;
+              }
+#pragma unroll
+              for (int m = 16, half = 32; m >= 1; m >>= 1, half >>= 1) {
+                const bool up = (lane & m) != 0;
+#pragma unroll
+                for (int i = 0; i < half; ++i) {
+                  const float mine = up ? w[half + i] : w[i];
+                  const float other = up ? w[i] : w[half + i];
+                  w[i] = mine + __shfl_xor_sync(0xffffffffu, other, m);
+                }
+              }
+              st_acc[2 * pass] += w[0]; st_acc[2 * pass + 1] += w[1];
+            }
+          }
+        }
+        ++g;
+      }
+    }
+    flush_stats();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc<512>(tmem_base);
+  }
+}
+
+}  // namespace rg
+
+// =================================================================================================
+// Host side
+// =================================================================================================
+namespace rg {
+
+typedef CUresult (*RingEncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                 const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                 CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static RingEncodeFn ring_encode_fn() {
+  static RingEncodeFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = (RingEncodeFn)p;
+  }
+  return fn;
+}
+
+static int ring_num_sms() {
+  static int n = 0;
+  if (!n) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    if (n <= 0) n = 148;
+  }
+  return n;
+}
+
+constexpr int RING_SMEM_LIMIT = 227 * 1024;
+
+struct RingGeom {
+  int kc, rows;                 // reduction / produced channels
+  int in_ext[3], out_ext[3];    // d,h,w of the tensor read / written by this mode
+  int pad[3];
+  const int64_t* in_str; const int64_t* out_str;
+  RingParams p;
+  int smem_bytes;
+};
+
+// Fills everything except tensor maps and pointers; returns RG_OK / RG_E_UNSUPPORTED.
+static int ring_geometry(const rg_igemm_desc* d, RingGeom* g) {
+  RG_UNSUPPORTED(d->mode != 0 && d->mode != 1, "ring conv: fprop / dgrad only");
+  for (int i = 0; i < 3; ++i) {
+    RG_UNSUPPORTED(d->stride[i] != 1, "ring conv: stride must be 1");
+    RG_UNSUPPORTED(d->kernel[i] < 1 || d->kernel[i] > 8, "ring conv: kernel extent must be 1..8");
+    RG_UNSUPPORTED(d->pad[i] < 0 || d->pad[i] > d->kernel[i] - 1, "ring conv: padding must be within the kernel");
+    RG_UNSUPPORTED(d->out_dhw[i] != d->in_dhw[i] + 2 * d->pad[i] - d->kernel[i] + 1 || d->out_dhw[i] < 1,
+                   "ring conv: extents inconsistent with geometry");
+  }
+  g->kc = d->mode == 0 ? d->cin : d->cout;
+  g->rows = d->mode == 0 ? d->cout : d->cin;
+  RG_UNSUPPORTED(g->kc % 64 != 0 || g->rows % 64 != 0, "ring conv: channel counts must be multiples of 64");
+  RG_UNSUPPORTED(d->x_strides[3] % 8 != 0 || d->y_strides[3] % 8 != 0, "ring conv: voxel stride must be a multiple of 8");
+  for (int i = 0; i < 3; ++i) {
+    g->in_ext[i] = d->mode == 0 ? d->in_dhw[i] : d->out_dhw[i];
+    g->out_ext[i] = d->mode == 0 ? d->out_dhw[i] : d->in_dhw[i];
+    g->pad[i] = d->mode == 0 ? d->pad[i] : d->kernel[i] - 1 - d->pad[i];
+  }
+  g->in_str = d->mode == 0 ? d->x_strides : d->y_strides;
+  g->out_str = d->mode == 0 ? d->y_strides : d->x_strides;
+  RingParams& p = g->p;
+  memset(&p, 0, sizeof(p));
+  p.kd = d->kernel[0]; p.kh = d->kernel[1]; p.kw = d->kernel[2];
+  p.pd = g->pad[0]; p.ph = g->pad[1]; p.pw = g->pad[2];
+  p.q_chunks = g->kc / 64; p.n_tiles_n = g->rows / 64;
+  p.wb = RING_TW + p.kw - 1;
+  const int hb = RING_TH + p.kh - 1;
+  RG_UNSUPPORTED(p.wb > 256 || hb > 256, "ring conv: halo box too large");
+  p.slice_tx = hb * p.wb * 128;
+  p.slice_bytes = (p.slice_tx + 1023) & ~1023;
+  p.stage_bytes = (p.kd < STAGE_KD ? p.kd : STAGE_KD) * WBLK_BYTES;
+  // slices per weight stage: prefer a configuration with one group of drain slack (2S + KD - 1 <= 8)
+  int s2 = (RING_BLOCKS - (p.kd - 1)) / 2;
+  if (s2 >= 2) { p.S = s2; p.lag = 2; } else { p.S = RING_BLOCKS - (p.kd - 1); p.lag = 1; }
+  if (p.S > 4) p.S = 4;
+  for (;;) {
+    p.nb = 3;
+    const int avail = RING_SMEM_LIMIT - 1024 - RING_TAIL_BYTES - p.nb * p.stage_bytes;
+    int na = avail / p.slice_bytes;
+    if (na > 2 * p.S) na = 2 * p.S;
+    if (na > MAX_NA) na = MAX_NA;
+    if (na >= p.S + 1 || (na >= p.S && p.S == 1)) { p.na = na; break; }
+    RG_UNSUPPORTED(p.S == 1, "ring conv: slice does not fit shared memory");
+    --p.S;
+    if (2 * p.S + p.kd - 1 > RING_BLOCKS) p.lag = 1;
+  }
+  g->smem_bytes = 1024 + p.na * p.slice_bytes + p.nb * p.stage_bytes + RING_TAIL_BYTES;
+  p.tiles_h = (g->out_ext[1] + RING_TH - 1) / RING_TH;
+  p.tiles_w = (g->out_ext[2] + RING_TW - 1) / RING_TW;
+  p.batch = d->n;
+  p.in_d = g->in_ext[0];
+  p.out_d = g->out_ext[0]; p.out_h = g->out_ext[1]; p.out_w = g->out_ext[2];
+  // depth segment length: balance wave quantisation against the (KD-1) extra slices every segment re-reads
+  const long long cols = (long long)d->n * p.tiles_h * p.tiles_w * p.n_tiles_n;
+  const int sms = ring_num_sms();
+  double best = 1e300; int best_len = p.out_d;
+  for (int segs = 1; segs <= p.out_d; ++segs) {
+    const int len = (p.out_d + segs - 1) / segs;
+    if ((p.out_d + len - 1) / len != segs) continue;
+    if (len < 4 && segs > 1) break;
+    const long long units = cols * segs;
+    const double waves = (double)((units + sms - 1) / sms);
+    const double cost = waves * (len + 0.35 * (p.kd - 1) + 1.0);
+    if (cost < best) { best = cost; best_len = len; }
+  }
+  p.seg_len = best_len;
+  p.segs = (p.out_d + best_len - 1) / best_len;
+  p.cout_total = g->rows;
+  p.act = d->act; p.slope = d->slope;
+  p.ys_n = g->out_str[0]; p.ys_d = g->out_str[1]; p.ys_h = g->out_str[2]; p.ys_w = g->out_str[3];
+  return RG_OK;
+}
+
+// fp32 [Cout][Cin][kd][kh][kw] -> bf16 [nt][q][kh][kw][i][64 produced][64 reduction], kd = KD-1-i (see kernel header).
+__global__ void ring_pack_kernel(const float* __restrict__ w, int cout, int cin, int kd, int kh, int kw, int mode,
+                                 __nv_bfloat16* __restrict__ out) {
+  const int rows = mode == 0 ? cout : cin, kc = mode == 0 ? cin : cout;
+  const int Q = kc / 64;
+  const long long total = (long long)cout * cin * kd * kh * kw;
+  for (long long o = blockIdx.x * (long long)blockDim.x + threadIdx.x; o < total; o += (long long)gridDim.x * blockDim.x) {
+    long long r = o;
+    const int ck = (int)(r % 64); r /= 64;
+    const int cn = (int)(r % 64); r /= 64;
+    const int i = (int)(r % kd); r /= kd;
+    const int b = (int)(r % kw); r /= kw;
+    const int a = (int)(r % kh); r /= kh;
+    const int q = (int)(r % Q); const int nt = (int)(r / Q);
+    int co, ci, td, th, tw;
+    if (mode == 0) { co = nt * 64 + cn; ci = q * 64 + ck; td = kd - 1 - i; th = a; tw = b; }
+    else { ci = nt * 64 + cn; co = q * 64 + ck; td = i; th = kh - 1 - a; tw = kw - 1 - b; }
+    (void)rows;
+    out[o] = __float2bfloat16_rn(w[((((long long)co * cin + ci) * kd + td) * kh + th) * kw + tw]);
+  }
+}
+
+}  // namespace rg
+
+using namespace rg;
+
+extern "C" {
+
+int rg_ring_supported(const rg_igemm_desc* d) {
+  if (!d) return 0;
+  RingGeom g;
+  return ring_geometry(d, &g) == RG_OK ? 1 : 0;
+}
+
+int rg_ring_pack_weights(const float* w, int cout, int cin, const int* kernel, int mode, void* out_bf16, void* stream) {
+  RG_CHECK_ARG(w && out_bf16 && kernel && cout > 0 && cin > 0 && (mode == 0 || mode == 1), "rg_ring_pack_weights: bad argument");
+  RG_UNSUPPORTED(cout % 64 != 0 || cin % 64 != 0, "rg_ring_pack_weights: channel counts must be multiples of 64");
+  const long long total = (long long)cout * cin * kernel[0] * kernel[1] * kernel[2];
+  ring_pack_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(w, cout, cin, kernel[0], kernel[1], kernel[2], mode,
+                                                                          (__nv_bfloat16*)out_bf16);
+  RG_LAUNCH_CHECK("rg_ring_pack_weights");
+  return RG_OK;
+}
+
+int rg_ring_run(const rg_igemm_desc* d, const void* in, const void* w_ring, const float* bias, void* out, float* stats_sum,
+                float* stats_sqsum, void* stream) {
+  RG_CHECK_ARG(d && in && w_ring && out, "rg_ring_run: null argument");
+  RG_CHECK_ARG((stats_sum == nullptr) == (stats_sqsum == nullptr), "rg_ring_run: stats pointers must come together");
+  RingGeom g;
+  int rc = ring_geometry(d, &g);
+  if (rc) return rc;
+  RingEncodeFn enc = ring_encode_fn();
+  if (!enc) { set_error("cuTensorMapEncodeTiled unavailable"); return RG_E_CUDA; }
+  RingParams& p = g.p;
+  RG_CHECK_ARG(((uintptr_t)in & 15) == 0 && ((uintptr_t)out & 15) == 0, "rg_ring_run: tensors must be 16-byte aligned");
+  for (int i = 0; i < 4; ++i)
+    RG_UNSUPPORTED((g.in_str[i] * 2) % 16 != 0 || (g.out_str[i] * 2) % 16 != 0, "rg_ring_run: strides must be multiples of 16 bytes");
+  {
+    cuuint64_t dims[5] = {(cuuint64_t)g.kc, (cuuint64_t)g.in_ext[2], (cuuint64_t)g.in_ext[1], (cuuint64_t)g.in_ext[0], (cuuint64_t)d->n};
+    cuuint64_t gs[4] = {(cuuint64_t)(g.in_str[3] * 2), (cuuint64_t)(g.in_str[2] * 2), (cuuint64_t)(g.in_str[1] * 2), (cuuint64_t)(g.in_str[0] * 2)};
+    cuuint32_t bx[5] = {64, (cuuint32_t)p.wb, (cuuint32_t)(RING_TH + p.kh - 1), 1, 1};
+    cuuint32_t es[5] = {1, 1, 1, 1, 1};
+    CUresult r = enc(&p.a_map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, (void*)in, dims, gs, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { set_error("ring conv: cuTensorMapEncodeTiled (activation) failed: %d", (int)r); return RG_E_CUDA; }
+  }
+  {
+    const long long rows = (long long)p.n_tiles_n * p.q_chunks * p.kh * p.kw * p.kd * 64;
+    cuuint64_t dims[2] = {64, (cuuint64_t)rows};
+    cuuint64_t gs[1] = {128};
+    cuuint32_t bx[2] = {64, 64};
+    cuuint32_t es[2] = {1, 1};
+    CUresult r = enc(&p.b_map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, (void*)w_ring, dims, gs, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { set_error("ring conv: cuTensorMapEncodeTiled (weights) failed: %d", (int)r); return RG_E_CUDA; }
+  }
+  p.y = (__nv_bfloat16*)out;
+  p.bias = bias; p.stats_sum = stats_sum; p.stats_sq = stats_sqsum;
+  static int smem_set = 0;
+  if (smem_set < g.smem_bytes) {
+    cudaError_t e = cudaFuncSetAttribute(ring_conv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, RING_SMEM_LIMIT);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(ring_conv)");
+    smem_set = RING_SMEM_LIMIT;
+  }
+  const long long units = (long long)p.batch * p.segs * p.tiles_h * p.tiles_w * p.n_tiles_n;
+  const int grid = (int)(units < ring_num_sms() ? units : ring_num_sms());
+  ring_conv_kernel<<<grid, RING_THREADS, g.smem_bytes, (cudaStream_t)stream>>>(p);
+  RG_LAUNCH_CHECK("rg_ring_run");
+  return RG_OK;
+}
+
+/* Introspection for tests / DESIGN.md: the configuration the host would pick for this layer. */
+int rg_ring_config(const rg_igemm_desc* d, int* out8) {
+  RG_CHECK_ARG(d && out8, "rg_ring_config: null argument");
+  RingGeom g;
+  int rc = ring_geometry(d, &g);
+  if (rc) return rc;
+  out8[0] = g.p.S; out8[1] = g.p.lag; out8[2] = g.p.na; out8[3] = g.p.nb; out8[4] = g.p.seg_len; out8[5] = g.p.segs;
+  out8[6] = g.smem_bytes; out8[7] = g.p.slice_bytes;
+  return RG_OK;
+}
+
+}  // extern "C"

@@ -103,3 +103,25 @@ def test_precision_switch():
         assert rb.get_precision() == "fp32"
     with pytest.raises(ValueError):
         rb.set_precision("fp16")
+
+
+def test_ring_config_reported_by_the_library():
+    """The host-side configuration logic (slices per weight stage, drain lag, smem budget) through the C ABI."""
+    import ctypes as C
+    from raygun_b200 import _C
+    d = _C.IgemmDesc()
+    d.mode, d.n, d.cin, d.cout = 0, 2, 64, 64
+    d.in_dhw[:] = [134, 134, 134]
+    d.out_dhw[:] = [128, 128, 128]
+    d.kernel[:] = [7, 7, 7]
+    d.stride[:] = [1, 1, 1]
+    d.pad[:] = [0, 0, 0]
+    d.x_strides[:] = [134 ** 3 * 64, 134 * 134 * 64, 134 * 64, 64]
+    d.y_strides[:] = [128 ** 3 * 64, 128 * 128 * 64, 128 * 64, 64]
+    out = (C.c_int * 8)()
+    _C.check(_C.lib().rg_ring_config(C.byref(d), out), "rg_ring_config")
+    S, lag, na, nb, seg_len, segs, smem, pitch = list(out)
+    assert S == 2 and lag == 1 and na >= 3 and nb == 3
+    assert S + 7 - 1 <= 8 and smem <= 227 * 1024 and pitch % 1024 == 0 and seg_len * segs >= 128
+    d.stride[:] = [2, 2, 2]
+    assert _C.lib().rg_ring_supported(C.byref(d)) == 0
