@@ -16,7 +16,8 @@
 //     (d-d0) mod 8.  S consecutive input slices share every weight stage (S + KD - 1 <= 8), which divides the weight
 //     traffic by S.  When a plane has received its last slice, the epilogue warps drain it (bias, activation, bf16,
 //     Instance/BatchNorm sum / sum-of-squares), re-zero the block and hand it back.
-// Warp roles: warp 0 = TMA producer, warp 1 = MMA issuer + TMEM owner, warps 2-5 = epilogue.
+// Warp roles: warp 0 = TMA producer, warp 1 = MMA issuer + TMEM owner, warps 2-9 = epilogue (two per TMEM lane
+// quadrant, 32 columns each).
 #include <cuda.h>
 #include <cuda_bf16.h>
 
@@ -25,7 +26,7 @@
 
 namespace rg {
 
-constexpr int RING_THREADS = 192;
+constexpr int RING_THREADS = 320;       // warp 0 producer, warp 1 MMA issuer, warps 2-9 epilogue
 constexpr int RING_BLOCKS = 8;            // accumulator blocks of 64 TMEM columns
 constexpr int WBLK_BYTES = 64 * 128;      // weights of one (tap, kd): 64 produced channels x 64 reduction channels bf16
 constexpr int STAGE_KD = 4;               // kd blocks per weight stage (<= 256 MMA columns)
@@ -101,7 +102,7 @@ __global__ void __launch_bounds__(RING_THREADS, 1) ring_conv_kernel(const __grid
   if (warp == 0 && lane == 0) {
     for (int s = 0; s < p.na; ++s) { ptx::mbar_init(afull(s), 1); ptx::mbar_init(aempty(s), 1); }
     for (int s = 0; s < p.nb; ++s) { ptx::mbar_init(bfull(s), 1); ptx::mbar_init(bempty(s), 1); }
-    for (int s = 0; s < 2; ++s) { ptx::mbar_init(tfull(s), 1); ptx::mbar_init(tempty(s), 128); }
+    for (int s = 0; s < 2; ++s) { ptx::mbar_init(tfull(s), 1); ptx::mbar_init(tempty(s), 256); }
     ptx::fence_mbar_init();
     ptx::prefetch_tmap(&p.a_map);
     ptx::prefetch_tmap(&p.b_map);
@@ -111,7 +112,7 @@ __global__ void __launch_bounds__(RING_THREADS, 1) ring_conv_kernel(const __grid
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  if (warp >= 2) {   // all accumulator blocks start at zero: every MMA accumulates
+  if (warp >= 2 && warp < 6) {   // all accumulator blocks start at zero: every MMA accumulates
     const uint32_t t = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
 #pragma unroll 1
     for (int c = 0; c < 512; c += 32) ptx::tmem_st_32x32_fill(t + c, 0u);
@@ -253,22 +254,21 @@ __global__ void __launch_bounds__(RING_THREADS, 1) ring_conv_kernel(const __grid
     }
     __syncwarp();
   } else {
-    // ================= epilogue (warps 2..5) =================
+    // ================= epilogue (warps 2..9): warp pair (quad, half) owns TMEM lanes 32*quad.. and 32 of the 64 columns
     const int quad = warp & 3;
+    const int half = (warp - 2) >> 2;
     const int row = quad * 32 + lane;
     const int rh = row >> 3, rw = row & 7;
-    const uint32_t t_lane = tmem_base + ((uint32_t)(quad * 32) << 16);
+    const uint32_t t_lane = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(half * 32);
     const bool want_stats = p.stats_sum != nullptr;
-    float st_acc[4] = {0.f, 0.f, 0.f, 0.f};
+    float st_sum = 0.f, st_sq = 0.f;          // lane l: channel half*32 + l of the current (n, channel tile)
     int st_n = -1, st_nt = -1;
     auto flush_stats = [&]() {
       if (!want_stats || st_n < 0) return;
-      const int c = st_nt * 64 + 2 * lane;
-      float* ps = p.stats_sum + (size_t)st_n * p.cout_total + c;
-      float* pq = p.stats_sq + (size_t)st_n * p.cout_total + c;
-      atomicAdd(ps, st_acc[0]); atomicAdd(ps + 1, st_acc[1]);
-      atomicAdd(pq, st_acc[2]); atomicAdd(pq + 1, st_acc[3]);
-      st_acc[0] = st_acc[1] = st_acc[2] = st_acc[3] = 0.f;
+      const size_t c = (size_t)st_n * p.cout_total + st_nt * 64 + half * 32 + lane;
+      atomicAdd(p.stats_sum + c, st_sum);
+      atomicAdd(p.stats_sq + c, st_sq);
+      st_sum = st_sq = 0.f;
     };
     int g = 0;
     for (int u = blockIdx.x; u < total_units; u += gridDim.x) {
@@ -276,17 +276,17 @@ __global__ void __launch_bounds__(RING_THREADS, 1) ring_conv_kernel(const __grid
       if (r.n != st_n || r.nt != st_nt) { flush_stats(); st_n = r.n; st_nt = r.nt; }
       const int oh = r.h0 + rh, ow = r.w0 + rw;
       const bool valid = oh < p.out_h && ow < p.out_w;
-      float bias_r[64];
+      float bias_r[32];
 #pragma unroll
-      for (int c = 0; c < 64; ++c) bias_r[c] = 0.f;
+      for (int c = 0; c < 32; ++c) bias_r[c] = 0.f;
       if (p.bias) {
 #pragma unroll
-        for (int c = 0; c < 64; c += 4) {
-          const float4 b4 = *reinterpret_cast<const float4*>(p.bias + r.nt * 64 + c);
+        for (int c = 0; c < 32; c += 4) {
+          const float4 b4 = *reinterpret_cast<const float4*>(p.bias + r.nt * 64 + half * 32 + c);
           bias_r[c] = b4.x; bias_r[c + 1] = b4.y; bias_r[c + 2] = b4.z; bias_r[c + 3] = b4.w;
         }
       }
-      __nv_bfloat16* ybase = p.y + (size_t)r.n * p.ys_n + (size_t)oh * p.ys_h + (size_t)ow * p.ys_w + r.nt * 64;
+      __nv_bfloat16* ybase = p.y + (size_t)r.n * p.ys_n + (size_t)oh * p.ys_h + (size_t)ow * p.ys_w + r.nt * 64 + half * 32;
       for (int zg = r.z_begin; zg <= r.z_end; zg += p.S) {
         ptx::mbar_wait_backoff(tfull(g & 1), (uint32_t)((g >> 1) & 1));
         ptx::tc_fence_after();
@@ -299,52 +299,60 @@ __global__ void __launch_bounds__(RING_THREADS, 1) ring_conv_kernel(const __grid
         }
         for (int d = d_first; d <= d_last; ++d) {
           const uint32_t taddr = t_lane + (uint32_t)(((d - r.d0) & (RING_BLOCKS - 1)) * 64);
-          uint32_t v[64];
+          uint32_t v[32];
           ptx::tmem_ld_32x32(taddr, v);
-          ptx::tmem_ld_32x32(taddr + 32, v + 32);
           ptx::tmem_ld_wait();
           ptx::tmem_st_32x32_fill(taddr, 0u);
-          ptx::tmem_st_32x32_fill(taddr + 32, 0u);
           if (d == d_last) {      // accumulators drained and re-zeroed: hand the blocks back before the arithmetic
             ptx::tmem_st_wait();
             ptx::tc_fence_before();
             ptx::mbar_arrive(tempty(g & 1));
           }
-          uint32_t pk[32];
+          float f[32];
 #pragma unroll
-          for (int c = 0; c < 64; c += 2) {
-            float f0 = act_apply(__uint_as_float(v[c]) + bias_r[c], p.act, p.slope);
-            float f1 = act_apply(__uint_as_float(v[c + 1]) + bias_r[c + 1], p.act, p.slope);
-            if (!valid) { f0 = 0.f; f1 = 0.f; }
-            __nv_bfloat162 h2 = __floats2bfloat162_rn(f0, f1);
+          for (int c = 0; c < 32; ++c) f[c] = __uint_as_float(v[c]) + bias_r[c];
+          if (p.act == RG_ACT_RELU) {
+#pragma unroll
+            for (int c = 0; c < 32; ++c) f[c] = fmaxf(f[c], 0.f);
+          } else if (p.act == RG_ACT_LEAKY) {
+#pragma unroll
+            for (int c = 0; c < 32; ++c) f[c] = f[c] > 0.f ? f[c] : f[c] * p.slope;
+          } else if (p.act != RG_ACT_NONE) {
+#pragma unroll
+            for (int c = 0; c < 32; ++c) f[c] = act_apply(f[c], p.act, p.slope);
+          }
+          uint32_t pk[16];
+#pragma unroll
+          for (int c = 0; c < 32; c += 2) {
+            __nv_bfloat162 h2 = __floats2bfloat162_rn(valid ? f[c] : 0.f, valid ? f[c + 1] : 0.f);
             pk[c >> 1] = *reinterpret_cast<uint32_t*>(&h2);
           }
           if (valid) {
             uint4* dst = reinterpret_cast<uint4*>(ybase + (size_t)d * p.ys_d);
 #pragma unroll
-            for (int j = 0; j < 8; ++j) dst[j] = make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+            for (int j = 0; j < 4; ++j) dst[j] = make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
           }
           if (want_stats) {
-            // transpose-reduce over the warp's 32 rows: after 5 halving steps lane l holds channels 2l, 2l+1
+            // transpose-reduce over the warp's 32 rows: after 5 halving steps lane l holds channel l of this half
 #pragma unroll
             for (int pass = 0; pass < 2; ++pass) {
-              float w[64];
+              float w[32];
 #pragma unroll
-              for (int c = 0; c < 64; c += 2) {
-                const float2 f = __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&pk[c >> 1]));
-                w[c] = pass ? f.x * f.x : f.x; w[c + 1] = pass ? f.y * f.y : f.y;
+              for (int c = 0; c < 32; c += 2) {
+                const float2 x = __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&pk[c >> 1]));
+                w[c] = pass ? x.x * x.x : x.x; w[c + 1] = pass ? x.y * x.y : x.y;
               }
 #pragma unroll
-              for (int m = 16, half = 32; m >= 1; m >>= 1, half >>= 1) {
+              for (int m = 16, hf = 16; m >= 1; m >>= 1, hf >>= 1) {
                 const bool up = (lane & m) != 0;
 #pragma unroll
-                for (int i = 0; i < half; ++i) {
-                  const float mine = up ? w[half + i] : w[i];
-                  const float other = up ? w[i] : w[half + i];
+                for (int i = 0; i < hf; ++i) {
+                  const float mine = up ? w[hf + i] : w[i];
+                  const float other = up ? w[i] : w[hf + i];
                   w[i] = mine + __shfl_xor_sync(0xffffffffu, other, m);
                 }
               }
-              st_acc[2 * pass] += w[0]; st_acc[2 * pass + 1] += w[1];
+              if (pass) st_sq += w[0]; else st_sum += w[0];
             }
           }
         }
