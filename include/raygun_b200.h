@@ -122,6 +122,15 @@ int rg_ring_pack_weights(const float* w, int cout, int cin, const int* kernel3, 
 int rg_ring_run(const rg_igemm_desc* desc, const void* in, const void* w_ring, const float* bias, void* out,
                 float* stats_sum, float* stats_sqsum, void* stream);
 
+/* ---- halo-resident weight gradient (stride 1; halo_wgrad_sm100.cu) ------------------------------------------
+ * Same role as rg_igemm_wgrad (autograd of Conv3d, reference: torch.nn.Conv3d call sites UNet.py:69-87,
+ * ResNet.py:262-327) for stride-1 layers: one X plane with its (kh,kw) halo per 128-voxel chunk serves every tap
+ * of a pass through row-shifted UMMA descriptors.  desc->mode must be 2.  dw fp32 [Cout,Cin,kD,kH,kW] is
+ * ACCUMULATED into (caller zeroes); workspace = rg_halo_wgrad_workspace_bytes(desc) bytes of device scratch.   */
+int rg_halo_wgrad_supported(const rg_igemm_desc* desc);
+size_t rg_halo_wgrad_workspace_bytes(const rg_igemm_desc* desc);
+int rg_halo_wgrad(const rg_igemm_desc* desc, const void* x, const void* dy, float* dw, void* workspace, void* stream);
+
 /* ---- 1x1x1 convolutions onto <= 4 channels (BaseSystem.py:209-224: Conv3d(ngf, output_nc, 1) + Tanh) -------
  * HBM-bound streaming kernels over a bf16 NDHWC x (Cin/8 a power of two <= 32); w fp32 [Cout][Cin].
  * fprop fuses bias + activation; wgrad accumulates into dw / dbias (caller zeroes).                     */

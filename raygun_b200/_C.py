@@ -27,6 +27,7 @@ SYMBOLS = [
     "rg_conv3d_direct_fprop", "rg_conv3d_direct_dgrad", "rg_conv3d_direct_wgrad",
     "rg_plan_create", "rg_plan_destroy", "rg_plan_workspace_bytes", "rg_pack_weights",
     "rg_igemm_run", "rg_igemm_wgrad", "rg_ring_supported", "rg_ring_config", "rg_ring_pack_weights", "rg_ring_run",
+    "rg_halo_wgrad_supported", "rg_halo_wgrad_workspace_bytes", "rg_halo_wgrad",
     "rg_pw_conv_fprop", "rg_pw_conv_dgrad", "rg_pw_conv_wgrad",
     "rg_copy5", "rg_im2col_hw", "rg_pad3d_fwd", "rg_pad3d_bwd",
     "rg_norm_stats", "rg_norm_finalize", "rg_norm_apply", "rg_norm_bwd",
@@ -78,6 +79,7 @@ def lib():
                 l = C.CDLL(LIB_PATH)
                 l.rg_last_error.restype = C.c_char_p
                 l.rg_plan_workspace_bytes.restype = C.c_size_t
+                l.rg_halo_wgrad_workspace_bytes.restype = C.c_size_t
                 _lib = l
     return _lib
 

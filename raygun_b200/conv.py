@@ -134,7 +134,7 @@ import os
 
 _ring_descs: "dict[tuple, IgemmDesc | None]" = {}
 _ring_packs: "dict[tuple, tuple]" = {}
-RING_MAX_PRODUCED = int(os.environ.get("RAYGUN_B200_RING_MAX_PRODUCED", "64"))   # 0 disables the ring kernel
+RING_MAX_PRODUCED = int(os.environ.get("RAYGUN_B200_RING_MAX_PRODUCED", "192"))   # 0 disables the ring kernel
 
 
 def _ring_desc(mode, n, cin, cout, in_dhw, out_dhw, kernel, stride, pad, xs, ys, act, slope):
@@ -158,6 +158,31 @@ def _ring_desc(mode, n, cin, cout, in_dhw, out_dhw, kernel, stride, pad, xs, ys,
     ok = lib().rg_ring_supported(C.byref(d)) == 1
     _ring_descs[key] = d if ok else None
     return _ring_descs[key]
+
+
+_halo_descs: "dict[tuple, IgemmDesc | None]" = {}
+HALO_WGRAD = os.environ.get("RAYGUN_B200_HALO_WGRAD", "1") != "0"
+
+
+def _halo_wgrad_desc(n, cin, cout, in_dhw, out_dhw, kernel, stride, pad, xs, ys):
+    """IgemmDesc (mode 2) when the halo-resident weight-gradient kernel should run this layer, else None."""
+    if not HALO_WGRAD or tuple(stride) != (1, 1, 1) or cin % 64 or cout % 64:
+        return None
+    key = (n, cin, cout, tuple(in_dhw), tuple(out_dhw), tuple(kernel), tuple(pad), tuple(xs), tuple(ys))
+    if key in _halo_descs:
+        return _halo_descs[key]
+    d = IgemmDesc()
+    d.mode, d.n, d.cin, d.cout = 2, n, cin, cout
+    d.in_dhw[:] = list(in_dhw)
+    d.out_dhw[:] = list(out_dhw)
+    d.kernel[:] = list(kernel)
+    d.stride[:] = [1, 1, 1]
+    d.pad[:] = list(pad)
+    d.x_strides[:] = list(xs)
+    d.y_strides[:] = list(ys)
+    ok = lib().rg_halo_wgrad_supported(C.byref(d)) == 1
+    _halo_descs[key] = d if ok else None
+    return _halo_descs[key]
 
 
 def ring_packed_weights(w: torch.Tensor, mode: int):
@@ -327,6 +352,19 @@ def conv_wgrad(x, dy, w_shape, stride, pad, groups=1, want_bias=False):
     if _igemm_ok(cin_g, cout, kernel, stride, groups) and groups == 1:
         xb, dyb = K.convert(x, torch.bfloat16), K.convert(dy, torch.bfloat16)
         n = x.shape[0]
+        hd = _halo_wgrad_desc(n, cin_g, cout, tuple(x.shape[2:]), tuple(dy.shape[2:]), kernel, stride, pad,
+                              _sp_strides(xb), _sp_strides(dyb))
+        if hd is not None:
+            dw = torch.zeros(tuple(w_shape), dtype=torch.float32, device=x.device)
+            ws = torch.empty(dw.numel(), dtype=torch.float32, device=x.device)
+            with _Timed("wgrad", 2.0 * dyb.numel() * cin_g * kernel[0] * kernel[1] * kernel[2], x.device):
+                check(lib().rg_halo_wgrad(C.byref(hd), ptr(xb), ptr(dyb), ptr(dw), ptr(ws), stream_ptr(x.device)),
+                      "rg_halo_wgrad")
+            count_launch(2)
+            stats["igemm"] += 1
+            stats["halo_wgrad"] = stats.get("halo_wgrad", 0) + 1
+            db = K.norm_stats(dyb, _C.NORM_BATCH)[0] if want_bias else None
+            return dw, db
         plan = _get_plan(2, n, cin_g, cout, tuple(x.shape[2:]), tuple(dy.shape[2:]), kernel, stride, pad,
                          _sp_strides(xb), _sp_strides(dyb), ACT_NONE, 0.0)
         if plan is not None:

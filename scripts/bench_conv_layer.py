@@ -37,6 +37,8 @@ def timeit(fn, iters=5, warm=2):
 
 def main():
     which = sys.argv[1] if len(sys.argv) > 1 else "all"
+    if "--no-halo" in sys.argv:
+        CV.HALO_WGRAD = False
     if "--ring-max" in sys.argv:
         CV.RING_MAX_PRODUCED = int(sys.argv[sys.argv.index("--ring-max") + 1])
     names = [k for k in LAYERS if which == "all" or k.startswith(which)]
@@ -55,10 +57,12 @@ def main():
             r0 = CV.stats.get("ring", 0)
             t_d = timeit(lambda: CV.conv_dgrad(dy, w, tuple(x.shape), (1, 1, 1), p))
             ring_d = CV.stats.get("ring", 0) > r0
+            r0 = CV.stats.get("halo_wgrad", 0)
             t_w = timeit(lambda: CV.conv_wgrad(x, dy, tuple(w.shape), (1, 1, 1), p))
+            halo_w = CV.stats.get("halo_wgrad", 0) > r0
         print(f"{name:16s} {flops / 1e9:9.1f} GF | fprop {t_f:8.3f} ms {flops / t_f / 1e9:7.1f} TF/s {'ring' if ring_f else 'igemm'}"
               f" | dgrad {t_d:8.3f} ms {flops / t_d / 1e9:7.1f} TF/s {'ring' if ring_d else 'igemm'}"
-              f" | wgrad {t_w:8.3f} ms {flops / t_w / 1e9:7.1f} TF/s", flush=True)
+              f" | wgrad {t_w:8.3f} ms {flops / t_w / 1e9:7.1f} TF/s {'halo' if halo_w else 'igemm'}", flush=True)
 
 
 if __name__ == "__main__":

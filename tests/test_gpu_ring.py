@@ -114,3 +114,57 @@ def test_ring_dgrad_matches_autograd(case):
         dx, _, _ = CV.conv_dgrad(dyg, w.to(DEV), tuple(x.shape), (1, 1, 1), _t3(p))
     assert CV.stats.get("ring", 0) == before + 1, "slice-ring kernel was not taken"
     assert _rel(dx, ref) <= 1e-2, _rel(dx, ref)
+
+
+WGRAD = [
+    # cin, cout, kernel, pad, input spatial, batch
+    (64, 64, 7, 0, (12, 22, 14), 1),          # head shape class: 25 tap pairs in 4 groups, unpaired last tap
+    (64, 64, 3, 1, (9, 10, 11), 2),           # zero padding: X planes outside the volume are skipped, ragged tiles
+    (128, 64, 3, 1, (6, 16, 8), 1),           # two ci chunks
+    (64, 128, 3, 0, (7, 18, 10), 1),          # BN = 128
+    (64, 256, (1, 3, 3), (0, 1, 1), (3, 16, 16), 1),   # BN = 256: two accumulators per CTA
+    (64, 64, (7, 1, 1), (3, 0, 0), (12, 16, 8), 1),
+    (64, 64, 1, 0, (5, 8, 8), 2),
+    (64, 64, (2, 4, 3), (1, 2, 1), (9, 10, 11), 1),
+]
+
+
+@pytest.mark.parametrize("case", WGRAD)
+def test_halo_wgrad_matches_autograd(case):
+    import raygun_b200 as rb
+    from raygun_b200 import conv as CV
+    cin, cout, k, p, sp, n = case
+    torch.manual_seed(24)
+    x = _q(torch.randn(n, cin, *sp))
+    w = torch.nn.Conv3d(cin, cout, k, padding=p, bias=False).weight.detach().requires_grad_(True)
+    y = TF.conv3d(x, w, None, padding=p)
+    dy = _q(torch.randn_like(y))
+    (ref,) = torch.autograd.grad(y, w, dy)
+    before = CV.stats.get("halo_wgrad", 0)
+    with rb.precision("bf16"):
+        xg = x.to(DEV).bfloat16().contiguous(memory_format=torch.channels_last_3d)
+        dyg = dy.to(DEV).bfloat16().contiguous(memory_format=torch.channels_last_3d)
+        dw, db = CV.conv_wgrad(xg, dyg, tuple(w.shape), (1, 1, 1), _t3(p), want_bias=True)
+    assert CV.stats.get("halo_wgrad", 0) == before + 1, "halo wgrad kernel was not taken"
+    assert dw.dtype == torch.float32 and tuple(dw.shape) == tuple(w.shape)
+    assert _rel(dw, ref) <= 2e-3, _rel(dw, ref)           # fp32 accumulation of exact bf16 products
+    assert _rel(db, dy.sum(dim=(0, 2, 3, 4))) <= 2e-3
+
+
+def test_halo_wgrad_many_splits_is_linear_in_dy():
+    """A multi-wave problem (more CTAs than SMs, several voxel splits) plus a size-independent property:
+    dW(x, a*dy1 + dy2) == a*dW(x, dy1) + dW(x, dy2) up to bf16 rounding of the combined dy."""
+    import raygun_b200 as rb
+    from raygun_b200 import conv as CV
+    torch.manual_seed(25)
+    n, c, sp = 2, 64, (20, 48, 40)
+    x = torch.randn(n, c, *sp, device=DEV).bfloat16().contiguous(memory_format=torch.channels_last_3d)
+    dy1 = torch.randn(n, c, *sp, device=DEV).bfloat16().contiguous(memory_format=torch.channels_last_3d)
+    dy2 = torch.randn(n, c, *sp, device=DEV).bfloat16().contiguous(memory_format=torch.channels_last_3d)
+    comb = (2.0 * dy1.float() + dy2.float()).bfloat16().contiguous(memory_format=torch.channels_last_3d)
+    with rb.precision("bf16"):
+        f = lambda g: CV.conv_wgrad(x, g, (c, c, 3, 3, 3), (1, 1, 1), (1, 1, 1))[0]
+        a, b, ab = f(dy1), f(dy2), f(comb)
+    ref = TF.conv3d(x.float().transpose(0, 1), comb.float().transpose(0, 1), padding=1).transpose(0, 1)   # [co][ci][k..]
+    assert _rel(ab, ref) <= 5e-3
+    assert _rel(ab, 2.0 * a + b) <= 1e-2
