@@ -251,26 +251,36 @@ __global__ void vec_act_bwd_kernel(T5 yd, const __nv_bfloat16* __restrict__ y, T
 }
 
 
+// Folded stem input: y[n, d, h, w, (ci*kh + a)*kw + b] = x[n, ci, d, h + a - ph, w + b - pw] (zero outside / beyond
+// Cin*kh*kw).  One block per output row (n, d, h): no per-element index division; the 8 channels of a thread walk
+// the (ci, a, b) odometer incrementally.
 template <typename TS>
-__global__ void im2col_hw_kernel(T5 xd, const TS* __restrict__ x, int kh, int kw, int ph, int pw, T5 yd,
-                                 __nv_bfloat16* __restrict__ y) {
-  const long long total = yd.numel() >> 3;
+__global__ void __launch_bounds__(256) im2col_hw_kernel(T5 xd, const TS* __restrict__ x, int kh, int kw, int ph, int pw,
+                                                        T5 yd, __nv_bfloat16* __restrict__ y) {
+  const int cg = (int)(yd.c >> 3);
   const int cvalid = (int)xd.c * kh * kw;
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-    VIdx p = vunravel(i, yd);
-    float v[8];
+  const int W = (int)yd.w, H = (int)yd.h, D = (int)yd.d;
+  const long long rows = yd.n * D * H;
+  for (long long row = blockIdx.x; row < rows; row += gridDim.x) {
+    const int h = (int)(row % H);
+    const long long t = row / H;
+    const int d = (int)(t % D), n = (int)(t / D);
+    const TS* xrow = x + n * xd.sn + d * xd.sd;
+    __nv_bfloat16* yrow = y + n * yd.sn + d * yd.sd + h * yd.sh;
+    for (int j = threadIdx.x; j < W * cg; j += blockDim.x) {
+      const int w = j / cg, c0 = (j - w * cg) << 3;
+      int b = c0 % kw, tt = c0 / kw, a = tt % kh, ci = tt / kh;
+      float v[8];
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      const int c = p.c + k;
-      float val = 0.f;
-      if (c < cvalid) {
-        const int kw_ = c % kw; int t = c / kw; const int kh_ = t % kh; const int ci = t / kh;
-        const long long ih = p.h + kh_ - ph, iw = p.w + kw_ - pw;
-        if (ih >= 0 && ih < xd.h && iw >= 0 && iw < xd.w) val = ldf(x + xd.off(p.n, ci, p.d, ih, iw));
+      for (int k = 0; k < 8; ++k) {
+        float val = 0.f;
+        const int ih = h + a - ph, iw = w + b - pw;
+        if (c0 + k < cvalid && ih >= 0 && ih < xd.h && iw >= 0 && iw < xd.w) val = ldf(xrow + ci * xd.sc + ih * xd.sh + iw * xd.sw);
+        v[k] = val;
+        if (++b == kw) { b = 0; if (++a == kh) { a = 0; ++ci; } }
       }
-      v[k] = val;
+      st8(yrow + (long long)w * yd.sw + c0, v);
     }
-    st8(y + voff(yd, p.n, p.d, p.h, p.w, p.c), v);
   }
 }
 
@@ -405,7 +415,7 @@ int rg_im2col_hw(const rg_tensor5* xd, const void* x, int kh, int kw, int ph, in
   if (total == 0) return RG_OK;
   cudaStream_t st = (cudaStream_t)stream;
   RG_DISPATCH_FLOAT(xd->dtype, TS, {
-    im2col_hw_kernel<TS><<<grid_for(total, 256), 256, 0, st>>>(view(xd), (const TS*)x, kh, kw, ph, pw, view(yd), (__nv_bfloat16*)y);
+    im2col_hw_kernel<TS><<<grid_for(yd->n * yd->d * yd->h, 1, 148 * 32), 256, 0, st>>>(view(xd), (const TS*)x, kh, kw, ph, pw, view(yd), (__nv_bfloat16*)y);
   })
   RG_LAUNCH_CHECK("rg_im2col_hw");
   return RG_OK;

@@ -39,7 +39,7 @@ struct alignas(64) HaloWgradParams {
 
 template <int BN>
 __global__ void __launch_bounds__(HW_THREADS, 1) halo_wgrad_kernel(const __grid_constant__ HaloWgradParams p) {
-  constexpr int NACC = 512 / BN;
+  constexpr int NACC = 512 / BN;            // accumulators (tap pairs) per CTA
   constexpr int DY_BYTES = (BN / 64) * HW_TILE_BYTES;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = ptx::smem_u32(smem_raw);
@@ -109,14 +109,26 @@ __global__ void __launch_bounds__(HW_THREADS, 1) halo_wgrad_kernel(const __grid_
     }
   } else if (warp == 1) {
     // ================= MMA issuer (whole warp convergent; one elected lane issues) =================
-    const bool leader = ptx::elect_one_sync();
+    const uint32_t lead = ptx::elect_one_sync() ? 1u : 0u;
     constexpr uint32_t idesc = ptx::idesc_bf16(128, BN, 1, 1);          // both operands MN-major
     const uint32_t sbo_a = (uint32_t)(p.wb * 128);
     const uint32_t b_hi = ((1024u >> 4) & 0x3FFFu) | (1u << 14) | (2u << 29);
     const uint32_t a_hi = ((sbo_a >> 4) & 0x3FFFu) | (1u << 14) | (2u << 29);
     const uint32_t b_lbo = ((uint32_t)(HW_TILE_BYTES >> 4) & 0x3FFFu) << 16;
+    // per tap pair (loop-invariant): row shift of the first tap and LBO = distance to the second, both >> 4
+    uint32_t a_off[NACC];
+    const int npairs = j_end - j_begin;
+#pragma unroll
+    for (int jj = 0; jj < NACC; ++jj) {
+      const int j = j_begin + jj;
+      const int ta = 2 * j, tb = (2 * j + 1 < ntaps_hw) ? 2 * j + 1 : 2 * j;       // unpaired last tap: duplicate
+      const int sha = (ta / p.kw) * p.wb + (ta % p.kw);
+      const int shb = (tb / p.kw) * p.wb + (tb % p.kw);
+      a_off[jj] = (uint32_t)(sha * 8) | ((((uint32_t)((shb - sha) * 128) >> 4) & 0x3FFFu) << 16);
+    }
+    const uint32_t k_step_a = (uint32_t)((2 * p.wb * 128) >> 4);       // 16 voxels (K) = two h rows of the tile
     int st = 0; uint32_t ph = 0;
-    bool first = true;
+    uint32_t acc = 0;
     for (int c = c_begin; c < c_end; ++c) {
       int n, d, h0, w0;
       decode(c, n, d, h0, w0);
@@ -125,28 +137,24 @@ __global__ void __launch_bounds__(HW_THREADS, 1) halo_wgrad_kernel(const __grid_
       ptx::mbar_wait(full(st), ph);
       ptx::tc_fence_after();
       const uint32_t sa = base + (uint32_t)(st * stage_bytes);
+      const uint32_t a_base = (sa >> 4) & 0x3FFFu;
       const uint32_t b_lo0 = (((sa + (uint32_t)p.slice_bytes) >> 4) & 0x3FFFu) | b_lbo;
-      for (int j = j_begin; j < j_end; ++j) {
-        const int ta = 2 * j, tb = min(2 * j + 1, ntaps_hw - 1) == 2 * j + 1 ? 2 * j + 1 : 2 * j;   // unpaired: duplicate
-        const int sha = (ta / p.kw) * p.wb + (ta % p.kw);
-        const int shb = (tb / p.kw) * p.wb + (tb % p.kw);
-        const uint32_t a_lo0 = (((sa + (uint32_t)(sha * 128)) >> 4) & 0x3FFFu) | ((((uint32_t)((shb - sha) * 128) >> 4) & 0x3FFFu) << 16);
-        const uint32_t dcol = tmem_base + (uint32_t)((j - j_begin) * BN);
-        if (leader) {
 #pragma unroll
-          for (int k = 0; k < 8; ++k) {
-            // 16 voxels (K) = two 8-voxel groups = two h rows of the tile
-            const uint32_t a_lo = a_lo0 + (uint32_t)((k * 2 * p.wb * 128) >> 4);
-            const uint32_t b_lo = b_lo0 + (uint32_t)(k * 128);
-            ptx::umma_bf16(dcol, ((uint64_t)a_hi << 32) | a_lo, ((uint64_t)b_hi << 32) | b_lo, idesc, (!first || k > 0) ? 1u : 0u);
-          }
+      for (int jj = 0; jj < NACC; ++jj) {
+        if (jj < npairs) {
+          const uint32_t a_lo0 = a_base + a_off[jj];
+          const uint32_t dcol = tmem_base + (uint32_t)(jj * BN);
+#pragma unroll
+          for (int k = 0; k < 8; ++k)
+            ptx::umma_bf16_pred(dcol, ((uint64_t)a_hi << 32) | (a_lo0 + k * k_step_a), ((uint64_t)b_hi << 32) | (b_lo0 + (uint32_t)(k * 128)),
+                                idesc, k > 0 ? 1u : acc, lead);
         }
       }
-      if (leader) ptx::umma_commit(empty(st));
+      ptx::umma_commit_pred(empty(st), lead);
       if (++st == p.stages) { st = 0; ph ^= 1u; }
-      first = false;
+      acc = 1u;
     }
-    if (leader) ptx::umma_commit(done_bar);
+    ptx::umma_commit_pred(done_bar, lead);
     __syncwarp();
   } else {
     // ================= epilogue: TMEM -> vector reductions into ws[tap][ci][co] =================

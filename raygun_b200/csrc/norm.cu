@@ -15,6 +15,10 @@ __device__ __forceinline__ int group_of(int kind, long long n, long long c, long
   return kind == RG_NORM_INSTANCE ? (int)(n * C + c) : (int)c;
 }
 
+}  // namespace rg
+#include "norm_dense.cuh"
+namespace rg {
+
 // MODE 0: (x, x^2).  MODE 1: (g, g*xhat) with g = dy * act'(y).
 template <int MODE, typename TX, typename TG>
 __device__ __forceinline__ void red_terms(const NormCtx& cx, int grp, const T5& xd, const TX* x, const T5& gd,
@@ -311,6 +315,15 @@ static int launch_reduce2(const NormCtx& cx, const rg_tensor5* xd, const TX* x, 
                           const rg_tensor5* yd, const TG* y, float* out0, float* out1, cudaStream_t st) {
   T5 xv = view(xd), gv = gd ? view(gd) : xv, yv = yd ? view(yd) : xv;
   long long vox = xv.d * xv.h * xv.w;
+  if (dense_ok(xd, x) && dense_cg_ok(xd) && xv.n <= 65535 &&
+      (MODE == 0 || (dense_ok(gd, dy) && (cx.act == RG_ACT_NONE || dense_ok(yd, y))))) {
+    dim3 grid;
+    DenseGeom gm = dense_geom(xd, &grid, 48);
+    if (MODE) { gm.gn = gd->sn; if (yd) gm.yn = yd->sn; }
+    dense_reduce2_kernel<MODE><<<grid, 256, 0, st>>>(cx, gm, (const __nv_bfloat16*)x, (const __nv_bfloat16*)dy,
+                                                     (const __nv_bfloat16*)y, out0, out1);
+    return RG_OK;
+  }
   if (vec_ok(xd, x) && (MODE == 0 || (vec_ok(gd, dy) && (cx.act == RG_ACT_NONE || vec_ok(yd, y))))) {
     long long blocks_x = (148LL * 4 + xv.n - 1) / xv.n;
     long long vpb = (vox + blocks_x - 1) / blocks_x;
@@ -385,6 +398,16 @@ int rg_norm_apply(const rg_tensor5* xd, const void* x, int kind, const float* me
   bool ci = channels_inner(yd);
   int rdt = residual ? rd->dtype : xd->dtype;
   T5 rv = residual ? view(rd) : view(xd);
+  if (dense_ok(xd, x) && dense_ok(yd, y) && (!residual || dense_ok(rd, residual)) && dense_cg_ok(xd) && xd->n <= 65535) {
+    dim3 dgrid;
+    DenseGeom gm = dense_geom(xd, &dgrid);
+    gm.on = yd->sn;
+    if (residual) gm.gn = rd->sn;
+    dense_norm_apply_kernel<<<dgrid, 256, 0, st>>>(cx, beta, gm, (const __nv_bfloat16*)x, (const __nv_bfloat16*)residual,
+                                                   (__nv_bfloat16*)y);
+    RG_LAUNCH_CHECK("rg_norm_apply(dense)");
+    return RG_OK;
+  }
   if (vec_ok(xd, x) && vec_ok(yd, y) && (!residual || vec_ok(rd, residual))) {
     vec_norm_apply_kernel<<<grid_for(total >> 3, 256), 256, 0, st>>>(cx, beta, view(xd), (const __nv_bfloat16*)x, rv,
                                                                      (const __nv_bfloat16*)residual, view(yd), (__nv_bfloat16*)y);
@@ -430,6 +453,18 @@ int rg_norm_bwd(const rg_tensor5* xd, const void* x, const rg_tensor5* dyd, cons
     int grid = grid_for(total, 256);
     bool ci = channels_inner(dxd);
     T5 yv = (yd && y) ? view(yd) : xv;
+    if (dense_ok(xd, x) && dense_ok(dyd, dy) && dense_ok(dxd, dx) && (act == RG_ACT_NONE || dense_ok(yd, y)) &&
+        dense_cg_ok(xd) && xd->n <= 65535) {
+      dim3 dgrid;
+      DenseGeom gm = dense_geom(xd, &dgrid);
+      gm.gn = dyd->sn; gm.on = dxd->sn;
+      if (act != RG_ACT_NONE) gm.yn = yd->sn;
+      dense_norm_bwd_dx_kernel<<<dgrid, 256, 0, st>>>(cx, training, red, (float)(1.0 / count), groups, gm,
+                                                      (const __nv_bfloat16*)x, (const __nv_bfloat16*)dy,
+                                                      (const __nv_bfloat16*)y, (__nv_bfloat16*)dx);
+      RG_LAUNCH_CHECK("rg_norm_bwd dx(dense)");
+      return RG_OK;
+    }
     if (vec_ok(xd, x) && vec_ok(dyd, dy) && vec_ok(dxd, dx) && (act == RG_ACT_NONE || vec_ok(yd, y))) {
       vec_norm_bwd_dx_kernel<<<grid_for(total >> 3, 256), 256, 0, st>>>(
           cx, training, red, (float)(1.0 / count), xv, (const __nv_bfloat16*)x, view(dyd), (const __nv_bfloat16*)dy, yv,

@@ -21,6 +21,8 @@
 #include <cuda.h>
 #include <cuda_bf16.h>
 
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "sm100_ptx.cuh"
 
@@ -33,6 +35,7 @@ constexpr int STAGE_KD = 4;               // kd blocks per weight stage (<= 256 
 constexpr int RING_TH = 16, RING_TW = 8;  // output tile (h, w); 8 = one swizzle-atom row group
 constexpr int MAX_S = 8, MAX_NA = 12, MAX_NB = 4;
 constexpr int PTAB_N = 2 * MAX_S;                                   // pieces per weight-stage part (<= 2 per slice)
+constexpr int PREG_N = 8;                                           // ... kept in registers: S <= 4 slices per group
 constexpr int RING_PTAB_OFF = 8 * (2 * MAX_NA + 2 * MAX_NB + 4) + 32;
 constexpr int RING_TAIL_BYTES = RING_PTAB_OFF + 2 * PTAB_N * 16 + 64;
 
@@ -61,18 +64,48 @@ struct alignas(64) RingParams {
 
 struct RingUnit { int nt, n, h0, w0, d0, len, z_begin, z_end; };
 
-__device__ __forceinline__ RingUnit ring_decode(const RingParams& p, int u) {
-  RingUnit r;
-  r.nt = u % p.n_tiles_n; u /= p.n_tiles_n;
-  const int iw = u % p.tiles_w; u /= p.tiles_w;
-  const int ih = u % p.tiles_h; u /= p.tiles_h;
-  const int sg = u % p.segs; r.n = u / p.segs;
-  r.h0 = ih * RING_TH; r.w0 = iw * RING_TW; r.d0 = sg * p.seg_len;
-  r.len = min(p.seg_len, p.out_d - r.d0);
-  r.z_begin = r.d0 - p.pd;
-  r.z_end = r.d0 + r.len - 1 - p.pd + p.kd - 1;
-  return r;
-}
+// Work partition: the (column, output plane) space is flattened column-major and cut into gridDim.x equal ranges, so
+// every CTA does the same number of plane-taps (no wave quantisation); a range is walked as at most a few units
+// (column, d0, len), each of which re-reads only the KD-1 halo slices of its column.
+struct RingWalk {
+  long long pos, end;
+  __device__ __forceinline__ RingWalk(const RingParams& p) {
+    if (p.segs > 0) {          // equal depth segments, round-robin over CTAs (neighbouring columns run concurrently)
+      pos = blockIdx.x;
+      end = (long long)p.batch * p.segs * p.tiles_h * p.tiles_w * p.n_tiles_n;
+    } else {
+      const long long total = (long long)p.batch * p.tiles_h * p.tiles_w * p.n_tiles_n * p.out_d;
+      pos = total * blockIdx.x / gridDim.x;
+      end = total * (blockIdx.x + 1) / gridDim.x;
+    }
+  }
+  __device__ __forceinline__ bool next(const RingParams& p, RingUnit& r) {
+    if (pos >= end) return false;
+    int u;
+    if (p.segs > 0) {
+      u = (int)pos;
+      pos += gridDim.x;
+      r.nt = u % p.n_tiles_n; u /= p.n_tiles_n;
+      const int iw = u % p.tiles_w; u /= p.tiles_w;
+      const int ih = u % p.tiles_h; u /= p.tiles_h;
+      const int sg = u % p.segs; r.n = u / p.segs;
+      r.h0 = ih * RING_TH; r.w0 = iw * RING_TW; r.d0 = sg * p.seg_len;
+      r.len = min(p.seg_len, p.out_d - r.d0);
+    } else {
+      u = (int)(pos / p.out_d);
+      r.d0 = (int)(pos - (long long)u * p.out_d);
+      r.len = (int)min((long long)(p.out_d - r.d0), end - pos);
+      pos += r.len;
+      r.nt = u % p.n_tiles_n; u /= p.n_tiles_n;
+      const int iw = u % p.tiles_w; u /= p.tiles_w;
+      const int ih = u % p.tiles_h; r.n = u / p.tiles_h;
+      r.h0 = ih * RING_TH; r.w0 = iw * RING_TW;
+    }
+    r.z_begin = r.d0 - p.pd;
+    r.z_end = r.d0 + r.len - 1 - p.pd + p.kd - 1;
+    return true;
+  }
+};
 
 __global__ void __launch_bounds__(RING_THREADS, 1) ring_conv_kernel(const __grid_constant__ RingParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -95,7 +128,6 @@ __global__ void __launch_bounds__(RING_THREADS, 1) ring_conv_kernel(const __grid
   auto tempty = [&](int s) { return bar0 + 8u * (2 * MAX_NA + 2 * MAX_NB + 2 + s); };
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int total_units = p.batch * p.segs * p.tiles_h * p.tiles_w * p.n_tiles_n;
   const int ntaps_hw = p.kh * p.kw;
   const int parts = (p.kd + STAGE_KD - 1) / STAGE_KD;
 
@@ -127,8 +159,8 @@ __global__ void __launch_bounds__(RING_THREADS, 1) ring_conv_kernel(const __grid
       // ================= TMA producer =================
       int a_i = 0; uint32_t a_ph = 0;
       int b_i = 0; uint32_t b_ph = 0;
-      for (int u = blockIdx.x; u < total_units; u += gridDim.x) {
-        const RingUnit r = ring_decode(p, u);
+      RingUnit r;
+      for (RingWalk walk(p); walk.next(p, r);) {
         for (int zg = r.z_begin; zg <= r.z_end; zg += p.S) {
           for (int q = 0; q < p.q_chunks; ++q) {
             auto load_slice = [&](int s) {
@@ -166,7 +198,7 @@ __global__ void __launch_bounds__(RING_THREADS, 1) ring_conv_kernel(const __grid
     // ================= MMA issuer =================
     // The whole warp runs this loop convergently (so addresses / descriptors stay in the uniform datapath and the
     // tcgen05.mma operands need no per-instruction lane election loop); one elected lane issues.
-    const bool leader = ptx::elect_one_sync();
+    const uint32_t lead = ptx::elect_one_sync() ? 1u : 0u;
     const uint32_t idesc_base = ptx::idesc_bf16(128, 0, 0, 0);
     const uint32_t a_hi = (((uint32_t)(p.wb * 128) >> 4) & 0x3FFFu) | (1u << 14) | (2u << 29);   // SBO | version | SW128
     const uint32_t b_hi = ((1024u >> 4) & 0x3FFFu) | (1u << 14) | (2u << 29);
@@ -174,8 +206,8 @@ __global__ void __launch_bounds__(RING_THREADS, 1) ring_conv_kernel(const __grid
     int a_i = 0; uint32_t a_ph = 0;
     int b_i = 0; uint32_t b_ph = 0;
     int g = 0, waited = -1;
-    for (int u = blockIdx.x; u < total_units; u += gridDim.x) {
-      const RingUnit r = ring_decode(p, u);
+    RingUnit r;
+    for (RingWalk walk(p); walk.next(p, r);) {
       bool first = true;
       for (int zg = r.z_begin; zg <= r.z_end; zg += p.S) {
         // piece table of this group: which accumulator blocks each (slice, weight-stage part) feeds.  It is the same
@@ -208,46 +240,65 @@ __global__ void __launch_bounds__(RING_THREADS, 1) ring_conv_kernel(const __grid
         }
         __syncwarp();
         nvalid = pcnt[2];
+        // the table is invariant over the taps and reduction chunks of the group: keep it in registers
+        const int n0 = pcnt[0], n1 = pcnt[1];
+        uint4 e0[PREG_N], e1[PREG_N];
+#pragma unroll
+        for (int j = 0; j < PREG_N; ++j) {
+          e0[j] = j < n0 ? ptab[j] : make_uint4(0, 0, 0, 0);
+          e1[j] = j < n1 ? ptab[PTAB_N + j] : make_uint4(0, 0, 0, 0);
+        }
         const int need = first ? g - 1 : g - p.lag;
         while (waited < need) { ++waited; ptx::mbar_wait(tempty(waited & 1), (uint32_t)((waited >> 1) & 1)); }
         ptx::tc_fence_after();
         for (int q = 0; q < p.q_chunks; ++q) {
-          uint32_t ready = 0;       // slices of this chunk whose TMA has been waited for
+          // slices of this chunk: wait for their TMA, then fold the slot address into the per-piece A base
+          for (int j = 0; j < nvalid; ++j) {
+            int slot = a_i + j; uint32_t sph = a_ph;
+            if (slot >= p.na) { slot -= p.na; sph ^= 1u; }
+            ptx::mbar_wait(afull(slot), sph);
+          }
+          ptx::tc_fence_after();
+          uint32_t ab0[PREG_N], ab1[PREG_N];
+#pragma unroll
+          for (int j = 0; j < PREG_N; ++j) {
+            int s0 = a_i + (int)e0[j].z; if (s0 >= p.na) s0 -= p.na;
+            int s1 = a_i + (int)e1[j].z; if (s1 >= p.na) s1 -= p.na;
+            ab0[j] = ((smem_a + (uint32_t)(s0 * p.slice_bytes)) >> 4) | lbo_lo;
+            ab1[j] = ((smem_a + (uint32_t)(s1 * p.slice_bytes)) >> 4) | lbo_lo;
+          }
           for (int t = 0; t < ntaps_hw; ++t) {
             const int tkh = t / p.kw, tkw = t - tkh * p.kw;
             const uint32_t a_shift = (uint32_t)((tkh * p.wb + tkw) * 8);        // rows * 128 B >> 4
-            for (int part = 0; part < parts; ++part) {
-              ptx::mbar_wait(bfull(b_i), b_ph);
-              ptx::tc_fence_after();
-              const uint32_t b_lo = (((smem_b + (uint32_t)(b_i * p.stage_bytes)) >> 4) & 0x3FFFu) | lbo_lo;
-              const int n = pcnt[part];
-              for (int j = 0; j < n; ++j) {
-                const uint4 e = ptab[part * PTAB_N + j];
-                int slot = a_i + (int)e.z; uint32_t sph = a_ph;
-                if (slot >= p.na) { slot -= p.na; sph ^= 1u; }
-                if (t == 0 && !((ready >> e.z) & 1u)) {
-                  ptx::mbar_wait(afull(slot), sph);
-                  ptx::tc_fence_after();
-                  ready |= 1u << e.z;
-                }
-                const uint32_t a_lo = ((((smem_a + (uint32_t)(slot * p.slice_bytes)) >> 4) + a_shift) & 0x3FFFu) | lbo_lo;
-                if (leader) {
 #pragma unroll
-                  for (int k = 0; k < 4; ++k)
-                    ptx::umma_bf16(e.x, ((uint64_t)a_hi << 32) | (uint64_t)(a_lo + 2 * k),
-                                   ((uint64_t)b_hi << 32) | (uint64_t)(b_lo + e.w + 2 * k), e.y, 1u);
+            for (int part = 0; part < 2; ++part) {
+              if (part < parts) {
+                ptx::mbar_wait(bfull(b_i), b_ph);
+                ptx::tc_fence_after();
+                const uint32_t b_lo = (((smem_b + (uint32_t)(b_i * p.stage_bytes)) >> 4) & 0x3FFFu) | lbo_lo;
+                const int n = part ? n1 : n0;
+#pragma unroll
+                for (int j = 0; j < PREG_N; ++j) {
+                  if (j < n) {
+                    const uint4 e = part ? e1[j] : e0[j];
+                    const uint32_t a_lo = (part ? ab1[j] : ab0[j]) + a_shift;
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                      ptx::umma_bf16_pred(e.x, ((uint64_t)a_hi << 32) | (uint64_t)(a_lo + 2 * k),
+                                          ((uint64_t)b_hi << 32) | (uint64_t)(b_lo + e.w + 2 * k), e.y, 1u, lead);
+                  }
                 }
+                ptx::umma_commit_pred(bempty(b_i), lead);
+                if (++b_i == p.nb) { b_i = 0; b_ph ^= 1u; }
               }
-              if (leader) ptx::umma_commit(bempty(b_i));
-              if (++b_i == p.nb) { b_i = 0; b_ph ^= 1u; }
             }
           }
           for (int j = 0; j < nvalid; ++j) {
-            if (leader) ptx::umma_commit(aempty(a_i));
+            ptx::umma_commit_pred(aempty(a_i), lead);
             if (++a_i == p.na) { a_i = 0; a_ph ^= 1u; }
           }
         }
-        if (leader) ptx::umma_commit(tfull(g & 1));
+        ptx::umma_commit_pred(tfull(g & 1), lead);
         ++g;
         first = false;
       }
@@ -271,8 +322,8 @@ __global__ void __launch_bounds__(RING_THREADS, 1) ring_conv_kernel(const __grid
       st_sum = st_sq = 0.f;
     };
     int g = 0;
-    for (int u = blockIdx.x; u < total_units; u += gridDim.x) {
-      const RingUnit r = ring_decode(p, u);
+    RingUnit r;
+    for (RingWalk walk(p); walk.next(p, r);) {
       if (r.n != st_n || r.nt != st_nt) { flush_stats(); st_n = r.n; st_nt = r.nt; }
       const int oh = r.h0 + rh, ow = r.w0 + rw;
       const bool valid = oh < p.out_h && ow < p.out_w;
@@ -468,20 +519,25 @@ static int ring_geometry(const rg_igemm_desc* d, RingGeom* g) {
   p.in_d = g->in_ext[0];
   p.out_d = g->out_ext[0]; p.out_h = g->out_ext[1]; p.out_w = g->out_ext[2];
   // depth segment length: balance wave quantisation against the (KD-1) extra slices every segment re-reads
-  const long long cols = (long long)d->n * p.tiles_h * p.tiles_w * p.n_tiles_n;
-  const int sms = ring_num_sms();
-  double best = 1e300; int best_len = p.out_d;
-  for (int segs = 1; segs <= p.out_d; ++segs) {
-    const int len = (p.out_d + segs - 1) / segs;
-    if ((p.out_d + len - 1) / len != segs) continue;
-    if (len < 4 && segs > 1) break;
-    const long long units = cols * segs;
-    const double waves = (double)((units + sms - 1) / sms);
-    const double cost = waves * (len + 0.35 * (p.kd - 1) + 1.0);
-    if (cost < best) { best = cost; best_len = len; }
+  {
+    const long long cols = (long long)d->n * p.tiles_h * p.tiles_w * p.n_tiles_n;
+    const int sms = ring_num_sms();
+    double best = 1e300; int best_len = p.out_d;
+    for (int segs = 1; segs <= p.out_d; ++segs) {
+      const int len = (p.out_d + segs - 1) / segs;
+      if ((p.out_d + len - 1) / len != segs) continue;
+      if (len < 4 && segs > 1) break;
+      const long long units = cols * segs;
+      const double waves = (double)((units + sms - 1) / sms);
+      const double cost = waves * (len + 0.35 * (p.kd - 1) + 1.0);
+      if (cost < best) { best = cost; best_len = len; }
+    }
+    p.seg_len = best_len;
+    p.segs = (p.out_d + best_len - 1) / best_len;
+    static const char* mode = getenv("RAYGUN_B200_RING_PARTITION");
+    if (!(mode && mode[0] == 's')) p.segs = 0;    // default "balanced": equal flattened plane ranges per CTA;
+                                                  // RAYGUN_B200_RING_PARTITION=segments keeps round-robin segments
   }
-  p.seg_len = best_len;
-  p.segs = (p.out_d + best_len - 1) / best_len;
   p.cout_total = g->rows;
   p.act = d->act; p.slope = d->slope;
   p.ys_n = g->out_str[0]; p.ys_d = g->out_str[1]; p.ys_h = g->out_str[2]; p.ys_w = g->out_str[3];
@@ -572,8 +628,10 @@ int rg_ring_run(const rg_igemm_desc* d, const void* in, const void* w_ring, cons
     if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(ring_conv)");
     smem_set = RING_SMEM_LIMIT;
   }
-  const long long units = (long long)p.batch * p.segs * p.tiles_h * p.tiles_w * p.n_tiles_n;
-  const int grid = (int)(units < ring_num_sms() ? units : ring_num_sms());
+  long long want;
+  if (p.segs > 0) want = (long long)p.batch * p.segs * p.tiles_h * p.tiles_w * p.n_tiles_n;
+  else want = ((long long)p.batch * p.tiles_h * p.tiles_w * p.n_tiles_n * p.out_d + 3) / 4;
+  const int grid = (int)(want < ring_num_sms() ? (want < 1 ? 1 : want) : ring_num_sms());
   ring_conv_kernel<<<grid, RING_THREADS, g.smem_bytes, (cudaStream_t)stream>>>(p);
   RG_LAUNCH_CHECK("rg_ring_run");
   return RG_OK;

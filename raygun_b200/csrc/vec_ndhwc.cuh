@@ -33,6 +33,14 @@ struct VIdx { long long n, d, h, w; int c; };
 __device__ __forceinline__ VIdx vunravel(long long i, const T5& t) {
   VIdx r;
   const int cg = (int)(t.c >> 3);
+  if (i < 0x7fffffffLL) {      // 32-bit index arithmetic (a 64-bit div/mod costs ~5x more instructions)
+    unsigned j = (unsigned)i, q;
+    q = j / (unsigned)cg; r.c = (int)(j - q * (unsigned)cg) << 3; j = q;
+    q = j / (unsigned)t.w; r.w = j - q * (unsigned)t.w; j = q;
+    q = j / (unsigned)t.h; r.h = j - q * (unsigned)t.h; j = q;
+    q = j / (unsigned)t.d; r.d = j - q * (unsigned)t.d; r.n = q;
+    return r;
+  }
   r.c = (int)(i % cg) << 3; i /= cg;
   r.w = i % t.w; i /= t.w;
   r.h = i % t.h; i /= t.h;

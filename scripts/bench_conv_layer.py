@@ -37,6 +37,12 @@ def timeit(fn, iters=5, warm=2):
 
 def main():
     which = sys.argv[1] if len(sys.argv) > 1 else "all"
+    if "--lib" in sys.argv:      # A/B against an older build of the library (pair with --no-halo if it predates it)
+        import ctypes
+        from raygun_b200 import _C
+        l = ctypes.CDLL(sys.argv[sys.argv.index("--lib") + 1])
+        l.rg_last_error.restype = ctypes.c_char_p
+        _C._lib = l
     if "--no-halo" in sys.argv:
         CV.HALO_WGRAD = False
     if "--ring-max" in sys.argv:
