@@ -209,22 +209,59 @@ def run_ours(args):
     x_dev = K.u8_normalise(host_x.to(dev), dtype=torch.float32)
     t_dev = K.u8_normalise(host_t.to(dev), dtype=torch.float32)
 
-    def step(x, t):
+    def fwd_bwd(x, t):
         for p in params:
             p.grad = None
         y = g(x)
         loss = F.smooth_l1_loss(t, y)
         loss.backward()
+        return loss
+
+    def sync_grads():
         if world > 1:   # data-parallel: average gradients over ranks (flat bucket, NCCL over NVLink)
             flat = torch.cat([p.grad.reshape(-1) for p in params])
             dist.all_reduce(flat)
             flat.div_(world)
+
+    def step(x, t):
+        loss = fwd_bwd(x, t)
+        sync_grads()
         return loss
 
+    # The step is ~300 kernel launches of 5 us - 10 ms each: capture normalise + forward + backward + loss in ONE CUDA
+    # graph (static uint8 input buffers) so launch gaps do not sit between the kernels.  --no-graph keeps eager launches.
+    graph = None
+    xu_s = host_x.to(dev)
+    tu_s = host_t.to(dev)
+    if not args.no_graph:
+        try:
+            for _ in range(3):
+                fwd_bwd(K.u8_normalise(xu_s, dtype=torch.float32), K.u8_normalise(tu_s, dtype=torch.float32))
+            torch.cuda.synchronize()
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                loss_s = fwd_bwd(K.u8_normalise(xu_s, dtype=torch.float32), K.u8_normalise(tu_s, dtype=torch.float32))
+            graph.replay()
+            torch.cuda.synchronize()
+        except Exception as exc:      # noqa: BLE001 -- fall back to eager launches, and say so in the JSON line
+            print(f"bench.py: CUDA graph capture failed ({exc!r}); running eager", file=sys.stderr)
+            graph = None
+            torch.cuda.synchronize()
+
+    def graph_step():
+        graph.replay()
+        sync_grads()
+        return loss_s
+
     def e2e_step():
-        xu = host_x.to(dev, non_blocking=True)
-        tu = host_t.to(dev, non_blocking=True)
-        loss = step(K.u8_normalise(xu, dtype=torch.float32), K.u8_normalise(tu, dtype=torch.float32))
+        if graph is not None:
+            xu_s.copy_(host_x, non_blocking=True)
+            tu_s.copy_(host_t, non_blocking=True)
+            loss = graph_step()
+        else:
+            xu = host_x.to(dev, non_blocking=True)
+            tu = host_t.to(dev, non_blocking=True)
+            loss = step(K.u8_normalise(xu, dtype=torch.float32), K.u8_normalise(tu, dtype=torch.float32))
         return float(loss.detach())     # D2H of the step's result
 
     def barrier():
@@ -253,8 +290,9 @@ def run_ours(args):
     if rank == 0:
         sampler.start()
     l0 = _C.launch_count
-    ms = timed(lambda: step(x_dev, t_dev), args.steps)
-    launches = (_C.launch_count - l0) // args.steps
+    step(x_dev, t_dev)                  # count the launches of one (eager) step; the graph replays the same kernels
+    launches = _C.launch_count - l0 + (2 if graph is not None else 0)       # + the two u8_normalise launches in the graph
+    ms = timed(graph_step if graph is not None else (lambda: step(x_dev, t_dev)), args.steps)
     clocks = sampler.stop() if rank == 0 else None
     ms_e2e = timed(e2e_step, args.steps)
 
@@ -264,21 +302,36 @@ def run_ours(args):
     step(x_dev, t_dev)
     torch.cuda.synchronize()
     prof, CV.profile = CV.profile, None
-    by_kind = {}
-    for kind, fl, a, b in prof:
-        d = by_kind.setdefault(kind, [0.0, 0.0, 0])
-        d[0] += fl
-        d[1] += a.elapsed_time(b)
-        d[2] += 1
+    by_kind, by_kernel = {}, {}
+    for kind, fl, a, b, kname in prof:
+        dt = a.elapsed_time(b)
+        for table, key in ((by_kind, kind), (by_kernel, kname)):
+            d = table.setdefault(key, [0.0, 0.0, 0])
+            d[0] += fl
+            d[1] += dt
+            d[2] += 1
     peaks = load_peaks()
     tot_fl = sum(v[0] for v in by_kind.values())
     tot_ms = sum(v[1] for v in by_kind.values())
-    achieved = tot_fl / (tot_ms * 1e-3) / 1e12 if tot_ms > 0 else 0.0
+    # the dominant kernel = the one with the largest share of the step; achieved = its algorithmic FLOPs / its time
+    dom = max(by_kernel, key=lambda k: by_kernel[k][1])
+    dfl, dms, dn = by_kernel[dom]
+    achieved = dfl / (dms * 1e-3) / 1e12 if dms > 0 else 0.0
     peak = peaks["tf_sustained"]
-    roofline = dict(bound="tensor", kernel="igemm_conv_kernel / igemm_wgrad_kernel (tcgen05, all conv launches of one step)",
-                    achieved=achieved, peak=peak, unit="TFLOP/s", frac=achieved / peak,
-                    peak_kind=f"{peaks['source']} sustained bf16 (burst {peaks['tf_burst']})", traffic=None,
-                    launches=sum(v[2] for v in by_kind.values()), share_of_step=tot_ms / ms,
+    traffic = None
+    try:        # DRAM bytes per launch of that kernel from the committed `ncu --set full` capture (profiles/)
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            traffic = json.load(f).get(dom, {}).get("dram_bytes_per_launch")
+    except OSError:
+        pass
+    roofline = dict(bound="tensor", kernel=f"{dom} (tcgen05; {dn} launches per step)", achieved=achieved, peak=peak,
+                    unit="TFLOP/s", frac=achieved / peak,
+                    peak_kind=f"{peaks['source']} sustained bf16 (burst {peaks['tf_burst']})", traffic=traffic,
+                    algorithmic_tflop_per_launch=dfl / dn / 1e12, ms_per_launch=dms / dn, share_of_step=dms / ms,
+                    all_convs=dict(tflops=tot_fl / (tot_ms * 1e-3) / 1e12 if tot_ms > 0 else 0.0,
+                                   frac=(tot_fl / (tot_ms * 1e-3) / 1e12) / peak if tot_ms > 0 else 0.0,
+                                   launches=sum(v[2] for v in by_kind.values()), share_of_step=tot_ms / ms),
+                    by_kernel={k: dict(tflops=v[0] / (v[1] * 1e-3) / 1e12, ms=v[1], launches=v[2]) for k, v in by_kernel.items()},
                     by_kind={k: dict(tflops=v[0] / (v[1] * 1e-3) / 1e12, ms=v[1], launches=v[2]) for k, v in by_kind.items()})
 
     if rank == 0:
@@ -297,7 +350,8 @@ def run_ours(args):
                    config=dict(workload=f"{args.workload}: G-ResNet{n_blocks} (ngf {ngf}, InstanceNorm, reflect 'same') "
                                         f"fwd+bwd+SmoothL1 on {batch}x1x{side}^3 per GPU",
                                l2="activation working set (GBs) >> 126 MB L2; no explicit flush",
-                               parallelism=f"dp{world}" if world > 1 else "single", algorithmic_tflop_per_step=3 * fwd / 1e12),
+                               parallelism=f"dp{world}" if world > 1 else "single", algorithmic_tflop_per_step=3 * fwd / 1e12,
+                               cuda_graph=graph is not None),
                    step_tflops=3 * fwd * world / (ms * 1e-3) / 1e12,
                    e2e=dict(value=vox / (ms_e2e * 1e-3), unit="voxels/s", ms_per_step=ms_e2e,
                             h2d_bytes_per_step=int(host_x.numel() + host_t.numel()), d2h_bytes_per_step=4),
@@ -317,6 +371,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS))
+    ap.add_argument("--no-graph", action="store_true", help="launch every kernel eagerly instead of replaying one CUDA graph")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -24,10 +24,10 @@ profile = None
 
 
 class _Timed:
-    def __init__(self, kind, flops, device):
+    def __init__(self, kind, flops, device, kernel="igemm_conv_kernel"):
         self.on = profile is not None
         if self.on:
-            self.kind, self.flops = kind, flops
+            self.kind, self.flops, self.kernel = kind, flops, kernel
             self.e0 = torch.cuda.Event(enable_timing=True)
             self.e1 = torch.cuda.Event(enable_timing=True)
             self.stream = torch.cuda.current_stream(device)
@@ -40,7 +40,7 @@ class _Timed:
     def __exit__(self, *exc):
         if self.on:
             self.e1.record(self.stream)
-            profile.append((self.kind, self.flops, self.e0, self.e1))
+            profile.append((self.kind, self.flops, self.e0, self.e1, self.kernel))
         return False
 
 
@@ -246,7 +246,7 @@ def conv_fprop(x, w, bias, stride, pad, groups=1, act=ACT_NONE, slope=0.0, want_
         if rd is not None:
             wr = ring_packed_weights(w, 0)
             st = torch.zeros(2, n * cout, dtype=torch.float32, device=x.device) if want_stats else None
-            with _Timed("fprop", 2.0 * y.numel() * cin_t * kernel[0] * kernel[1] * kernel[2], x.device):
+            with _Timed("fprop", 2.0 * y.numel() * cin_t * kernel[0] * kernel[1] * kernel[2], x.device, "ring_conv_kernel"):
                 check(lib().rg_ring_run(C.byref(rd), ptr(xb), ptr(wr), ptr(bias_f), ptr(y),
                                         ptr(st[0]) if want_stats else None, ptr(st[1]) if want_stats else None,
                                         stream_ptr(x.device)), "rg_ring_run(fprop)")
@@ -304,7 +304,7 @@ def conv_dgrad(dy, w, x_shape, stride, pad, groups=1, bias=None, act=ACT_NONE, s
         if rd is not None:
             wr = ring_packed_weights(w, 1)
             st = torch.zeros(2, n * cin_t, dtype=torch.float32, device=dy.device) if want_stats else None
-            with _Timed("dgrad", 2.0 * dyb.numel() * cin_t * kernel[0] * kernel[1] * kernel[2], dy.device):
+            with _Timed("dgrad", 2.0 * dyb.numel() * cin_t * kernel[0] * kernel[1] * kernel[2], dy.device, "ring_conv_kernel"):
                 check(lib().rg_ring_run(C.byref(rd), ptr(dyb), ptr(wr), ptr(bias_f), ptr(dx),
                                         ptr(st[0]) if want_stats else None, ptr(st[1]) if want_stats else None,
                                         stream_ptr(dy.device)), "rg_ring_run(dgrad)")
@@ -357,7 +357,7 @@ def conv_wgrad(x, dy, w_shape, stride, pad, groups=1, want_bias=False):
         if hd is not None:
             dw = torch.zeros(tuple(w_shape), dtype=torch.float32, device=x.device)
             ws = torch.empty(dw.numel(), dtype=torch.float32, device=x.device)
-            with _Timed("wgrad", 2.0 * dyb.numel() * cin_g * kernel[0] * kernel[1] * kernel[2], x.device):
+            with _Timed("wgrad", 2.0 * dyb.numel() * cin_g * kernel[0] * kernel[1] * kernel[2], x.device, "halo_wgrad_kernel"):
                 check(lib().rg_halo_wgrad(C.byref(hd), ptr(xb), ptr(dyb), ptr(dw), ptr(ws), stream_ptr(x.device)),
                       "rg_halo_wgrad")
             count_launch(2)
@@ -369,7 +369,7 @@ def conv_wgrad(x, dy, w_shape, stride, pad, groups=1, want_bias=False):
                          _sp_strides(xb), _sp_strides(dyb), ACT_NONE, 0.0)
         if plan is not None:
             dw = torch.zeros(tuple(w_shape), dtype=torch.float32, device=x.device)
-            with _Timed("wgrad", 2.0 * dyb.numel() * cin_g * kernel[0] * kernel[1] * kernel[2], x.device):
+            with _Timed("wgrad", 2.0 * dyb.numel() * cin_g * kernel[0] * kernel[1] * kernel[2], x.device, "igemm_wgrad_kernel"):
                 check(lib().rg_igemm_wgrad(plan.handle, ptr(xb), ptr(dyb), ptr(dw), None, None,
                                            stream_ptr(x.device)), "rg_igemm_wgrad")
             count_launch()

@@ -14,6 +14,8 @@
 #include <cuda.h>
 #include <cuda_bf16.h>
 
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "sm100_ptx.cuh"
 
@@ -34,6 +36,9 @@ struct alignas(64) HaloWgradParams {
   int n_pass, n_co_tiles, n_splits, chunks_per_split, total_chunks;
   int tiles_h, tiles_w, out_d, in_d, batch;
   int wb, slice_bytes, slice_tx, stages;
+  int kd_first, kd_step, n_kd;   // depth taps this launch covers: kd = kd_first + i*kd_step
+  int dpair;                     // 1: N = {dY[d], dY[d+1]} x 64 co -> taps kd and kd-1 in one MMA (BN = 128)
+  int planes;                    // out_d + dpair (the chunk walk starts one plane early when dpair)
   float* ws;                     // [taps][cin][cout] fp32 partial sums
 };
 
@@ -61,7 +66,7 @@ __global__ void __launch_bounds__(HW_THREADS, 1) halo_wgrad_kernel(const __grid_
   const int split = u / p.n_co_tiles;
   const int gi = pass % p.groups;
   const int q = (pass / p.groups) % p.q_chunks;
-  const int kd = pass / (p.groups * p.q_chunks);
+  const int kd = p.kd_first + p.kd_step * (pass / (p.groups * p.q_chunks));
   const int j_begin = (int)(((long long)gi * p.pairs_total) / p.groups);
   const int j_end = (int)(((long long)(gi + 1) * p.pairs_total) / p.groups);
   const int c_begin = split * p.chunks_per_split;
@@ -84,7 +89,7 @@ __global__ void __launch_bounds__(HW_THREADS, 1) halo_wgrad_kernel(const __grid_
   auto decode = [&](int c, int& n, int& d, int& h0, int& w0) {
     const int iw = c % p.tiles_w; c /= p.tiles_w;
     const int ih = c % p.tiles_h; c /= p.tiles_h;
-    d = c % p.out_d; n = c / p.out_d;
+    d = c % p.planes - p.dpair; n = c / p.planes;
     h0 = ih * HW_TH; w0 = iw * HW_TW;
   };
 
@@ -103,7 +108,8 @@ __global__ void __launch_bounds__(HW_THREADS, 1) halo_wgrad_kernel(const __grid_
         ptx::tma_load_5d(sa, &p.x_map, full(st), q * 64, w0 - p.pw, h0 - p.ph, z, n);
 #pragma unroll
         for (int s = 0; s < BN / 64; ++s)
-          ptx::tma_load_5d(sa + (uint32_t)(p.slice_bytes + s * HW_TILE_BYTES), &p.dy_map, full(st), co_tile * BN + s * 64, w0, h0, d, n);
+          ptx::tma_load_5d(sa + (uint32_t)(p.slice_bytes + s * HW_TILE_BYTES), &p.dy_map, full(st),
+                           p.dpair ? co_tile * 64 : co_tile * BN + s * 64, w0, h0, p.dpair ? d + s : d, n);
         if (++st == p.stages) { st = 0; ph ^= 1u; }
       }
     }
@@ -166,8 +172,8 @@ __global__ void __launch_bounds__(HW_THREADS, 1) halo_wgrad_kernel(const __grid_
     {
       const int per_plane = p.tiles_h * p.tiles_w;
       const int p0 = c_begin / per_plane, p1 = (c_end - 1) / per_plane;
-      for (int pl = p0; pl <= p1 && pl < p0 + p.out_d; ++pl) {
-        const int z = pl % p.out_d + kd - p.pd;
+      for (int pl = p0; pl <= p1 && pl < p0 + p.planes; ++pl) {
+        const int z = pl % p.planes - p.dpair + kd - p.pd;
         any = any || (z >= 0 && z < p.in_d);
       }
     }
@@ -176,9 +182,12 @@ __global__ void __launch_bounds__(HW_THREADS, 1) halo_wgrad_kernel(const __grid_
         const int t = 2 * j + (quad >> 1);
         if (t >= ntaps_hw) continue;                          // unpaired second half (warp-uniform)
         const int ci = q * 64 + (quad & 1) * 32 + lane;
-        float* dst = p.ws + ((size_t)(kd * ntaps_hw + t) * p.cin + ci) * p.cout + co_tile * BN;
+        float* dst0 = p.ws + ((size_t)(kd * ntaps_hw + t) * p.cin + ci) * p.cout;
 #pragma unroll 1
         for (int cb = 0; cb < BN; cb += 32) {
+          // dpair: columns 64..127 are the same 64 output channels against dY[d+1], i.e. depth tap kd-1
+          float* dst = p.dpair ? dst0 - (size_t)(cb >> 6) * ntaps_hw * p.cin * p.cout + co_tile * 64 + (cb & 63) - cb
+                               : dst0 + co_tile * BN;
           uint32_t v[32];
           ptx::tmem_ld_32x32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)((j - j_begin) * BN + cb), v);
           ptx::tmem_ld_wait();
@@ -255,7 +264,9 @@ constexpr int HW_TAIL_BYTES = 8 * (2 * HW_MAX_STAGES + 1) + 64;
 
 struct HwGeom { HaloWgradParams p; int bn; int smem_bytes; int grid; };
 
-static int hw_geometry(const rg_igemm_desc* d, HwGeom* g) {
+// variant 0: every depth tap, N = output channels.  variant 1 (cout == 64): depth taps 1,3,5,.. paired with their
+// predecessor through N = {dY[d], dY[d+1]} (full-rate N = 128 MMAs).  variant 2: the last depth tap alone (KD odd).
+static int hw_geometry(const rg_igemm_desc* d, HwGeom* g, int variant = 0) {
   RG_UNSUPPORTED(d->mode != 2, "halo wgrad: descriptor mode must be 2 (wgrad)");
   for (int i = 0; i < 3; ++i) {
     RG_UNSUPPORTED(d->stride[i] != 1, "halo wgrad: stride must be 1");
@@ -272,12 +283,15 @@ static int hw_geometry(const rg_igemm_desc* d, HwGeom* g) {
   p.pd = d->pad[0]; p.ph = d->pad[1]; p.pw = d->pad[2];
   p.cin = d->cin; p.cout = d->cout;
   g->bn = d->cout % 256 == 0 ? 256 : (d->cout % 128 == 0 ? 128 : 64);
+  p.kd_first = 0; p.kd_step = 1; p.n_kd = p.kd; p.dpair = 0;
+  if (variant == 1) { g->bn = 128; p.dpair = 1; p.kd_first = 1; p.kd_step = 2; p.n_kd = p.kd / 2; }
+  if (variant == 2) { g->bn = 64; p.kd_first = p.kd - 1; p.n_kd = 1; }
   const int nacc = 512 / g->bn;
   p.q_chunks = d->cin / 64;
   p.pairs_total = (p.kh * p.kw + 1) / 2;
   p.groups = (p.pairs_total + nacc - 1) / nacc;
-  p.n_pass = p.kd * p.q_chunks * p.groups;
-  p.n_co_tiles = d->cout / g->bn;
+  p.n_pass = p.n_kd * p.q_chunks * p.groups;
+  p.n_co_tiles = p.dpair ? d->cout / 64 : d->cout / g->bn;
   p.wb = HW_TW + p.kw - 1;
   const int hb = HW_TH + p.kh - 1;
   RG_UNSUPPORTED(p.wb > 256 || hb > 256, "halo wgrad: halo box too large");
@@ -291,7 +305,8 @@ static int hw_geometry(const rg_igemm_desc* d, HwGeom* g) {
   p.tiles_h = (d->out_dhw[1] + HW_TH - 1) / HW_TH;
   p.tiles_w = (d->out_dhw[2] + HW_TW - 1) / HW_TW;
   p.out_d = d->out_dhw[0]; p.in_d = d->in_dhw[0]; p.batch = d->n;
-  p.total_chunks = d->n * p.out_d * p.tiles_h * p.tiles_w;
+  p.planes = p.out_d + p.dpair;
+  p.total_chunks = d->n * p.planes * p.tiles_h * p.tiles_w;
   // voxel splits: about four waves of CTAs, but at least 32 chunks per CTA so the reduction epilogue stays small
   const long long base_units = (long long)p.n_pass * p.n_co_tiles;
   long long splits = (4LL * hw_num_sms()) / base_units;
@@ -357,17 +372,27 @@ int rg_halo_wgrad(const rg_igemm_desc* d, const void* x, const void* dy, float* 
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) { set_error("halo wgrad: cuTensorMapEncodeTiled failed: %d", (int)r); return RG_E_CUDA; }
   }
-  p.ws = (float*)workspace;
   const int taps = p.kd * p.kh * p.kw;
   cudaError_t e = cudaMemsetAsync(workspace, 0, rg_halo_wgrad_workspace_bytes(d), st);
   if (e != cudaSuccess) return cuda_fail(e, "cudaMemsetAsync(halo wgrad workspace)");
-  if (g.bn == 256) rc = hw_launch<256>(g, st);
-  else if (g.bn == 128) rc = hw_launch<128>(g, st);
-  else rc = hw_launch<64>(g, st);
-  if (rc) return rc;
-  RG_LAUNCH_CHECK("rg_halo_wgrad");
+  static const char* nopair = getenv("RAYGUN_B200_WGRAD_NO_DPAIR");
+  const bool dpair = d->cout == 64 && p.kd >= 4 &&     // (3-tap kernels: two short launches cost more than they gain)
+                     !(nopair && nopair[0] == '1');
+  for (int variant = dpair ? 1 : 0; variant <= (dpair ? 2 : 0); ++variant) {
+    if (variant == 2 && p.kd % 2 == 0) break;
+    HwGeom gv;
+    rc = hw_geometry(d, &gv, variant);
+    if (rc) return rc;
+    gv.p.x_map = p.x_map; gv.p.dy_map = p.dy_map;
+    gv.p.ws = (float*)workspace;
+    if (gv.bn == 256) rc = hw_launch<256>(gv, st);
+    else if (gv.bn == 128) rc = hw_launch<128>(gv, st);
+    else rc = hw_launch<64>(gv, st);
+    if (rc) return rc;
+    RG_LAUNCH_CHECK("rg_halo_wgrad");
+  }
   dim3 fg((d->cout + 31) / 32, d->cin, (taps + 31) / 32);
-  halo_wgrad_finish_kernel<<<fg, dim3(32, 8), 0, st>>>(p.ws, taps, d->cin, d->cout, dw);
+  halo_wgrad_finish_kernel<<<fg, dim3(32, 8), 0, st>>>((const float*)workspace, taps, d->cin, d->cout, dw);
   RG_LAUNCH_CHECK("rg_halo_wgrad(finish)");
   return RG_OK;
 }

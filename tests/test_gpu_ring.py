@@ -126,6 +126,8 @@ WGRAD = [
     (64, 64, (7, 1, 1), (3, 0, 0), (12, 16, 8), 1),
     (64, 64, 1, 0, (5, 8, 8), 2),
     (64, 64, (2, 4, 3), (1, 2, 1), (9, 10, 11), 1),
+    (64, 64, (4, 3, 3), (2, 1, 1), (9, 10, 11), 2),   # even KD >= 4: every depth tap handled by the depth-paired N = 128 variant
+    (128, 64, (5, 1, 3), (2, 0, 1), (7, 9, 16), 1),   # odd KD: paired taps + the last tap alone, two ci chunks
 ]
 
 
