@@ -161,6 +161,10 @@ int rg_pad3d_fwd(const rg_tensor5* xd, const void* x, const rg_tensor5* yd, void
 /* dx (zeroed by caller) += fold(dy) */
 int rg_pad3d_bwd(const rg_tensor5* dyd, const void* dy, const rg_tensor5* dxd, void* dx,
                  const int32_t lo[3], int mode, void* stream);
+/* In-place fill of the `margin`-voxel shell of a padded bf16 NDHWC buffer whose interior is already written (the
+ * producing convolution's epilogue wrote it through strides): the reference's explicit padded copy
+ * (F.pad / padding_mode="reflect", UNet.py:61-69, ResNet.py:262-270) reduced to O(surface) bytes.               */
+int rg_pad_border_fill(const rg_tensor5* bufd, void* buf, const int32_t margin[3], int mode, void* stream);
 
 /* ---- normalisation (nn.InstanceNorm3d / nn.BatchNorm3d; ResNet.py:236,284,299,334,408,417;
  *      NLayerDiscriminator.py:112,146-168; UNet.py:84-88) --------------------------------

@@ -226,7 +226,7 @@ def _igemm_ok(cin, cout, kernel, stride, groups):
 # --------------------------------------------------------------------------------------------
 # the three convolution kernels, as raw tensor functions
 # --------------------------------------------------------------------------------------------
-def conv_fprop(x, w, bias, stride, pad, groups=1, act=ACT_NONE, slope=0.0, want_stats=False, out_dtype=None):
+def conv_fprop(x, w, bias, stride, pad, groups=1, act=ACT_NONE, slope=0.0, want_stats=False, out_dtype=None, out=None):
     """y = act(conv3d(x, w) + bias) with zero padding `pad`.  Returns (y, sum, sqsum) -- the two
     per-(n,cout) statistics are None unless want_stats and the tensor-core epilogue produced them."""
     require_device(x)
@@ -238,9 +238,19 @@ def conv_fprop(x, w, bias, stride, pad, groups=1, act=ACT_NONE, slope=0.0, want_
         raise RuntimeError(f"conv3d: kernel {kernel} does not fit input {tuple(x.shape)}")
     cdt = out_dtype or K.compute_dtype()
     bias_f = bias.detach() if bias is not None else None
+    if out is not None and (tuple(out.shape) != (n, cout, *od) or out.dtype != cdt or out.stride(1) != 1):
+        out = None              # caller falls back to a copy when the result is not `out`
+
+    def _alloc(dtype):
+        if out is not None and out.dtype == dtype:
+            return out
+        if dtype == torch.bfloat16 and tuple(stride) == (1, 1, 1) and K.arena_enabled():
+            return K.empty5_arena((n, cout, *od), dtype, x.device)
+        return K.empty5((n, cout, *od), dtype, x.device)
+
     if _igemm_ok(cin_t, cout, kernel, stride, groups) and cdt == torch.bfloat16:
         xb = K.convert(x, torch.bfloat16)
-        y = K.empty5((n, cout, *od), torch.bfloat16, x.device)
+        y = _alloc(torch.bfloat16)
         rd = _ring_desc(0, n, cin_t, cout, (d, h, wd_), od, kernel, stride, pad, _sp_strides(xb), _sp_strides(y),
                         act, float(slope))
         if rd is not None:
@@ -268,13 +278,13 @@ def conv_fprop(x, w, bias, stride, pad, groups=1, act=ACT_NONE, slope=0.0, want_
             return (y, st[0], st[1]) if want_stats else (y, None, None)
     if _pw_ok(cin_t, cout, kernel, stride, pad, groups):
         xb = K.convert(x, torch.bfloat16)
-        y = K.empty5((n, cout, *od), cdt, x.device)
+        y = _alloc(cdt)
         check(lib().rg_pw_conv_fprop(C.byref(t5(xb)), ptr(xb), ptr(w.detach().contiguous()), ptr(bias_f), C.c_int(act),
                                      C.c_float(slope), C.byref(t5(y)), ptr(y), stream_ptr(x.device)), "rg_pw_conv_fprop")
         count_launch()
         stats["pointwise"] = stats.get("pointwise", 0) + 1
         return y, None, None
-    y = K.empty5((n, cout, *od), cdt, x.device)
+    y = _alloc(cdt)
     g = _geom(kernel, stride, pad, groups, act, slope)
     wc = w.detach()
     if not wc.is_contiguous():
@@ -287,7 +297,7 @@ def conv_fprop(x, w, bias, stride, pad, groups=1, act=ACT_NONE, slope=0.0, want_
 
 
 def conv_dgrad(dy, w, x_shape, stride, pad, groups=1, bias=None, act=ACT_NONE, slope=0.0, want_stats=False,
-               out_dtype=None):
+               out_dtype=None, out=None):
     """dx of the conv whose weight is `w` ([Cout,Cin/g,k..]); also ConvTranspose3d forward
     (then `bias`/`act` are the transposed conv's epilogue and x_shape its output shape)."""
     require_device(dy)
@@ -298,7 +308,10 @@ def conv_dgrad(dy, w, x_shape, stride, pad, groups=1, bias=None, act=ACT_NONE, s
     bias_f = bias.detach() if bias is not None else None
     if _igemm_ok(cin_t, cout_t, kernel, stride, groups) and cdt == torch.bfloat16:
         dyb = K.convert(dy, torch.bfloat16)
-        dx = K.empty5(tuple(x_shape), torch.bfloat16, dy.device)
+        if out is not None and tuple(out.shape) == tuple(x_shape) and out.dtype == torch.bfloat16 and out.stride(1) == 1:
+            dx = out
+        else:
+            dx = K.empty5(tuple(x_shape), torch.bfloat16, dy.device)
         rd = _ring_desc(1, n, cin_t, cout_t, tuple(x_shape[2:]), (od, oh, ow), kernel, stride, pad, _sp_strides(dx),
                         _sp_strides(dyb), act, float(slope))
         if rd is not None:

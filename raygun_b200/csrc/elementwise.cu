@@ -284,6 +284,36 @@ __global__ void __launch_bounds__(256) im2col_hw_kernel(T5 xd, const TS* __restr
   }
 }
 
+// In-place border fill of a padded NDHWC bf16 buffer whose INTERIOR a convolution epilogue has already written:
+// mirrors (reflect) or clamps (replicate) or zeroes the `m`-voxel shell, touching only O(surface) bytes instead of
+// the read + write of the whole volume an explicit pad copy costs.  One block per padded row (n, d, h).
+__global__ void __launch_bounds__(256) border_fill_kernel(T5 t, __nv_bfloat16* __restrict__ p, int md, int mh, int mw, int mode) {
+  const int cg = (int)(t.c >> 3), W = (int)t.w, H = (int)t.h, D = (int)t.d;
+  const int iD = D - 2 * md, iH = H - 2 * mh, iW = W - 2 * mw;          // interior extents
+  const long long rows = t.n * D * H;
+  for (long long row = blockIdx.x; row < rows; row += gridDim.x) {
+    const int h = (int)(row % H);
+    const long long q = row / H;
+    const int d = (int)(q % D), n = (int)(q / D);
+    bool vd, vh, vw;
+    const int sd_ = (int)pad_src(d, md, iD, mode, vd) + md, sh_ = (int)pad_src(h, mh, iH, mode, vh) + mh;
+    const bool row_interior = (sd_ == d && sh_ == h);
+    __nv_bfloat16* dst = p + n * t.sn + d * t.sd + h * t.sh;
+    const __nv_bfloat16* src = p + n * t.sn + sd_ * t.sd + sh_ * t.sh;
+    // interior rows only need their 2*mw edge voxels; border rows need the full width
+    const int nw = row_interior ? 2 * mw : W;
+    for (int j = threadIdx.x; j < nw * cg; j += blockDim.x) {
+      int w = j / cg;
+      const int c = (j - w * cg) << 3;
+      if (row_interior && w >= mw) w = W - 2 * mw + w;                 // right edge
+      const int sw_ = (int)pad_src(w, mw, iW, mode, vw) + mw;
+      float v[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      if (vd && vh && vw) ld8(src + (long long)sw_ * t.sw + c, v);
+      st8(dst + (long long)w * t.sw + c, v);
+    }
+  }
+}
+
 }  // namespace rg
 
 using namespace rg;
@@ -418,6 +448,22 @@ int rg_im2col_hw(const rg_tensor5* xd, const void* x, int kh, int kw, int ph, in
     im2col_hw_kernel<TS><<<grid_for(yd->n * yd->d * yd->h, 1, 148 * 32), 256, 0, st>>>(view(xd), (const TS*)x, kh, kw, ph, pw, view(yd), (__nv_bfloat16*)y);
   })
   RG_LAUNCH_CHECK("rg_im2col_hw");
+  return RG_OK;
+}
+
+int rg_pad_border_fill(const rg_tensor5* td, void* buf, const int32_t margin[3], int mode, void* stream) {
+  RG_CHECK_ARG(td && buf && margin, "rg_pad_border_fill: null argument");
+  RG_CHECK_ARG(mode >= RG_PAD_ZEROS && mode <= RG_PAD_REPLICATE, "rg_pad_border_fill: bad mode %d", mode);
+  RG_UNSUPPORTED(!vec_ok(td, buf), "rg_pad_border_fill: buffer must be bf16 NDHWC with C %% 8 == 0");
+  for (int i = 0; i < 3; ++i) RG_CHECK_ARG(margin[i] >= 0 && margin[i] < 30, "rg_pad_border_fill: bad margin");
+  const long long id = td->d - 2 * margin[0], ih = td->h - 2 * margin[1], iw = td->w - 2 * margin[2];
+  RG_CHECK_ARG(id >= 1 && ih >= 1 && iw >= 1, "rg_pad_border_fill: margin larger than the buffer");
+  if (mode == RG_PAD_REFLECT)
+    RG_CHECK_ARG(margin[0] < id && margin[1] < ih && margin[2] < iw, "rg_pad_border_fill: reflect margin must be smaller than the interior");
+  if (td->n * td->c == 0) return RG_OK;
+  border_fill_kernel<<<grid_for(td->n * td->d * td->h, 1, 148 * 32), 256, 0, (cudaStream_t)stream>>>(
+      view(td), (__nv_bfloat16*)buf, margin[0], margin[1], margin[2], mode);
+  RG_LAUNCH_CHECK("rg_pad_border_fill");
   return RG_OK;
 }
 

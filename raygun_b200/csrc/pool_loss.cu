@@ -1,5 +1,6 @@
 // Max-pool, nearest up-sampling, loss reductions (warp-shuffle), u8 normalise / denormalise, Adam.
 #include "common.cuh"
+#include "vec_ndhwc.cuh"
 
 namespace rg {
 
@@ -19,6 +20,36 @@ __global__ void maxpool_fwd_kernel(T5 xd, const TS* __restrict__ x, T5 yd, TD* _
           m = (v > m || v != v) ? v : m;  // NaN propagates like ATen
         }
     stf(y + yd.off(p.n, p.c, p.d, p.h, p.w), m);
+  }
+}
+
+// NDHWC bf16 fast path: one block per output row (n, d, h); a thread reduces the window of 8 channels of one output
+// voxel with 16-byte loads (HBM-bound: reads the input once, 32-bit index arithmetic only).
+__global__ void __launch_bounds__(256) vec_maxpool_fwd_kernel(T5 xd, const __nv_bfloat16* __restrict__ x, T5 yd,
+                                                              __nv_bfloat16* __restrict__ y, int fd, int fh, int fw) {
+  const int cg = (int)(yd.c >> 3), W = (int)yd.w, H = (int)yd.h, D = (int)yd.d;
+  const long long rows = yd.n * D * H;
+  for (long long row = blockIdx.x; row < rows; row += gridDim.x) {
+    const int h = (int)(row % H);
+    const long long t = row / H;
+    const int d = (int)(t % D), n = (int)(t / D);
+    const __nv_bfloat16* xrow = x + n * xd.sn + (long long)d * fd * xd.sd + (long long)h * fh * xd.sh;
+    __nv_bfloat16* yrow = y + n * yd.sn + d * yd.sd + h * yd.sh;
+    for (int j = threadIdx.x; j < W * cg; j += blockDim.x) {
+      const int w = j / cg, c = (j - w * cg) << 3;
+      float m[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) m[k] = -INFINITY;
+      for (int a = 0; a < fd; ++a)
+        for (int b = 0; b < fh; ++b)
+          for (int e = 0; e < fw; ++e) {
+            float v[8];
+            ld8(xrow + a * xd.sd + b * xd.sh + (long long)(w * fw + e) * xd.sw + c, v);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) m[k] = (v[k] > m[k] || v[k] != v[k]) ? v[k] : m[k];
+          }
+      st8(yrow + (long long)w * yd.sw + c, m);
+    }
   }
 }
 
@@ -184,6 +215,12 @@ int rg_maxpool3d_fwd(const rg_tensor5* xd, const void* x, const int32_t f[3], co
   long long total = view(yd).numel();
   if (total == 0) return RG_OK;
   cudaStream_t st = (cudaStream_t)stream;
+  if (vec_ok(xd, x) && vec_ok(yd, y)) {
+    vec_maxpool_fwd_kernel<<<grid_for(yd->n * yd->d * yd->h, 1, 148 * 32), 256, 0, st>>>(
+        view(xd), (const __nv_bfloat16*)x, view(yd), (__nv_bfloat16*)y, f[0], f[1], f[2]);
+    RG_LAUNCH_CHECK("rg_maxpool3d_fwd(vec)");
+    return RG_OK;
+  }
   int grid = grid_for(total, 256);
   bool ci = channels_inner(yd);
   RG_DISPATCH_FLOAT(xd->dtype, TS, RG_DISPATCH_FLOAT(yd->dtype, TD, {

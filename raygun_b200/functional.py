@@ -55,8 +55,8 @@ class _Conv3d(torch.autograd.Function):
     Returns (y, sum, sqsum): the statistics feed the following norm layer (non-differentiable)."""
 
     @staticmethod
-    def forward(ctx, x, w, bias, stride, pad, groups, act, slope, want_stats):
-        y, s, q = CV.conv_fprop(x, w, bias, stride, pad, groups, act, slope, want_stats)
+    def forward(ctx, x, w, bias, stride, pad, groups, act, slope, want_stats, out=None):
+        y, s, q = CV.conv_fprop(x, w, bias, stride, pad, groups, act, slope, want_stats, out=out)
         ctx.geom = (stride, pad, groups, act, slope)
         ctx.has_bias = bias is not None
         ctx.save_for_backward(x, w, y if act != ACT_NONE else None)
@@ -78,7 +78,7 @@ class _Conv3d(torch.autograd.Function):
             dw, db = CV.conv_wgrad(x, dy, w.shape, stride, pad, groups, want_bias=ctx.has_bias)
             if not ctx.needs_input_grad[1]:
                 dw = None
-        return dx, dw, db, None, None, None, None, None, None
+        return dx, dw, db, None, None, None, None, None, None, None
 
 
 
@@ -89,13 +89,13 @@ class _StemConv3d(torch.autograd.Function):
     The folded input is recomputed in backward instead of being saved."""
 
     @staticmethod
-    def forward(ctx, x, w, bias, pad, act, slope, want_stats):
+    def forward(ctx, x, w, bias, pad, act, slope, want_stats, out=None):
         cout, cin, kd, kh, kw = w.shape
         cf = cin * kh * kw
         xc = K.im2col_hw(x, kh, kw, pad[1], pad[2], 64)
         w2 = w.detach().permute(0, 2, 1, 3, 4).reshape(cout, kd, cf)          # [co][kd][(ci,kh,kw)]
         w2 = torch.nn.functional.pad(w2, (0, 64 - cf)).permute(0, 2, 1).reshape(cout, 64, kd, 1, 1).contiguous()
-        y, s, q = CV.conv_fprop(xc, w2, bias, (1, 1, 1), (pad[0], 0, 0), 1, act, slope, want_stats)
+        y, s, q = CV.conv_fprop(xc, w2, bias, (1, 1, 1), (pad[0], 0, 0), 1, act, slope, want_stats, out=out)
         ctx.cfg = (pad, act, slope, tuple(w.shape), tuple(w2.shape))
         ctx.has_bias = bias is not None
         ctx.save_for_backward(x, w, y if act != ACT_NONE else None)
@@ -119,7 +119,7 @@ class _StemConv3d(torch.autograd.Function):
             dw2, db = CV.conv_wgrad(xc, dy, w2shape, (1, 1, 1), (pad[0], 0, 0), 1, want_bias=ctx.has_bias)
             dw = dw2.reshape(cout, 64, kd)[:, : cin * kh * kw].reshape(cout, cin, kh, kw, kd).permute(0, 1, 4, 2, 3)
             dw = dw.contiguous() if ctx.needs_input_grad[1] else None
-        return dx, dw, db, None, None, None, None
+        return dx, dw, db, None, None, None, None, None
 
 
 def _stem_eligible(x, w, stride, groups):
@@ -128,11 +128,15 @@ def _stem_eligible(x, w, stride, groups):
             and cin % 64 != 0 and cin * kh * kw <= 64 and cout % 64 == 0 and kd <= 8)
 
 
-def conv3d(x, w, bias=None, stride=1, padding=0, groups=1, act=ACT_NONE, slope=0.0, want_stats=False):
+def conv3d(x, w, bias=None, stride=1, padding=0, groups=1, act=ACT_NONE, slope=0.0, want_stats=False, out=None):
+    """`out` (inference only): a preallocated NDHWC view the kernel should write into, e.g. a channel slice of the
+    skip-connection concat buffer; the result IS `out` when the kernel could honour it (callers check identity)."""
+    if torch.is_grad_enabled():
+        out = None
     if _stem_eligible(x, w, _t3(stride), int(groups)):
-        y, s, q = _StemConv3d.apply(x, w, bias, _t3(padding), act, float(slope), bool(want_stats))
+        y, s, q = _StemConv3d.apply(x, w, bias, _t3(padding), act, float(slope), bool(want_stats), out)
     else:
-        y, s, q = _Conv3d.apply(x, w, bias, _t3(stride), _t3(padding), int(groups), act, float(slope), bool(want_stats))
+        y, s, q = _Conv3d.apply(x, w, bias, _t3(stride), _t3(padding), int(groups), act, float(slope), bool(want_stats), out)
     if want_stats:
         return y, (s, q) if s.numel() else None
     return y
@@ -143,12 +147,12 @@ class _ConvTranspose3d(torch.autograd.Function):
     Forward is the data-gradient kernel of the conv that shares the weight [Cin_T, Cout_T, k..]."""
 
     @staticmethod
-    def forward(ctx, x, w, bias, stride, pad, out_pad, act, slope, want_stats):
+    def forward(ctx, x, w, bias, stride, pad, out_pad, act, slope, want_stats, out=None):
         n, cin, d, h, wd_ = x.shape
         k = w.shape[2:]
         osz = [(i - 1) * s - 2 * p + kk + op for i, s, p, kk, op in zip((d, h, wd_), stride, pad, k, out_pad)]
         y, s, q = CV.conv_dgrad(x, w, (n, w.shape[1], *osz), stride, pad, 1, bias=bias, act=act, slope=slope,
-                                want_stats=want_stats)
+                                want_stats=want_stats, out=out)
         ctx.geom = (stride, pad, act, slope)
         ctx.has_bias = bias is not None
         ctx.save_for_backward(x, w, y if act != ACT_NONE else None)
@@ -174,13 +178,15 @@ class _ConvTranspose3d(torch.autograd.Function):
                 db = s
             if not ctx.needs_input_grad[1]:
                 dw = None
-        return dx, dw, db, None, None, None, None, None, None
+        return dx, dw, db, None, None, None, None, None, None, None
 
 
 def conv_transpose3d(x, w, bias=None, stride=1, padding=0, output_padding=0, act=ACT_NONE, slope=0.0,
-                     want_stats=False):
+                     want_stats=False, out=None):
+    if torch.is_grad_enabled():
+        out = None
     y, s, q = _ConvTranspose3d.apply(x, w, bias, _t3(stride), _t3(padding), _t3(output_padding), act, float(slope),
-                                     bool(want_stats))
+                                     bool(want_stats), out)
     if want_stats:
         return y, (s, q) if s.numel() else None
     return y

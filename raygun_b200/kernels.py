@@ -59,6 +59,49 @@ def empty5(shape, dtype, device):
     return torch.empty(shape, dtype=dtype, device=device)
 
 
+# ---- pad arenas (inference) -------------------------------------------------------------------------
+# Under torch.no_grad() the bf16 convolutions write their output into the INTERIOR of a buffer that is one voxel
+# larger on every side.  A following convolution with reflect / replicate padding <= 1 then only mirrors the thin
+# shell in place (rg_pad_border_fill) instead of copying the whole tensor into a padded one -- the explicit
+# `F.pad` + conv of the reference (UNet.py:61-69) costs a read + write of every activation.
+ARENA_MARGIN = 1
+
+
+def arena_enabled() -> bool:
+    import os
+    return (not torch.is_grad_enabled()) and get_precision() == "bf16" and os.environ.get("RAYGUN_B200_ARENA", "1") != "0"
+
+
+def empty5_arena(shape, dtype, device, margin=ARENA_MARGIN):
+    """Interior view (logical `shape`) of a freshly allocated NDHWC buffer with `margin` extra voxels per side."""
+    n, c, d, h, w = shape
+    m = margin
+    full = empty5((n, c, d + 2 * m, h + 2 * m, w + 2 * m), dtype, device)
+    full._rg_arena = m
+    return full[:, :, m:m + d, m:m + h, m:m + w]
+
+
+def arena_of(x, lo, hi):
+    """(full_buffer, margin) when x is exactly the interior of a pad arena whose margin covers lo / hi, else None."""
+    b = x._base
+    m = getattr(b, "_rg_arena", None) if b is not None else None
+    if m is None or max(max(lo), max(hi)) > m:
+        return None
+    n, c, d, h, w = x.shape
+    if tuple(b.shape) != (n, c, d + 2 * m, h + 2 * m, w + 2 * m) or x.stride() != b.stride():
+        return None
+    bs = b.stride()
+    if x.storage_offset() != b.storage_offset() + m * (bs[2] + bs[3] + bs[4]):
+        return None
+    return b, m
+
+
+def border_fill(full, margin, mode):
+    check(lib().rg_pad_border_fill(C.byref(t5(full)), ptr(full), i3((margin,) * 3), C.c_int(mode), stream_ptr(full.device)),
+          "rg_pad_border_fill")
+    count_launch()
+
+
 def is_ndhwc(t: torch.Tensor) -> bool:
     n, c, d, h, w = t.shape
     return t.dtype == torch.bfloat16 and tuple(t.stride()) == (d * h * w * c, 1, h * w * c, w * c, c)

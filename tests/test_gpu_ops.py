@@ -306,3 +306,38 @@ def test_vec_act_copy_cropcat_bf16_ndhwc():
     _close(y, y_ref, 0.0, "vec cropcat")
     _close(ag.grad, ga, 0.0, "vec cropcat da")
     _close(bg.grad, gb, 0.0, "vec cropcat db")
+
+
+DEV = "cuda:0"
+
+
+@pytest.mark.parametrize("mode", ["reflect", "replicate", "zeros"])
+def test_border_fill_equals_explicit_padding(mode):
+    """rg_pad_border_fill on the interior-written arena == F.pad of the interior (bit-exact copy of bf16 values)."""
+    from raygun_b200 import functional as F
+    from raygun_b200 import kernels as K
+    torch.manual_seed(5)
+    x = torch.randn(2, 16, 5, 7, 9).bfloat16()
+    inner = K.empty5_arena(tuple(x.shape), torch.bfloat16, torch.device(DEV), margin=2)
+    inner.copy_(x.to(DEV))
+    full = inner._base
+    full_before = full.clone()
+    K.border_fill(full, 2, F.PAD_MODES[mode])
+    tmode = {"zeros": "constant"}.get(mode, mode)
+    ref = torch.nn.functional.pad(x.float(), (2,) * 6, mode=tmode).bfloat16()
+    assert torch.equal(full.cpu(), ref)
+    assert torch.equal(full[:, :, 2:-2, 2:-2, 2:-2].cpu(), full_before[:, :, 2:-2, 2:-2, 2:-2].cpu())
+    assert K.arena_of(inner, (1, 1, 1), (2, 2, 2)) is not None and K.arena_of(inner, (3, 0, 0), (0, 0, 0)) is None
+    assert K.arena_of(inner[:, :8], (1, 1, 1), (1, 1, 1)) is None          # a channel slice is not the arena interior
+
+
+def test_vectorised_maxpool_matches_torch_on_strided_ndhwc_views():
+    from raygun_b200 import kernels as K
+    torch.manual_seed(6)
+    x = torch.randn(2, 24, 9, 10, 12).bfloat16()
+    xg = x.to(DEV).contiguous(memory_format=torch.channels_last_3d)
+    for f in ((2, 2, 2), (1, 2, 3), (3, 2, 1)):
+        ref = torch.nn.functional.max_pool3d(x.float(), f, f)
+        assert torch.equal(K.maxpool_fwd(xg, f).float().cpu(), ref)
+        sl = xg[:, 8:24]                                                     # channel slice: voxel stride 24, 16 channels
+        assert torch.equal(K.maxpool_fwd(sl, f).float().cpu(), ref[:, 8:24])
