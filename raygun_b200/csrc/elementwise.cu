@@ -269,6 +269,10 @@ __global__ void __launch_bounds__(256) im2col_hw_kernel(T5 xd, const TS* __restr
     __nv_bfloat16* yrow = y + n * yd.sn + d * yd.sd + h * yd.sh;
     for (int j = threadIdx.x; j < W * cg; j += blockDim.x) {
       const int w = j / cg, c0 = (j - w * cg) << 3;
+      if (c0 >= cvalid) {             // padding channels of the folded layout: plain zero store
+        *reinterpret_cast<uint4*>(yrow + (long long)w * yd.sw + c0) = make_uint4(0u, 0u, 0u, 0u);
+        continue;
+      }
       int b = c0 % kw, tt = c0 / kw, a = tt % kh, ci = tt / kh;
       float v[8];
 #pragma unroll

@@ -11,35 +11,51 @@ constexpr int PW_MAX_COUT = 4;
 
 struct PwW { const float* w; const float* bias; int cin, cout; };
 
-// threads t*cg .. t*cg+cg-1 (cg = Cin/8, a power of two <= 32) share one voxel
+// One block per row (n, d, h); threads j*cg .. j*cg+cg-1 (cg = Cin/8, a power of two <= 32) share one voxel of the
+// row.  A thread keeps its channel group for the whole kernel, so its weights live in registers and the only index
+// arithmetic per 16-byte load is a shift (rows may be strided views: pad arenas, crops).
 template <typename TY>
-__global__ void pw_fprop_kernel(PwW pw, T5 xd, const __nv_bfloat16* __restrict__ x, T5 yd, TY* __restrict__ y, int act,
-                                float slope) {
+__global__ void __launch_bounds__(256) pw_fprop_kernel(PwW pw, T5 xd, const __nv_bfloat16* __restrict__ x, T5 yd,
+                                                       TY* __restrict__ y, int act, float slope) {
   const int cg = pw.cin >> 3;
-  const long long vox_total = xd.n * xd.d * xd.h * xd.w;
-  const long long total = vox_total * cg;
-  const long long stride = (long long)gridDim.x * blockDim.x;     // multiple of 32 -> multiple of cg
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; (i & ~31LL) < total; i += stride) {   // warp-uniform trip count
-    const bool live = i < total;
-    float acc[PW_MAX_COUT] = {0.f, 0.f, 0.f, 0.f};
-    VIdx p;
-    if (live) {
-      p = vunravel(i, xd);
-      float v[8];
-      ld8(x + voff(xd, p.n, p.d, p.h, p.w, p.c), v);
-      for (int co = 0; co < pw.cout; ++co) {
-        float a = 0.f;
+  const int lg = 31 - __clz(cg);
+  const int cgi = threadIdx.x & (cg - 1), c = cgi << 3;
+  float wr[PW_MAX_COUT][8];
 #pragma unroll
-        for (int k = 0; k < 8; ++k) a = fmaf(v[k], __ldg(pw.w + co * pw.cin + p.c + k), a);
-        acc[co] = a;
+  for (int co = 0; co < PW_MAX_COUT; ++co)
+#pragma unroll
+    for (int k = 0; k < 8; ++k) wr[co][k] = co < pw.cout ? pw.w[co * pw.cin + c + k] : 0.f;
+  float br[PW_MAX_COUT];
+#pragma unroll
+  for (int co = 0; co < PW_MAX_COUT; ++co) br[co] = (pw.bias && co < pw.cout) ? pw.bias[co] : 0.f;
+  const int W = (int)xd.w, H = (int)xd.h, D = (int)xd.d;
+  const long long rows = xd.n * D * H;
+  const int items = W << lg, items_up = (items + 31) & ~31;        // warp-uniform trip count for the shuffles
+  for (long long row = blockIdx.x; row < rows; row += gridDim.x) {
+    const int h = (int)(row % H);
+    const long long t = row / H;
+    const int d = (int)(t % D), n = (int)(t / D);
+    const __nv_bfloat16* xrow = x + n * xd.sn + d * xd.sd + h * xd.sh + c;
+    TY* yrow = y + n * yd.sn + d * yd.sd + h * yd.sh;
+    for (int j = threadIdx.x; j < items_up; j += blockDim.x) {
+      const bool live = j < items;
+      const int w = j >> lg;
+      float acc[PW_MAX_COUT] = {0.f, 0.f, 0.f, 0.f};
+      if (live) {
+        float v[8];
+        ld8(xrow + (long long)w * xd.sw, v);
+#pragma unroll
+        for (int co = 0; co < PW_MAX_COUT; ++co)
+#pragma unroll
+          for (int k = 0; k < 8; ++k) acc[co] = fmaf(v[k], wr[co][k], acc[co]);
       }
-    }
-    for (int o = cg >> 1; o > 0; o >>= 1)
-      for (int co = 0; co < pw.cout; ++co) acc[co] += __shfl_xor_sync(0xffffffffu, acc[co], o);
-    if (live && p.c == 0) {
-      for (int co = 0; co < pw.cout; ++co) {
-        float v = acc[co] + (pw.bias ? __ldg(pw.bias + co) : 0.f);
-        stf(y + yd.off(p.n, co, p.d, p.h, p.w), act_apply(v, act, slope));
+      for (int o = cg >> 1; o > 0; o >>= 1)
+#pragma unroll
+        for (int co = 0; co < PW_MAX_COUT; ++co)
+          if (co < pw.cout) acc[co] += __shfl_xor_sync(0xffffffffu, acc[co], o);
+      if (live && cgi == 0) {
+        for (int co = 0; co < pw.cout; ++co)
+          stf(yrow + co * yd.sc + (long long)w * yd.sw, act_apply(acc[co] + br[co], act, slope));
       }
     }
   }
@@ -136,7 +152,7 @@ int rg_pw_conv_fprop(const rg_tensor5* xd, const void* x, const float* w, const 
   if (total == 0) return RG_OK;
   cudaStream_t st = (cudaStream_t)stream;
   RG_DISPATCH_FLOAT(yd->dtype, TY, {
-    pw_fprop_kernel<TY><<<grid_for(total, 256), 256, 0, st>>>(pw, view(xd), (const __nv_bfloat16*)x, view(yd), (TY*)y, act, slope);
+    pw_fprop_kernel<TY><<<grid_for(xd->n * xd->d * xd->h, 1, 148 * 32), 256, 0, st>>>(pw, view(xd), (const __nv_bfloat16*)x, view(yd), (TY*)y, act, slope);
   })
   RG_LAUNCH_CHECK("rg_pw_conv_fprop");
   return RG_OK;

@@ -40,23 +40,72 @@ def rank_blocks(origins, rank=0, world=1):
     return origins[rank::world]
 
 
-def read_block(volume_u8: torch.Tensor, origin, read_shape, context, device, scale=2.0, shift=-1.0, dtype=None):
-    """Fetch one read block as a normalised (1,1,d,h,w) device tensor; parts outside the volume are mirrored."""
+def _block_slices(volume_shape, origin, read_shape, context):
     lo_pad, hi_pad, sl = [], [], []
-    for o, r, c, v in zip(origin, read_shape, context, volume_u8.shape):
+    for o, r, c, v in zip(origin, read_shape, context, volume_shape):
         a, b = o - c, o - c + r
         lo, hi = max(0, -a), max(0, b - v)
         lo_pad.append(lo)
         hi_pad.append(hi)
         sl.append(slice(a + lo, b - hi))
-    sub = volume_u8[tuple(sl)]
+    return tuple(sl), tuple(lo_pad), tuple(hi_pad)
+
+
+def read_block(volume_u8: torch.Tensor, origin, read_shape, context, device, scale=2.0, shift=-1.0, dtype=None, stage=None):
+    """Fetch one read block as a normalised (1,1,d,h,w) device tensor; parts outside the volume are mirrored.
+    `stage`: optional pinned uint8 scratch (>= block size) so the strided host sub-volume crosses PCIe as ONE
+    asynchronous pinned copy instead of a pageable one."""
+    sl, lo_pad, hi_pad = _block_slices(volume_u8.shape, origin, read_shape, context)
+    sub = volume_u8[sl]
     if not sub.is_cuda:
-        sub = sub.contiguous().to(device, non_blocking=True)
+        if stage is not None:
+            st = stage[: sub.numel()].view(sub.shape)
+            st.copy_(sub)                                   # host gather (strided -> contiguous, pinned)
+            sub = st.to(device, non_blocking=True)
+        else:
+            sub = sub.contiguous().to(device, non_blocking=True)
     x = K.u8_normalise(sub.contiguous(), scale, shift, dtype or torch.float32)[None, None]
     if any(lo_pad) or any(hi_pad):
         ok = all(p < s for p, s in zip(lo_pad, x.shape[2:])) and all(p < s for p, s in zip(hi_pad, x.shape[2:]))
         x = F.pad3d(x, tuple(lo_pad), tuple(hi_pad), "reflect" if ok else "replicate")
     return x
+
+
+class _HostRing:
+    """A few pinned staging buffers with one CUDA event each: the host may run ahead of the GPU by len(ring) blocks
+    (gather block k+1 / scatter block k-1 while block k computes) without reusing a buffer that is still in flight."""
+
+    def __init__(self, nbytes, depth, device):
+        self.bufs = [torch.empty(nbytes, dtype=torch.uint8).pin_memory() for _ in range(depth)]
+        self.events = [None] * depth
+        self.pending = [None] * depth
+        self.i = 0
+        self.device = device
+
+    def acquire(self):
+        k = self.i
+        self.i = (self.i + 1) % len(self.bufs)
+        self.retire(k)
+        return k, self.bufs[k]
+
+    def retire(self, k):
+        if self.events[k] is not None:
+            self.events[k].synchronize()
+            self.events[k] = None
+        if self.pending[k] is not None:          # deferred host scatter of a finished device->host copy
+            dst, src = self.pending[k]
+            dst.copy_(src)
+            self.pending[k] = None
+
+    def release_after_gpu(self, k, pending=None):
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(self.device))
+        self.events[k] = ev
+        self.pending[k] = pending
+
+    def drain(self):
+        for k in range(len(self.bufs)):
+            self.retire(k)
 
 
 @torch.no_grad()
@@ -77,8 +126,18 @@ def predict_volume(model, volume_u8: torch.Tensor, read_shape, write_shape, out:
     was_training = model.training
     model.eval()
     done = vox = 0
+    host_in = not volume_u8.is_cuda and volume_u8.is_pinned()
+    host_out = not out.is_cuda
+    nbytes = read_shape[0] * read_shape[1] * read_shape[2]
+    ring_in = _HostRing(nbytes, 3, device) if host_in else None
+    ring_out = _HostRing(write_shape[0] * write_shape[1] * write_shape[2], 3, device) if host_out else None
     for origin in rank_blocks(block_origins(volume_u8.shape, write_shape, read_shape, fit), rank, world):
-        x = read_block(volume_u8, origin, read_shape, context, device, *scale_shift, dtype=dtype)
+        if ring_in is not None:
+            k, stage = ring_in.acquire()
+            x = read_block(volume_u8, origin, read_shape, context, device, *scale_shift, dtype=dtype, stage=stage)
+            ring_in.release_after_gpu(k)
+        else:
+            x = read_block(volume_u8, origin, read_shape, context, device, *scale_shift, dtype=dtype)
         y = model(x)
         y = y[0] if isinstance(y, (list, tuple)) else y
         if tuple(y.shape[2:]) == read_shape:          # 'same' network: crop the halo (worker.py:124-129)
@@ -90,9 +149,19 @@ def predict_volume(model, volume_u8: torch.Tensor, read_shape, write_shape, out:
         y = y[:, :1, : ext[0], : ext[1], : ext[2]]
         blk = K.denorm_clamp_u8(y)[0, 0]               # *255, clamp, truncating cast -- on the device
         dst = out[origin[0]: origin[0] + ext[0], origin[1]: origin[1] + ext[1], origin[2]: origin[2] + ext[2]]
-        dst.copy_(blk, non_blocking=True)
+        if ring_out is not None:
+            k, stage = ring_out.acquire()
+            st = stage[: blk.numel()].view(blk.shape)
+            st.copy_(blk, non_blocking=True)           # one pinned D2H; scattered into `out` when the buffer is reused
+            ring_out.release_after_gpu(k, pending=(dst, st))
+        else:
+            dst.copy_(blk, non_blocking=True)
         done += 1
         vox += ext[0] * ext[1] * ext[2]
+    if ring_out is not None:
+        ring_out.drain()
+    if ring_in is not None:
+        ring_in.drain()
     torch.cuda.synchronize(device)
     model.train(was_training)
     return out, done, vox
