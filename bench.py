@@ -152,9 +152,24 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    batch, side, n_blocks, ngf = WORKLOADS[args.workload]
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
+    if args.workload == "cfg4":
+        step, vox = unet_cpu_fn(64)
+        step()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            step()
+        dt = (time.perf_counter() - t0) / args.steps
+        sample = "cfg1: G-UNet forward on one 1x1x64^3 patch per step, fp32 (fully convolutional; full workload is blockwise 256^3 reads)"
+        print(json.dumps(dict(metric="generator_inference_voxels_per_sec", value=vox / dt, unit="voxels/s", impl="reference",
+                              n_gpus=args.gpus, steps=args.steps, warmup=1, ms_per_step=dt * 1e3, higher_is_better=True,
+                              scaling="strong", vs_baseline=None, dtype="f32", data="synthetic",
+                              config=dict(workload="cfg4: blockwise G-UNet prediction, CPU oracle port", sample=sample),
+                              cpu_baseline=dict(value=vox / dt, unit="voxels/s", cores=cores, kind="port", sample=sample),
+                              e2e=dict(value=vox / dt, unit="voxels/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0))))
+        return
+    batch, side, n_blocks, ngf = WORKLOADS[args.workload]
     sample_side = 48 if side >= 128 else 32
     step, vox = cpu_step_fn(n_blocks, ngf, sample_side)
     for _ in range(max(1, min(args.warmup, 1))):
@@ -364,17 +379,151 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
+# ---------------------------------------------------------------------------------------------
+# cfg4: blockwise G-UNet prediction (generator inference voxels/s), blocks sharded over ranks, no collective
+# ---------------------------------------------------------------------------------------------
+UNET_FLOP_PER_VOXEL = 1.850e6          # G-UNet forward, algorithmic (halo recompute is overhead, not credit)
+
+
+def unet_cpu_fn(side=64):
+    """cfg1: the reference-runnable anchor -- G-UNet forward on a 1x1x64^3 patch, fp32, host cores (oracle port)."""
+    from oracle import restate as O
+    from raygun_b200.cyclegan import make_generator
+    torch.manual_seed(42)
+    with contextlib.redirect_stdout(sys.stderr):
+        g = make_generator("unet", dict(input_nc=1, output_nc=1, ngf=64, fmap_inc_factor=2, num_downs=3,
+                                        padding_type="same", final_activation="Tanh"))
+    sd = {k: v.detach() for k, v in g.state_dict().items()}
+    spec = O.unet_spec(input_nc=1, ngf=64, fmap_inc_factor=2, downsample_factors=[(2, 2, 2)] * 2, padding_type="same")
+    x = O.u8_normalise(synth_batch(1, side, 42))
+
+    def step():
+        with torch.no_grad():
+            return O.generator_forward(sd, "unet", spec, x, final_activation="Tanh")
+
+    return step, side ** 3
+
+
+def run_predict(args):
+    import torch.distributed as dist
+
+    import raygun_b200 as rb
+    from raygun_b200 import _C
+    from raygun_b200 import conv as CV
+    from raygun_b200 import predict as P
+    from raygun_b200.cyclegan import make_generator
+    from raygun_b200.synth import em_like_u8
+    import numpy as np
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (raygun_b200 has no CPU path; use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    rb.set_precision("bf16")
+    R, W = 256, 208                                    # read / write block (halo 24 >= 22, origins = 0 mod 4: SURVEY 8c)
+    nb = (4, 4, 2)                                     # write blocks per axis: 32 blocks, a 880 x 880 x 464 volume
+    shape = tuple(n * W + (R - W) for n in nb)
+    torch.manual_seed(42)
+    with contextlib.redirect_stdout(sys.stderr):
+        g = make_generator("unet", dict(input_nc=1, output_nc=1, ngf=64, fmap_inc_factor=2, num_downs=3,
+                                        padding_type="same", final_activation="Tanh")).to(dev).eval()
+    tile = em_like_u8((232, 220, 220), seed=42)        # synthetic EM-like texture, mirrored-tiled to the volume size
+    reps = [-(-s // t) for s, t in zip(shape, tile.shape)]
+    vol_np = np.tile(np.concatenate([tile, tile[::-1]], 0), (reps[0], 1, 1))[: shape[0]]
+    vol_np = np.tile(np.concatenate([vol_np, vol_np[:, ::-1]], 1), (1, reps[1], 1))[:, : shape[1]]
+    vol_np = np.tile(np.concatenate([vol_np, vol_np[:, :, ::-1]], 2), (1, 1, reps[2]))[:, :, : shape[2]]
+    vol = torch.from_numpy(np.ascontiguousarray(vol_np)).pin_memory()
+    out = torch.zeros_like(vol).pin_memory()
+    vol_dev = vol.to(dev)
+    out_dev = torch.zeros_like(vol_dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            r = fn()
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1) / steps
+        if world > 1:
+            t = torch.tensor([ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t)
+        return ms, r
+
+    resident = lambda: P.predict_volume(g, vol_dev, (R,) * 3, (W,) * 3, out=out_dev, rank=rank, world=world, dtype=torch.bfloat16)
+    through_host = lambda: P.predict_volume(g, vol, (R,) * 3, (W,) * 3, out=out, rank=rank, world=world, dtype=torch.bfloat16)
+    for _ in range(max(1, min(args.warmup, 3)) if rank >= 0 else 0):
+        resident()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = _C.launch_count
+    ms, (_, nblk, vox) = timed(resident, args.steps)
+    launches = (_C.launch_count - l0) // args.steps
+    clocks = sampler.stop() if rank == 0 else None
+    ms_e2e, _ = timed(through_host, args.steps)
+    tot = torch.tensor([float(vox), float(nblk)], device=dev)
+    if world > 1:
+        dist.all_reduce(tot)
+    vox_all, nblk_all = float(tot[0]), int(tot[1])
+    if rank == 0:
+        peaks = load_peaks()
+        alg = vox_all * UNET_FLOP_PER_VOXEL / (ms * 1e-3) / 1e12
+        exe = nblk_all * R ** 3 * UNET_FLOP_PER_VOXEL / (ms * 1e-3) / 1e12
+        cores = os.cpu_count() or 1
+        torch.set_num_threads(cores)
+        cstep, cvox = unet_cpu_fn(64)
+        cstep()
+        t0 = time.perf_counter()
+        cstep()
+        cdt = time.perf_counter() - t0
+        out_line = dict(metric="generator_inference_voxels_per_sec", value=vox_all / (ms * 1e-3), unit="voxels/s", n_gpus=world,
+                        steps=args.steps, warmup=max(1, min(args.warmup, 3)), ms_per_step=ms, higher_is_better=True,
+                        scaling="strong", vs_baseline=None, dtype="bf16", data="synthetic",
+                        config=dict(workload=f"cfg4: blockwise G-UNet prediction, read {R}^3 / write {W}^3 (halo 24), "
+                                             f"{nblk_all} blocks of a {shape[0]}x{shape[1]}x{shape[2]} uint8 volume per step",
+                                    l2="every block's activations (GBs) >> 126 MB L2; no explicit flush",
+                                    parallelism=f"blocks round-robin over {world} ranks, no collective"),
+                        e2e=dict(value=vox_all / (ms_e2e * 1e-3), unit="voxels/s", ms_per_step=ms_e2e,
+                                 h2d_bytes_per_step=int(nblk_all * R ** 3), d2h_bytes_per_step=int(vox_all)),
+                        gpu_launches=int(launches),
+                        roofline=dict(bound="tensor", kernel="whole block pipeline (ring_conv_kernel dominant)", achieved=alg,
+                                      executed_incl_halo=exe, peak=peaks["tf_sustained"], unit="TFLOP/s",
+                                      frac=alg / peaks["tf_sustained"], frac_executed=exe / peaks["tf_sustained"],
+                                      peak_kind=f"{peaks['source']} sustained bf16 (burst {peaks['tf_burst']})", traffic=None),
+                        cpu_baseline=dict(value=cvox / cdt, unit="voxels/s", cores=cores, kind="port",
+                                          sample="cfg1: G-UNet forward on 1x1x64^3, fp32, oracle/restate.py, 1 warm-up + 1 timed"),
+                        clocks=clocks, conv_paths=dict(CV.stats))
+        print(json.dumps(out_line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS) + ["cfg4"])
     ap.add_argument("--no-graph", action="store_true", help="launch every kernel eagerly instead of replaying one CUDA graph")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
+    elif args.workload == "cfg4":
+        run_predict(args)
     else:
         run_ours(args)
 
