@@ -10,7 +10,7 @@
 // A CTA = (pass, output-channel tile, voxel split); a pass = one kd, one 64-channel ci chunk and up to 512/BN tap
 // pairs whose accumulators fill TMEM.  Partial sums go to an fp32 workspace laid out [tap][ci][co] with 16-byte vector
 // reductions; a final kernel transposes it into the checkpoint layout [co][ci][kd][kh][kw].
-// Warp roles: warp 0 = TMA producer, warp 1 = MMA issuer (convergent, one elected lane), warps 2-5 = epilogue.
+// Warp roles: warp 0 = TMA producer, warp 1 = MMA issuer (one elected thread), warps 2-5 = epilogue.
 #include <cuda.h>
 #include <cuda_bf16.h>
 
@@ -114,8 +114,9 @@ __global__ void __launch_bounds__(HW_THREADS, 1) halo_wgrad_kernel(const __grid_
       }
     }
   } else if (warp == 1) {
-    // ================= MMA issuer (whole warp convergent; one elected lane issues) =================
-    const uint32_t lead = ptx::elect_one_sync() ? 1u : 0u;
+    // ================= MMA issuer: one elected thread runs the loop (inside an elect.sync region ptxas computes the
+    // descriptors in the uniform datapath; see the note in ring_conv_sm100.cu: the loop is issue-bound otherwise) ======
+    if (ptx::elect_one_sync()) {
     constexpr uint32_t idesc = ptx::idesc_bf16(128, BN, 1, 1);          // both operands MN-major
     const uint32_t sbo_a = (uint32_t)(p.wb * 128);
     const uint32_t b_hi = ((1024u >> 4) & 0x3FFFu) | (1u << 14) | (2u << 29);
@@ -150,17 +151,15 @@ __global__ void __launch_bounds__(HW_THREADS, 1) halo_wgrad_kernel(const __grid_
         if (jj < npairs) {
           const uint32_t a_lo0 = a_base + a_off[jj];
           const uint32_t dcol = tmem_base + (uint32_t)(jj * BN);
-#pragma unroll
-          for (int k = 0; k < 8; ++k)
-            ptx::umma_bf16_pred(dcol, ((uint64_t)a_hi << 32) | (a_lo0 + k * k_step_a), ((uint64_t)b_hi << 32) | (b_lo0 + (uint32_t)(k * 128)),
-                                idesc, k > 0 ? 1u : acc, lead);
+          ptx::umma_bf16_x8(dcol, a_lo0, k_step_a, a_hi, b_lo0, 128u, b_hi, idesc, acc);
         }
       }
-      ptx::umma_commit_pred(empty(st), lead);
+      ptx::umma_commit(empty(st));
       if (++st == p.stages) { st = 0; ph ^= 1u; }
       acc = 1u;
     }
-    ptx::umma_commit_pred(done_bar, lead);
+    ptx::umma_commit(done_bar);
+    }
     __syncwarp();
   } else {
     // ================= epilogue: TMEM -> vector reductions into ws[tap][ci][co] =================

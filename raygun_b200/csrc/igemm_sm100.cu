@@ -132,7 +132,7 @@ __global__ void __launch_bounds__(IGEMM_THREADS, 1) igemm_conv_kernel(const __gr
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    if (ptx::elect_one_sync()) {      // elect.sync region: ptxas keeps the descriptors in the uniform datapath
       // ================= MMA issuer =================
       constexpr uint32_t idesc = ptx::idesc_bf16(TILE_M, BN, 0, 0);
       int stage = 0; uint32_t phase = 0;
@@ -379,7 +379,7 @@ __global__ void __launch_bounds__(IGEMM_THREADS, 1) igemm_wgrad_kernel(const __g
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    if (ptx::elect_one_sync()) {      // elect.sync region: ptxas keeps the descriptors in the uniform datapath
       // ================= MMA issuer =================
       constexpr uint32_t idesc = ptx::idesc_bf16(TILE_M, BN, 1, 1);    // both operands MN-major
       int stage = 0; uint32_t phase = 0;

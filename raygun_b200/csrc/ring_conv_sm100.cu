@@ -33,11 +33,9 @@ constexpr int RING_BLOCKS = 8;            // accumulator blocks of 64 TMEM colum
 constexpr int WBLK_BYTES = 64 * 128;      // weights of one (tap, kd): 64 produced channels x 64 reduction channels bf16
 constexpr int STAGE_KD = 4;               // kd blocks per weight stage (<= 256 MMA columns)
 constexpr int RING_TH = 16, RING_TW = 8;  // output tile (h, w); 8 = one swizzle-atom row group
-constexpr int MAX_S = 8, MAX_NA = 12, MAX_NB = 4;
-constexpr int PTAB_N = 2 * MAX_S;                                   // pieces per weight-stage part (<= 2 per slice)
-constexpr int PREG_N = 8;                                           // ... kept in registers: S <= 4 slices per group
-constexpr int RING_PTAB_OFF = 8 * (2 * MAX_NA + 2 * MAX_NB + 4) + 32;
-constexpr int RING_TAIL_BYTES = RING_PTAB_OFF + 2 * PTAB_N * 16 + 64;
+constexpr int MAX_NA = 12, MAX_NB = 4;
+constexpr int MAX_GS = 4;                                           // slices per group (S) the MMA warp unrolls
+constexpr int RING_TAIL_BYTES = 8 * (2 * MAX_NA + 2 * MAX_NB + 4) + 64;
 
 struct alignas(64) RingParams {
   CUtensorMap a_map;      // 5-D {C, W, H, D, N}; box {64, WB, HB, 1, 1}
@@ -107,6 +105,21 @@ struct RingWalk {
   }
 };
 
+#ifdef RING_DEBUG_NARROW      // experiment: every MMA only 64 columns wide (wrong results; is the loop pipe- or issue-bound?)
+#define RING_DBG_N(c) 1
+#else
+#define RING_DBG_N(c) (c)
+#endif
+#ifdef RING_DEBUG_TIMING
+// developer instrumentation (scripts/ring_timing.py): cycles the MMA warp spends per wait site, per CTA
+__device__ unsigned long long ring_dbg[148 * 8];
+#define DBG_T0() const long long dbg_t0 = clock64()
+#define DBG_ADD(k) dbg_acc[k] += clock64() - dbg_t0
+#else
+#define DBG_T0()
+#define DBG_ADD(k)
+#endif
+
 __global__ void __launch_bounds__(RING_THREADS, 1) ring_conv_kernel(const __grid_constant__ RingParams p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = ptx::smem_u32(smem_raw);
@@ -117,8 +130,6 @@ __global__ void __launch_bounds__(RING_THREADS, 1) ring_conv_kernel(const __grid
   uint8_t* tail = base_ptr + (size_t)p.na * p.slice_bytes + (size_t)p.nb * p.stage_bytes;
   uint64_t* bars = reinterpret_cast<uint64_t*>(tail);     // afull[na] aempty[na] bfull[nb] bempty[nb] tfull[2] tempty[2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tail + 8 * (2 * MAX_NA + 2 * MAX_NB + 4));
-  uint4* ptab = reinterpret_cast<uint4*>(tail + RING_PTAB_OFF);          // [2 parts][PTAB_N] piece table of the MMA warp
-  int* pcnt = reinterpret_cast<int*>(tail + RING_PTAB_OFF + 2 * PTAB_N * 16);
   const uint32_t bar0 = ptx::smem_u32(bars);
   auto afull = [&](int s) { return bar0 + 8u * s; };
   auto aempty = [&](int s) { return bar0 + 8u * (MAX_NA + s); };
@@ -196,112 +207,125 @@ __global__ void __launch_bounds__(RING_THREADS, 1) ring_conv_kernel(const __grid
     }
   } else if (warp == 1) {
     // ================= MMA issuer =================
-    // The whole warp runs this loop convergently (so addresses / descriptors stay in the uniform datapath and the
-    // tcgen05.mma operands need no per-instruction lane election loop); one elected lane issues.
-    const uint32_t lead = ptx::elect_one_sync() ? 1u : 0u;
+    // The loop is ISSUE-bound unless it is lean: a 128 x 192 x 16 MMA occupies the tensor pipe for 96 clk and a single
+    // thread issues a dependent instruction every ~7-10 clk, so an MMA may cost ~10 instructions at most (measured with
+    // scripts/ring_timing.py: 16 instructions per MMA, 8 of them R2UR, ran at 137 clk per MMA whatever its width).
+    // tcgen05.mma takes every operand from UNIFORM registers.  Inside an elect.sync region ptxas knows that one
+    // thread is active and computes descriptors directly in the uniform datapath; a predicated issue from a
+    // convergent warp instead moves every operand R -> UR per MMA.  So: one elected thread runs the whole loop, the
+    // (slice, weight part) -> accumulator block mapping is integer arithmetic done once per group, and the four
+    // K steps of a chunk are one asm block.
+    if (ptx::elect_one_sync()) {
     const uint32_t idesc_base = ptx::idesc_bf16(128, 0, 0, 0);
     const uint32_t a_hi = (((uint32_t)(p.wb * 128) >> 4) & 0x3FFFu) | (1u << 14) | (2u << 29);   // SBO | version | SW128
     const uint32_t b_hi = ((1024u >> 4) & 0x3FFFu) | (1u << 14) | (2u << 29);
     const uint32_t lbo_lo = 1u << 16;
+    const uint32_t tmem_u = tmem_base;
     int a_i = 0; uint32_t a_ph = 0;
     int b_i = 0; uint32_t b_ph = 0;
     int g = 0, waited = -1;
     RingUnit r;
+#ifdef RING_DEBUG_TIMING
+    long long dbg_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    const long long dbg_start = clock64();
+#endif
     for (RingWalk walk(p); walk.next(p, r);) {
       bool first = true;
-      for (int zg = r.z_begin; zg <= r.z_end; zg += p.S) {
-        // piece table of this group: which accumulator blocks each (slice, weight-stage part) feeds.  It is the same
-        // for every (kh, kw) tap and reduction chunk, so it is built once (lane 0) and replayed from smem.
-        __syncwarp();
+      const int d0 = r.d0, d1 = d0 + r.len;
+      const int z_begin = d0 - p.pd, z_end = d1 - 1 - p.pd + p.kd - 1;
+      const int z_last = min(z_end, p.in_d - 1);
+      for (int zg = z_begin; zg <= z_end; zg += p.S) {
+        // slice zg+s: weight block i (kd = KD-1-i) feeds output plane d = dbase + i, dbase = z + pd - KD + 1, which
+        // lives in accumulator block (d - d0) & 7; only planes inside [d0, d1) exist: i in [ilo, ihi)
+        // Per (weight part, slice) that is at most two MMA pieces: blocks up to the end of the ring, then the rest
+        // from block 0.  Everything the tap loop needs is computed here, once per group.
+        uint32_t tm1[2][MAX_GS], id1[2][MAX_GS], id2[2][MAX_GS], wo1[2][MAX_GS], wo2[2][MAX_GS];
+        int ord[MAX_GS];
         int nvalid = 0;
-        if (lane == 0) {
-          int cnt[2] = {0, 0};
-          for (int s = 0; s < p.S; ++s) {
-            const int z = zg + s;
-            if (z > r.z_end || z < 0 || z >= p.in_d) continue;
-            // weight block i (kd = KD-1-i) of slice z feeds output plane d = z + pd - KD + 1 + i
-            const int dbase = z + p.pd - p.kd + 1;
-            for (int part = 0; part < parts; ++part) {
-              const int nblk = min(STAGE_KD, p.kd - part * STAGE_KD);
-              int i_lo = max(part * STAGE_KD, r.d0 - dbase);
-              const int i_hi = min(part * STAGE_KD + nblk, r.d0 + r.len - dbase);      // exclusive
-              while (i_lo < i_hi) {
-                const int blk = (dbase + i_lo - r.d0) & (RING_BLOCKS - 1);
-                const int c = min(i_hi - i_lo, RING_BLOCKS - blk);
-                ptab[part * PTAB_N + cnt[part]] = make_uint4(tmem_base + (uint32_t)(blk * 64), idesc_base | ((uint32_t)(c * 8) << 17),
-                                                              (uint32_t)nvalid, (uint32_t)((i_lo - part * STAGE_KD) * (WBLK_BYTES >> 4)));
-                ++cnt[part];
-                i_lo += c;
-              }
-            }
-            ++nvalid;
-          }
-          pcnt[0] = cnt[0]; pcnt[1] = cnt[1]; pcnt[2] = nvalid;
-        }
-        __syncwarp();
-        nvalid = pcnt[2];
-        // the table is invariant over the taps and reduction chunks of the group: keep it in registers
-        const int n0 = pcnt[0], n1 = pcnt[1];
-        uint4 e0[PREG_N], e1[PREG_N];
+        { DBG_T0();
 #pragma unroll
-        for (int j = 0; j < PREG_N; ++j) {
-          e0[j] = j < n0 ? ptab[j] : make_uint4(0, 0, 0, 0);
-          e1[j] = j < n1 ? ptab[PTAB_N + j] : make_uint4(0, 0, 0, 0);
+        for (int s = 0; s < MAX_GS; ++s) {
+          const int z = zg + s;
+          const bool valid = s < p.S && z >= 0 && z <= z_last;
+          const int dbase = z + p.pd - p.kd + 1;
+          const int ilo = max(0, d0 - dbase), ihi = valid ? min(p.kd, d1 - dbase) : 0;
+#pragma unroll
+          for (int part = 0; part < 2; ++part) {
+            const int p_lo = part * STAGE_KD, p_hi = min(p.kd, p_lo + STAGE_KD);
+            const int lo = max(p_lo, ilo), cnt = min(p_hi, ihi) - lo;
+            const int blk = (dbase - d0 + lo) & (RING_BLOCKS - 1);
+            const int c1 = min(cnt, RING_BLOCKS - blk);       // blocks before the ring wraps
+            tm1[part][s] = tmem_u + (uint32_t)(blk * 64);
+            id1[part][s] = cnt > 0 ? idesc_base | ((uint32_t)(RING_DBG_N(c1) * 8) << 17) : 0u;
+            id2[part][s] = cnt > c1 && cnt > 0 ? idesc_base | ((uint32_t)(RING_DBG_N(cnt - c1) * 8) << 17) : 0u;
+            wo1[part][s] = (uint32_t)((lo - p_lo) * (WBLK_BYTES >> 4));
+            wo2[part][s] = (uint32_t)((lo - p_lo + c1) * (WBLK_BYTES >> 4));
+          }
+          ord[s] = nvalid;
+          nvalid += valid ? 1 : 0;
         }
+        DBG_ADD(0); }
         const int need = first ? g - 1 : g - p.lag;
+        { DBG_T0();
         while (waited < need) { ++waited; ptx::mbar_wait(tempty(waited & 1), (uint32_t)((waited >> 1) & 1)); }
+        DBG_ADD(1); }
         ptx::tc_fence_after();
         for (int q = 0; q < p.q_chunks; ++q) {
-          // slices of this chunk: wait for their TMA, then fold the slot address into the per-piece A base
+          // slices of this chunk: wait for their TMA, then the A descriptor base of every slice
+          { DBG_T0();
           for (int j = 0; j < nvalid; ++j) {
             int slot = a_i + j; uint32_t sph = a_ph;
             if (slot >= p.na) { slot -= p.na; sph ^= 1u; }
             ptx::mbar_wait(afull(slot), sph);
           }
+          DBG_ADD(2); }
           ptx::tc_fence_after();
-          uint32_t ab0[PREG_N], ab1[PREG_N];
+          uint32_t abase[MAX_GS];
 #pragma unroll
-          for (int j = 0; j < PREG_N; ++j) {
-            int s0 = a_i + (int)e0[j].z; if (s0 >= p.na) s0 -= p.na;
-            int s1 = a_i + (int)e1[j].z; if (s1 >= p.na) s1 -= p.na;
-            ab0[j] = ((smem_a + (uint32_t)(s0 * p.slice_bytes)) >> 4) | lbo_lo;
-            ab1[j] = ((smem_a + (uint32_t)(s1 * p.slice_bytes)) >> 4) | lbo_lo;
+          for (int s = 0; s < MAX_GS; ++s) {
+            int slot = a_i + ord[s]; if (slot >= p.na) slot -= p.na;
+            abase[s] = ((smem_a + (uint32_t)(slot * p.slice_bytes)) >> 4) | lbo_lo;
           }
-          for (int t = 0; t < ntaps_hw; ++t) {
-            const int tkh = t / p.kw, tkw = t - tkh * p.kw;
+          for (int tkh = 0; tkh < p.kh; ++tkh)
+          for (int tkw = 0; tkw < p.kw; ++tkw) {
             const uint32_t a_shift = (uint32_t)((tkh * p.wb + tkw) * 8);        // rows * 128 B >> 4
 #pragma unroll
             for (int part = 0; part < 2; ++part) {
               if (part < parts) {
+                { DBG_T0();
                 ptx::mbar_wait(bfull(b_i), b_ph);
+                DBG_ADD(3); }
                 ptx::tc_fence_after();
                 const uint32_t b_lo = (((smem_b + (uint32_t)(b_i * p.stage_bytes)) >> 4) & 0x3FFFu) | lbo_lo;
-                const int n = part ? n1 : n0;
 #pragma unroll
-                for (int j = 0; j < PREG_N; ++j) {
-                  if (j < n) {
-                    const uint4 e = part ? e1[j] : e0[j];
-                    const uint32_t a_lo = (part ? ab1[j] : ab0[j]) + a_shift;
-#pragma unroll
-                    for (int k = 0; k < 4; ++k)
-                      ptx::umma_bf16_pred(e.x, ((uint64_t)a_hi << 32) | (uint64_t)(a_lo + 2 * k),
-                                          ((uint64_t)b_hi << 32) | (uint64_t)(b_lo + e.w + 2 * k), e.y, 1u, lead);
+                for (int s = 0; s < MAX_GS; ++s) {
+                  if (id1[part][s]) {
+                    const uint32_t a_lo = abase[s] + a_shift;
+                    ptx::umma_bf16_x4(tm1[part][s], a_lo, a_hi, b_lo + wo1[part][s], b_hi, id1[part][s]);
+                    if (id2[part][s]) ptx::umma_bf16_x4(tmem_u, a_lo, a_hi, b_lo + wo2[part][s], b_hi, id2[part][s]);
                   }
                 }
-                ptx::umma_commit_pred(bempty(b_i), lead);
+                ptx::umma_commit(bempty(b_i));
                 if (++b_i == p.nb) { b_i = 0; b_ph ^= 1u; }
               }
             }
           }
           for (int j = 0; j < nvalid; ++j) {
-            ptx::umma_commit_pred(aempty(a_i), lead);
+            ptx::umma_commit(aempty(a_i));
             if (++a_i == p.na) { a_i = 0; a_ph ^= 1u; }
           }
         }
-        ptx::umma_commit_pred(tfull(g & 1), lead);
+        ptx::umma_commit(tfull(g & 1));
         ++g;
         first = false;
       }
+    }
+#ifdef RING_DEBUG_TIMING
+    if (blockIdx.x < 148) {
+      dbg_acc[4] = clock64() - dbg_start;
+      for (int k = 0; k < 8; ++k) ring_dbg[blockIdx.x * 8 + k] = (unsigned long long)dbg_acc[k];
+    }
+#endif
     }
     __syncwarp();
   } else {
@@ -647,5 +671,11 @@ int rg_ring_config(const rg_igemm_desc* d, int* out8) {
   out8[6] = g.smem_bytes; out8[7] = g.p.slice_bytes;
   return RG_OK;
 }
+
+#ifdef RING_DEBUG_TIMING
+int rg_ring_debug_read(unsigned long long* out) {
+  return cudaMemcpyFromSymbol(out, rg::ring_dbg, sizeof(rg::ring_dbg)) == cudaSuccess ? 0 : -1;
+}
+#endif
 
 }  // extern "C"

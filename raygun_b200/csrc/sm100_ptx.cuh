@@ -139,6 +139,73 @@ __device__ __forceinline__ void umma_bf16_pred(uint32_t d_tmem, uint64_t a_desc,
       "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate), "r"(issue)
       : "memory");
 }
+// the four K = 16 steps of one 64-channel chunk: descriptor low words advance by 32 B (>> 4 = 2) per step; always accumulates
+__device__ __forceinline__ void umma_bf16_x4_pred(uint32_t d_tmem, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi,
+                                                  uint32_t idesc, uint32_t issue) {
+  asm volatile(
+      "{\n\t.reg .pred q, one;\n\t.reg .b64 a, b;\n\t.reg .b32 ta, tb;\n\t"
+      "setp.ne.b32 q, %6, 0;\n\t"
+      "setp.eq.b32 one, 0, 0;\n\t"
+      "mov.b64 a, {%1, %2};\n\t"
+      "mov.b64 b, {%3, %4};\n\t"
+      "@q tcgen05.mma.cta_group::1.kind::f16 [%0], a, b, %5, one;\n\t"
+      "add.u32 ta, %1, 2;\n\t add.u32 tb, %3, 2;\n\t mov.b64 a, {ta, %2};\n\t mov.b64 b, {tb, %4};\n\t"
+      "@q tcgen05.mma.cta_group::1.kind::f16 [%0], a, b, %5, one;\n\t"
+      "add.u32 ta, %1, 4;\n\t add.u32 tb, %3, 4;\n\t mov.b64 a, {ta, %2};\n\t mov.b64 b, {tb, %4};\n\t"
+      "@q tcgen05.mma.cta_group::1.kind::f16 [%0], a, b, %5, one;\n\t"
+      "add.u32 ta, %1, 6;\n\t add.u32 tb, %3, 6;\n\t mov.b64 a, {ta, %2};\n\t mov.b64 b, {tb, %4};\n\t"
+      "@q tcgen05.mma.cta_group::1.kind::f16 [%0], a, b, %5, one;\n\t}" ::"r"(d_tmem),
+      "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(issue)
+      : "memory");
+}
+__device__ __forceinline__ void umma_bf16_x4(uint32_t d_tmem, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi,
+                                             uint32_t idesc) {
+  asm volatile(
+      "{\n\t.reg .pred one;\n\t.reg .b64 a, b;\n\t.reg .b32 ta, tb;\n\t"
+      "setp.eq.b32 one, 0, 0;\n\t"
+      "mov.b64 a, {%1, %2};\n\t"
+      "mov.b64 b, {%3, %4};\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], a, b, %5, one;\n\t"
+      "add.u32 ta, %1, 2;\n\t add.u32 tb, %3, 2;\n\t mov.b64 a, {ta, %2};\n\t mov.b64 b, {tb, %4};\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], a, b, %5, one;\n\t"
+      "add.u32 ta, %1, 4;\n\t add.u32 tb, %3, 4;\n\t mov.b64 a, {ta, %2};\n\t mov.b64 b, {tb, %4};\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], a, b, %5, one;\n\t"
+      "add.u32 ta, %1, 6;\n\t add.u32 tb, %3, 6;\n\t mov.b64 a, {ta, %2};\n\t mov.b64 b, {tb, %4};\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], a, b, %5, one;\n\t}" ::"r"(d_tmem),
+      "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc)
+      : "memory");
+}
+// eight K = 16 steps (one 128-voxel chunk of a weight-gradient GEMM): descriptor low words advance by a_step / b_step;
+// the first step accumulates iff acc_first, the others always
+__device__ __forceinline__ void umma_bf16_x8(uint32_t d_tmem, uint32_t a_lo, uint32_t a_step, uint32_t a_hi, uint32_t b_lo,
+                                             uint32_t b_step, uint32_t b_hi, uint32_t idesc, uint32_t acc_first) {
+  asm volatile(
+      "{\n\t.reg .pred pa, one;\n\t.reg .b64 a, b;\n\t.reg .b32 ta, tb;\n\t"
+      "setp.ne.b32 pa, %8, 0;\n\t"
+      "setp.eq.b32 one, 0, 0;\n\t"
+      "mov.b32 ta, %1;\n\t mov.b32 tb, %4;\n\t mov.b64 a, {ta, %3};\n\t mov.b64 b, {tb, %6};\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], a, b, %7, pa;\n\t"
+      "add.u32 ta, ta, %2;\n\t add.u32 tb, tb, %5;\n\t mov.b64 a, {ta, %3};\n\t mov.b64 b, {tb, %6};\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], a, b, %7, one;\n\t"
+      "add.u32 ta, ta, %2;\n\t add.u32 tb, tb, %5;\n\t mov.b64 a, {ta, %3};\n\t mov.b64 b, {tb, %6};\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], a, b, %7, one;\n\t"
+      "add.u32 ta, ta, %2;\n\t add.u32 tb, tb, %5;\n\t mov.b64 a, {ta, %3};\n\t mov.b64 b, {tb, %6};\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], a, b, %7, one;\n\t"
+      "add.u32 ta, ta, %2;\n\t add.u32 tb, tb, %5;\n\t mov.b64 a, {ta, %3};\n\t mov.b64 b, {tb, %6};\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], a, b, %7, one;\n\t"
+      "add.u32 ta, ta, %2;\n\t add.u32 tb, tb, %5;\n\t mov.b64 a, {ta, %3};\n\t mov.b64 b, {tb, %6};\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], a, b, %7, one;\n\t"
+      "add.u32 ta, ta, %2;\n\t add.u32 tb, tb, %5;\n\t mov.b64 a, {ta, %3};\n\t mov.b64 b, {tb, %6};\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], a, b, %7, one;\n\t"
+      "add.u32 ta, ta, %2;\n\t add.u32 tb, tb, %5;\n\t mov.b64 a, {ta, %3};\n\t mov.b64 b, {tb, %6};\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], a, b, %7, one;\n\t"
+      "}" ::"r"(d_tmem),
+      "r"(a_lo), "r"(a_step), "r"(a_hi), "r"(b_lo), "r"(b_step), "r"(b_hi), "r"(idesc), "r"(acc_first)
+      : "memory");
+}
+// a warp-uniform value routed through REDUX so that it lives in a uniform register (and what is derived from it
+// stays in the uniform datapath: tcgen05.mma takes all its operands from there)
+__device__ __forceinline__ uint32_t uniform_u32(uint32_t v) { return __reduce_or_sync(0xffffffffu, v); }
 __device__ __forceinline__ void umma_commit_pred(uint32_t bar, uint32_t issue) {
   asm volatile(
       "{\n\t.reg .pred q;\n\t"

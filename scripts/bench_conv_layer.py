@@ -19,6 +19,13 @@ LAYERS = {
     "unet384_128": (1, 384, 128, (3, 3, 3), (1, 1, 1), (32, 32, 32)),
     "res256": (2, 256, 256, (3, 3, 3), (0, 0, 0), (34, 34, 34)),
     "unet64_64_256": (1, 64, 64, (3, 3, 3), (1, 1, 1), (256, 256, 256)),
+    # the G-UNet layers at the cfg4 block size (read 256^3)
+    "inf192_64": (1, 192, 64, (3, 3, 3), (1, 1, 1), (256, 256, 256)),
+    "inf64_128": (1, 64, 128, (3, 3, 3), (1, 1, 1), (128, 128, 128)),
+    "inf128_128": (1, 128, 128, (3, 3, 3), (1, 1, 1), (128, 128, 128)),
+    "inf384_128": (1, 384, 128, (3, 3, 3), (1, 1, 1), (128, 128, 128)),
+    "inf128_256": (1, 128, 256, (3, 3, 3), (1, 1, 1), (64, 64, 64)),
+    "inf256_256": (1, 256, 256, (3, 3, 3), (1, 1, 1), (64, 64, 64)),
 }
 
 
@@ -60,6 +67,9 @@ def main():
             r0 = CV.stats.get("ring", 0)
             t_f = timeit(lambda: CV.conv_fprop(x, w, None, (1, 1, 1), p, 1, 0, 0.0, want_stats=True))
             ring_f = CV.stats.get("ring", 0) > r0
+            if "--fprop-only" in sys.argv:
+                print(f"{name:16s} {flops / 1e9:9.1f} GF | fprop {t_f:8.3f} ms {flops / t_f / 1e9:7.1f} TF/s {'ring' if ring_f else 'igemm'}", flush=True)
+                continue
             r0 = CV.stats.get("ring", 0)
             t_d = timeit(lambda: CV.conv_dgrad(dy, w, tuple(x.shape), (1, 1, 1), p))
             ring_d = CV.stats.get("ring", 0) > r0
