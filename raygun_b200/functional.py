@@ -133,10 +133,11 @@ def conv3d(x, w, bias=None, stride=1, padding=0, groups=1, act=ACT_NONE, slope=0
     skip-connection concat buffer; the result IS `out` when the kernel could honour it (callers check identity)."""
     if torch.is_grad_enabled():
         out = None
-    if _stem_eligible(x, w, _t3(stride), int(groups)):
-        y, s, q = _StemConv3d.apply(x, w, bias, _t3(padding), act, float(slope), bool(want_stats), out)
-    else:
-        y, s, q = _Conv3d.apply(x, w, bias, _t3(stride), _t3(padding), int(groups), act, float(slope), bool(want_stats), out)
+    with K.arena_scope(not torch.is_grad_enabled()):
+        if _stem_eligible(x, w, _t3(stride), int(groups)):
+            y, s, q = _StemConv3d.apply(x, w, bias, _t3(padding), act, float(slope), bool(want_stats), out)
+        else:
+            y, s, q = _Conv3d.apply(x, w, bias, _t3(stride), _t3(padding), int(groups), act, float(slope), bool(want_stats), out)
     if want_stats:
         return y, (s, q) if s.numel() else None
     return y
@@ -185,8 +186,9 @@ def conv_transpose3d(x, w, bias=None, stride=1, padding=0, output_padding=0, act
                      want_stats=False, out=None):
     if torch.is_grad_enabled():
         out = None
-    y, s, q = _ConvTranspose3d.apply(x, w, bias, _t3(stride), _t3(padding), _t3(output_padding), act, float(slope),
-                                     bool(want_stats), out)
+    with K.arena_scope(not torch.is_grad_enabled()):
+        y, s, q = _ConvTranspose3d.apply(x, w, bias, _t3(stride), _t3(padding), _t3(output_padding), act, float(slope),
+                                         bool(want_stats), out)
     if want_stats:
         return y, (s, q) if s.numel() else None
     return y

@@ -67,9 +67,31 @@ def empty5(shape, dtype, device):
 ARENA_MARGIN = 1
 
 
+_arena_flag = None      # set by functional.* around autograd.Function.apply: Function.forward always runs with grad mode
+                        # off, so the caller's grad mode has to be handed down explicitly
+
+
+class arena_scope:
+    """with arena_scope(allow): kernels called inside see arena_enabled() == allow (and bf16, and the env switch)."""
+
+    def __init__(self, allow: bool):
+        self.allow = bool(allow)
+
+    def __enter__(self):
+        global _arena_flag
+        self.prev, _arena_flag = _arena_flag, self.allow
+
+    def __exit__(self, *exc):
+        global _arena_flag
+        _arena_flag = self.prev
+
+
 def arena_enabled() -> bool:
+    """Margin-allocated conv outputs are an inference-only layout (training keeps dense tensors for the norm kernels)."""
     import os
-    return (not torch.is_grad_enabled()) and get_precision() == "bf16" and os.environ.get("RAYGUN_B200_ARENA", "1") != "0"
+    if get_precision() != "bf16" or os.environ.get("RAYGUN_B200_ARENA", "1") == "0":
+        return False
+    return _arena_flag if _arena_flag is not None else not torch.is_grad_enabled()
 
 
 def empty5_arena(shape, dtype, device, margin=ARENA_MARGIN):

@@ -126,3 +126,21 @@ def test_ring_config_reported_by_the_library():
     assert segs == 0 or seg_len * segs >= 128      # segs == 0: balanced flattened partition (the default)
     d.stride[:] = [2, 2, 2]
     assert _C.lib().rg_ring_supported(C.byref(d)) == 0
+
+
+def test_arena_scope_hands_the_callers_grad_mode_down():
+    import torch
+    import raygun_b200 as rb
+    from raygun_b200 import kernels as K
+    with rb.precision("bf16"):
+        assert not K.arena_enabled()                      # grad mode on: training layout
+        with torch.no_grad():
+            assert K.arena_enabled()
+            with K.arena_scope(False):                    # e.g. inside Function.forward of a training step
+                assert not K.arena_enabled()
+            assert K.arena_enabled()
+        with K.arena_scope(True):
+            assert K.arena_enabled()
+        assert not K.arena_enabled()
+    with rb.precision("fp32"), torch.no_grad():
+        assert not K.arena_enabled()

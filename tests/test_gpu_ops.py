@@ -341,3 +341,20 @@ def test_vectorised_maxpool_matches_torch_on_strided_ndhwc_views():
         assert torch.equal(K.maxpool_fwd(xg, f).float().cpu(), ref)
         sl = xg[:, 8:24]                                                     # channel slice: voxel stride 24, 16 channels
         assert torch.equal(K.maxpool_fwd(sl, f).float().cpu(), ref[:, 8:24])
+
+
+def test_training_conv_outputs_stay_dense_and_inference_uses_arenas():
+    """autograd.Function.forward always runs with grad mode off: the caller's grad mode has to be handed down, or
+    training silently gets the margin-allocated inference layout (strided outputs -> slow norm kernels)."""
+    import raygun_b200 as rb
+    from raygun_b200 import nn as L
+    torch.manual_seed(5)
+    conv = L.Conv3d(64, 64, 3, padding=1).to(DEV)
+    x = torch.randn(1, 64, 8, 8, 8, device=DEV)
+    with rb.precision("bf16"):
+        y = conv(x.clone().requires_grad_(True))
+        assert y.requires_grad and y.is_contiguous(memory_format=torch.channels_last_3d)
+        with torch.no_grad():
+            z = conv(x)
+        assert getattr(z._base, "_rg_arena", None) == 1 and not z.is_contiguous(memory_format=torch.channels_last_3d)
+    assert torch.equal(y.detach().float(), z.float())
