@@ -249,7 +249,7 @@ def conv_fprop(x, w, bias, stride, pad, groups=1, act=ACT_NONE, slope=0.0, want_
         return K.empty5((n, cout, *od), dtype, x.device)
 
     if _igemm_ok(cin_t, cout, kernel, stride, groups) and cdt == torch.bfloat16:
-        xb = K.convert(x, torch.bfloat16)
+        xb = K.conv_operand(x)
         y = _alloc(torch.bfloat16)
         rd = _ring_desc(0, n, cin_t, cout, (d, h, wd_), od, kernel, stride, pad, _sp_strides(xb), _sp_strides(y),
                         act, float(slope))
@@ -277,7 +277,7 @@ def conv_fprop(x, w, bias, stride, pad, groups=1, act=ACT_NONE, slope=0.0, want_
             stats["igemm"] += 1
             return (y, st[0], st[1]) if want_stats else (y, None, None)
     if _pw_ok(cin_t, cout, kernel, stride, pad, groups):
-        xb = K.convert(x, torch.bfloat16)
+        xb = K.conv_operand(x)
         y = _alloc(cdt)
         check(lib().rg_pw_conv_fprop(C.byref(t5(xb)), ptr(xb), ptr(w.detach().contiguous()), ptr(bias_f), C.c_int(act),
                                      C.c_float(slope), C.byref(t5(y)), ptr(y), stream_ptr(x.device)), "rg_pw_conv_fprop")
@@ -307,7 +307,7 @@ def conv_dgrad(dy, w, x_shape, stride, pad, groups=1, bias=None, act=ACT_NONE, s
     cdt = out_dtype or K.compute_dtype()
     bias_f = bias.detach() if bias is not None else None
     if _igemm_ok(cin_t, cout_t, kernel, stride, groups) and cdt == torch.bfloat16:
-        dyb = K.convert(dy, torch.bfloat16)
+        dyb = K.conv_operand(dy)
         if out is not None and tuple(out.shape) == tuple(x_shape) and out.dtype == torch.bfloat16 and out.stride(1) == 1:
             dx = out
         else:

@@ -147,6 +147,19 @@ def convert(x: torch.Tensor, dtype) -> torch.Tensor:
     return copy_into(empty5(x.shape, dtype, x.device), x)
 
 
+def channels_inner_bf16(x: torch.Tensor) -> bool:
+    """bf16, channels innermost, every other stride and the base 16-byte aligned: what the TMA-fed kernels and the
+    16-byte vector kernels address directly (dense NDHWC, pad-arena interiors, channel slices, crops)."""
+    return (x.dtype == torch.bfloat16 and x.dim() == 5 and x.stride(1) == 1 and x.data_ptr() % 16 == 0
+            and all(s % 8 == 0 for i, s in enumerate(x.stride()) if i != 1))
+
+
+def conv_operand(x: torch.Tensor) -> torch.Tensor:
+    """`x` as a bf16 operand of the tensor-core / pointwise convolutions: strided channel-inner views are used in
+    place (no densifying copy), anything else is converted to dense NDHWC bf16."""
+    return x if channels_inner_bf16(x) else convert(x, torch.bfloat16)
+
+
 def im2col_hw(x, kh, kw, ph, pw, channels=64):
     """Fold the H/W taps of a small-Cin convolution into `channels` bf16 NDHWC channels."""
     require_device(x)

@@ -358,3 +358,27 @@ def test_training_conv_outputs_stay_dense_and_inference_uses_arenas():
             z = conv(x)
         assert getattr(z._base, "_rg_arena", None) == 1 and not z.is_contiguous(memory_format=torch.channels_last_3d)
     assert torch.equal(y.detach().float(), z.float())
+
+
+def test_strided_channel_inner_views_are_conv_operands_in_place():
+    """Pad-arena interiors / channel slices feed the TMA and pointwise kernels without a densifying copy."""
+    import raygun_b200 as rb
+    from raygun_b200 import conv as CV, kernels as K
+    torch.manual_seed(6)
+    full = torch.randn(1, 192, 12, 12, 12, device=DEV).bfloat16().contiguous(memory_format=torch.channels_last_3d)
+    x = full[:, 64:192, 1:11, 1:11, 1:11]                       # channel slice of an interior view
+    assert K.channels_inner_bf16(x) and K.conv_operand(x) is x
+    xd = x.contiguous(memory_format=torch.channels_last_3d)
+    with rb.precision("bf16"), torch.no_grad():
+        wt = torch.randn(128, 128, 2, 2, 2, device=DEV) * 0.05     # ConvTranspose3d k = s = 2 (UNet.py:265-269)
+        a, _, _ = CV.conv_dgrad(x, wt, (1, 128, 20, 20, 20), (2, 2, 2), (0, 0, 0))
+        b, _, _ = CV.conv_dgrad(xd, wt, (1, 128, 20, 20, 20), (2, 2, 2), (0, 0, 0))
+        assert torch.equal(a.float(), b.float())
+        w1 = torch.randn(1, 128, 1, 1, 1, device=DEV) * 0.1        # 1x1x1 head (BaseSystem.py:209-224)
+        a, _, _ = CV.conv_fprop(x, w1, None, (1, 1, 1), (0, 0, 0), 1, 3, 0.0)
+        b, _, _ = CV.conv_fprop(xd, w1, None, (1, 1, 1), (0, 0, 0), 1, 3, 0.0)
+        assert torch.equal(a.float(), b.float())
+        w3 = torch.randn(256, 128, 3, 3, 3, device=DEV) * 0.05     # igemm path (256 produced channels)
+        a, _, _ = CV.conv_fprop(x, w3, None, (1, 1, 1), (1, 1, 1), 1, 0, 0.0)
+        b, _, _ = CV.conv_fprop(xd, w3, None, (1, 1, 1), (1, 1, 1), 1, 0, 0.0)
+        assert torch.equal(a.float(), b.float())
