@@ -122,6 +122,16 @@ int rg_ring_pack_weights(const float* w, int cout, int cin, const int* kernel3, 
 int rg_ring_run(const rg_igemm_desc* desc, const void* in, const void* w_ring, const float* bias, void* out,
                 float* stats_sum, float* stats_sqsum, void* stream);
 
+/* ---- small-K stem convolution (stem_conv_sm100.cu) ---------------------------------------------------------
+ * Forward of a stride-1 Conv3d whose whole reduction Cin*kD*kH*kW is <= 64 (the 1 -> ngf 3^3 convolution that
+ * opens a U-Net, UNet.py:52-87 with input_nc = 1): im2col rows are gathered straight into the tensor-core operand
+ * tile in shared memory, so the 1-channel input and the output cross HBM once.  `x` is bf16 with arbitrary element
+ * strides (desc->x_strides = n,d,h,w; x_channel_stride for c); `w64` = bf16 [Cout][64], row co = the flattened
+ * [Cin][kD][kH][kW] weights of that output channel, zero padded; `y` bf16, channels innermost.  Zero padding only.  */
+int rg_stem_conv_supported(const rg_igemm_desc* desc);
+int rg_stem_conv_run(const rg_igemm_desc* desc, const void* x, long long x_channel_stride, const void* w64,
+                     const float* bias, void* y, void* stream);
+
 /* ---- halo-resident weight gradient (stride 1; halo_wgrad_sm100.cu) ------------------------------------------
  * Same role as rg_igemm_wgrad (autograd of Conv3d, reference: torch.nn.Conv3d call sites UNet.py:69-87,
  * ResNet.py:262-327) for stride-1 layers: one X plane with its (kh,kw) halo per 128-voxel chunk serves every tap

@@ -160,6 +160,61 @@ def _ring_desc(mode, n, cin, cout, in_dhw, out_dhw, kernel, stride, pad, xs, ys,
     return _ring_descs[key]
 
 
+STEM_DIRECT = os.environ.get("RAYGUN_B200_STEM_DIRECT", "1") != "0"
+_stem_packs: "dict[int, tuple]" = {}
+
+
+def stem_direct_ok(w, want_stats):
+    """The small-K stem kernel (stem_conv_sm100.cu) takes a stride-1 conv whose whole reduction fits one 64-wide K block."""
+    cout, cin, kd, kh, kw = w.shape
+    return (STEM_DIRECT and not want_stats and cin * kd * kh * kw <= 64 and cout % 32 == 0 and 32 <= cout <= 256
+            and K.compute_dtype() == torch.bfloat16)
+
+
+def stem_conv_fprop(x, w, bias, pad, act=ACT_NONE, slope=0.0, out=None):
+    """Forward of the first U-Net convolution (UNet.py:52-87, input_nc -> ngf) without the folded intermediate."""
+    require_device(x)
+    n, cin, d, h, wd_ = x.shape
+    cout = w.shape[0]
+    kernel = tuple(w.shape[2:])
+    od = [out_size(i, k, 1, p) for i, k, p in zip((d, h, wd_), kernel, pad)]
+    if min(od) < 1:
+        raise RuntimeError(f"conv3d: kernel {kernel} does not fit input {tuple(x.shape)}")
+    xb = x if x.dtype == torch.bfloat16 else K.convert(x, torch.bfloat16)
+    if out is not None and tuple(out.shape) == (n, cout, *od) and out.dtype == torch.bfloat16 and K.channels_inner_bf16(out):
+        y = out
+    elif K.arena_enabled():
+        y = K.empty5_arena((n, cout, *od), torch.bfloat16, x.device)
+    else:
+        y = K.empty5((n, cout, *od), torch.bfloat16, x.device)
+    ent = _stem_packs.get(id(w))
+    if ent is None or ent[0]() is not w or ent[1] != w._version or ent[2] != w.data_ptr():
+        w64 = torch.zeros(cout, 64, dtype=torch.bfloat16, device=w.device)
+        w64[:, : cin * kernel[0] * kernel[1] * kernel[2]] = w.detach().reshape(cout, -1).to(torch.bfloat16)
+        if len(_stem_packs) > 256:
+            for k in [k for k, e in _stem_packs.items() if e[0]() is None]:
+                del _stem_packs[k]
+        _stem_packs[id(w)] = ent = (weakref.ref(w), w._version, w.data_ptr(), w64)
+    d_ = IgemmDesc()
+    d_.mode, d_.n, d_.cin, d_.cout = 0, n, cin, cout
+    d_.in_dhw[:] = [d, h, wd_]
+    d_.out_dhw[:] = od
+    d_.kernel[:] = list(kernel)
+    d_.stride[:] = [1, 1, 1]
+    d_.pad[:] = list(pad)
+    d_.x_strides[:] = list(_sp_strides(xb))
+    d_.y_strides[:] = list(_sp_strides(y))
+    d_.act, d_.slope = act, float(slope)
+    d_.has_bias = 1 if bias is not None else 0
+    bias_f = bias.detach().float().contiguous() if bias is not None else None
+    with _Timed("fprop", 2.0 * y.numel() * cin * kernel[0] * kernel[1] * kernel[2], x.device, "stem_conv_kernel"):
+        check(lib().rg_stem_conv_run(C.byref(d_), ptr(xb), C.c_longlong(xb.stride(1)), ptr(ent[3]), ptr(bias_f), ptr(y),
+                                     stream_ptr(x.device)), "rg_stem_conv_run")
+    count_launch()
+    stats["stem_direct"] = stats.get("stem_direct", 0) + 1
+    return y
+
+
 _halo_descs: "dict[tuple, IgemmDesc | None]" = {}
 HALO_WGRAD = os.environ.get("RAYGUN_B200_HALO_WGRAD", "1") != "0"
 

@@ -92,11 +92,15 @@ class _StemConv3d(torch.autograd.Function):
     def forward(ctx, x, w, bias, pad, act, slope, want_stats, out=None):
         cout, cin, kd, kh, kw = w.shape
         cf = cin * kh * kw
-        xc = K.im2col_hw(x, kh, kw, pad[1], pad[2], 64)
-        w2 = w.detach().permute(0, 2, 1, 3, 4).reshape(cout, kd, cf)          # [co][kd][(ci,kh,kw)]
-        w2 = torch.nn.functional.pad(w2, (0, 64 - cf)).permute(0, 2, 1).reshape(cout, 64, kd, 1, 1).contiguous()
-        y, s, q = CV.conv_fprop(xc, w2, bias, (1, 1, 1), (pad[0], 0, 0), 1, act, slope, want_stats, out=out)
-        ctx.cfg = (pad, act, slope, tuple(w.shape), tuple(w2.shape))
+        if CV.stem_direct_ok(w, want_stats):
+            # whole reduction <= 64 (U-Net stem): im2col rows are built in shared memory, no folded intermediate
+            y, s, q = CV.stem_conv_fprop(x, w, bias, pad, act, slope, out=out), None, None
+        else:
+            xc = K.im2col_hw(x, kh, kw, pad[1], pad[2], 64)
+            w2 = w.detach().permute(0, 2, 1, 3, 4).reshape(cout, kd, cf)          # [co][kd][(ci,kh,kw)]
+            w2 = torch.nn.functional.pad(w2, (0, 64 - cf)).permute(0, 2, 1).reshape(cout, 64, kd, 1, 1).contiguous()
+            y, s, q = CV.conv_fprop(xc, w2, bias, (1, 1, 1), (pad[0], 0, 0), 1, act, slope, want_stats, out=out)
+        ctx.cfg = (pad, act, slope, tuple(w.shape), (cout, 64, kd, 1, 1))
         ctx.has_bias = bias is not None
         ctx.save_for_backward(x, w, y if act != ACT_NONE else None)
         if s is None:

@@ -15,7 +15,8 @@ from raygun_b200.cyclegan import make_generator
 from raygun_b200.synth import em_like_u8
 
 nb = int(sys.argv[1]) if len(sys.argv) > 1 and sys.argv[1].isdigit() else 2
-R, W = 256, 208
+R = int(os.environ.get("PREDICT_READ", "256"))
+W = R - 48
 side = nb * W + (R - W)
 dev = torch.device("cuda:0")
 rb.set_precision("bf16")
