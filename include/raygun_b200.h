@@ -132,6 +132,23 @@ int rg_stem_conv_supported(const rg_igemm_desc* desc);
 int rg_stem_conv_run(const rg_igemm_desc* desc, const void* x, long long x_channel_stride, const void* w64,
                      const float* bias, void* y, void* stream);
 
+/* ---- ConvTranspose3d, kernel = stride = 2 (upconv2_sm100.cu) -------------------------------------------------
+ * Forward of the U-Net up-sampling (`Upsample.up`, UNet.py:265-269) as one GEMM launch: every input voxel produces
+ * its 2x2x2 output voxels, D[voxel][(parity class, co)] = X[voxel][ci] . W[ci][(class, co)].  x: bf16 [n][Cin][d,h,w]
+ * channels innermost; y: bf16 [n][Cout][2d,2h,2w], channels innermost, any 16-byte aligned strides (e.g. a channel
+ * slice of the skip-concat buffer).  w_packed: bf16 [8][Cout][Cin], class = 4*pd + 2*ph + pw, i.e. the
+ * nn.ConvTranspose3d weight [Cin][Cout][2][2][2] permuted (2,3,4,1,0).                                          */
+typedef struct rg_upconv2_desc {
+  int32_t n, cin, cout;
+  int32_t in_dhw[3];
+  int64_t x_strides[4];  /* n,d,h,w element strides of x */
+  int64_t y_strides[4];  /* n,d,h,w element strides of y */
+  int32_t act; float slope;
+  int32_t has_bias, _pad;
+} rg_upconv2_desc;
+int rg_upconv2_supported(const rg_upconv2_desc* desc);
+int rg_upconv2_run(const rg_upconv2_desc* desc, const void* x, const void* w_packed, const float* bias, void* y, void* stream);
+
 /* ---- halo-resident weight gradient (stride 1; halo_wgrad_sm100.cu) ------------------------------------------
  * Same role as rg_igemm_wgrad (autograd of Conv3d, reference: torch.nn.Conv3d call sites UNet.py:69-87,
  * ResNet.py:262-327) for stride-1 layers: one X plane with its (kh,kw) halo per 128-voxel chunk serves every tap

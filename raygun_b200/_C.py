@@ -27,7 +27,7 @@ SYMBOLS = [
     "rg_conv3d_direct_fprop", "rg_conv3d_direct_dgrad", "rg_conv3d_direct_wgrad",
     "rg_plan_create", "rg_plan_destroy", "rg_plan_workspace_bytes", "rg_pack_weights",
     "rg_igemm_run", "rg_igemm_wgrad", "rg_ring_supported", "rg_ring_config", "rg_ring_pack_weights", "rg_ring_run",
-    "rg_stem_conv_supported", "rg_stem_conv_run",
+    "rg_stem_conv_supported", "rg_stem_conv_run", "rg_upconv2_supported", "rg_upconv2_run",
     "rg_halo_wgrad_supported", "rg_halo_wgrad_workspace_bytes", "rg_halo_wgrad",
     "rg_pw_conv_fprop", "rg_pw_conv_dgrad", "rg_pw_conv_wgrad",
     "rg_copy5", "rg_im2col_hw", "rg_pad3d_fwd", "rg_pad3d_bwd", "rg_pad_border_fill",
@@ -55,6 +55,12 @@ class IgemmDesc(C.Structure):
                 ("x_strides", C.c_int64 * 4), ("y_strides", C.c_int64 * 4),
                 ("act", C.c_int32), ("slope", C.c_float),
                 ("has_bias", C.c_int32), ("want_stats", C.c_int32), ("out_f32", C.c_int32)]
+
+
+class Upconv2Desc(C.Structure):
+    _fields_ = [("n", C.c_int32), ("cin", C.c_int32), ("cout", C.c_int32), ("in_dhw", C.c_int32 * 3),
+                ("x_strides", C.c_int64 * 4), ("y_strides", C.c_int64 * 4),
+                ("act", C.c_int32), ("slope", C.c_float), ("has_bias", C.c_int32), ("_pad", C.c_int32)]
 
 
 _lib = None

@@ -13,7 +13,7 @@ import torch
 
 from . import _C
 from . import kernels as K
-from ._C import ACT_NONE, ConvGeom, IgemmDesc, check, count_launch, i3, lib, ptr, require_device, stream_ptr, t5
+from ._C import ACT_NONE, ConvGeom, IgemmDesc, Upconv2Desc, check, count_launch, i3, lib, ptr, require_device, stream_ptr, t5
 
 stats = {"igemm": 0, "direct": 0}     # which path convolutions took (tests / bench inspect this)
 
@@ -212,6 +212,54 @@ def stem_conv_fprop(x, w, bias, pad, act=ACT_NONE, slope=0.0, out=None):
                                      stream_ptr(x.device)), "rg_stem_conv_run")
     count_launch()
     stats["stem_direct"] = stats.get("stem_direct", 0) + 1
+    return y
+
+
+UPCONV2 = os.environ.get("RAYGUN_B200_UPCONV2", "1") != "0"
+_up_packs: "dict[int, tuple]" = {}
+
+
+def upconv2_ok(x, w, stride, pad, out_pad, want_stats):
+    """ConvTranspose3d with kernel = stride = 2, no padding (U-Net `Upsample.up`, UNet.py:265-269): one fused launch."""
+    cin, cout = w.shape[0], w.shape[1]
+    return (UPCONV2 and not want_stats and tuple(w.shape[2:]) == (2, 2, 2) and tuple(stride) == (2, 2, 2)
+            and tuple(pad) == (0, 0, 0) and tuple(out_pad) == (0, 0, 0) and cin % 64 == 0 and 64 <= cin <= 512
+            and cout % 32 == 0 and 32 <= cout <= 512 and K.compute_dtype() == torch.bfloat16 and K.use_tensor_cores())
+
+
+def upconv2_fprop(x, w, bias, act=ACT_NONE, slope=0.0, out=None):
+    """y = ConvTranspose3d(x; w [Cin][Cout][2][2][2], stride 2): every input voxel writes its 2x2x2 output voxels."""
+    require_device(x)
+    n, cin, d, h, wd_ = x.shape
+    cout = w.shape[1]
+    xb = K.conv_operand(x)
+    shape = (n, cout, 2 * d, 2 * h, 2 * wd_)
+    if out is not None and tuple(out.shape) == shape and K.channels_inner_bf16(out):
+        y = out
+    elif K.arena_enabled():
+        y = K.empty5_arena(shape, torch.bfloat16, x.device)
+    else:
+        y = K.empty5(shape, torch.bfloat16, x.device)
+    ent = _up_packs.get(id(w))
+    if ent is None or ent[0]() is not w or ent[1] != w._version or ent[2] != w.data_ptr():
+        wp = w.detach().permute(2, 3, 4, 1, 0).reshape(8 * cout, cin).to(torch.bfloat16).contiguous()
+        if len(_up_packs) > 256:
+            for k in [k for k, e in _up_packs.items() if e[0]() is None]:
+                del _up_packs[k]
+        _up_packs[id(w)] = ent = (weakref.ref(w), w._version, w.data_ptr(), wp)
+    d_ = Upconv2Desc()
+    d_.n, d_.cin, d_.cout = n, cin, cout
+    d_.in_dhw[:] = [d, h, wd_]
+    d_.x_strides[:] = list(_sp_strides(xb))
+    d_.y_strides[:] = list(_sp_strides(y))
+    d_.act, d_.slope = act, float(slope)
+    d_.has_bias = 1 if bias is not None else 0
+    bias_f = bias.detach().float().contiguous() if bias is not None else None
+    with _Timed("fprop", 2.0 * xb.numel() * cout * 8, x.device, "upconv2_kernel"):
+        check(lib().rg_upconv2_run(C.byref(d_), ptr(xb), ptr(ent[3]), ptr(bias_f), ptr(y), stream_ptr(x.device)),
+              "rg_upconv2_run")
+    count_launch()
+    stats["upconv2"] = stats.get("upconv2", 0) + 1
     return y
 
 

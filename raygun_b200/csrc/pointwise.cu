@@ -14,48 +14,71 @@ struct PwW { const float* w; const float* bias; int cin, cout; };
 // One block per row (n, d, h); threads j*cg .. j*cg+cg-1 (cg = Cin/8, a power of two <= 32) share one voxel of the
 // row.  A thread keeps its channel group for the whole kernel, so its weights live in registers and the only index
 // arithmetic per 16-byte load is a shift (rows may be strided views: pad arenas, crops).
-template <typename TY>
+template <typename TY, int COUT>
 __global__ void __launch_bounds__(256) pw_fprop_kernel(PwW pw, T5 xd, const __nv_bfloat16* __restrict__ x, T5 yd,
                                                        TY* __restrict__ y, int act, float slope) {
   const int cg = pw.cin >> 3;
   const int lg = 31 - __clz(cg);
   const int cgi = threadIdx.x & (cg - 1), c = cgi << 3;
-  float wr[PW_MAX_COUT][8];
+  float wr[COUT][8];
 #pragma unroll
-  for (int co = 0; co < PW_MAX_COUT; ++co)
+  for (int co = 0; co < COUT; ++co)
 #pragma unroll
-    for (int k = 0; k < 8; ++k) wr[co][k] = co < pw.cout ? pw.w[co * pw.cin + c + k] : 0.f;
-  float br[PW_MAX_COUT];
+    for (int k = 0; k < 8; ++k) wr[co][k] = pw.w[co * pw.cin + c + k];
+  float br[COUT];
 #pragma unroll
-  for (int co = 0; co < PW_MAX_COUT; ++co) br[co] = (pw.bias && co < pw.cout) ? pw.bias[co] : 0.f;
+  for (int co = 0; co < COUT; ++co) br[co] = pw.bias ? pw.bias[co] : 0.f;
   const int W = (int)xd.w, H = (int)xd.h, D = (int)xd.d;
   const long long rows = xd.n * D * H;
   const int items = W << lg, items_up = (items + 31) & ~31;        // warp-uniform trip count for the shuffles
+  const int step = (int)blockDim.x;
   for (long long row = blockIdx.x; row < rows; row += gridDim.x) {
     const int h = (int)(row % H);
     const long long t = row / H;
     const int d = (int)(t % D), n = (int)(t / D);
     const __nv_bfloat16* xrow = x + n * xd.sn + d * xd.sd + h * xd.sh + c;
     TY* yrow = y + n * yd.sn + d * yd.sd + h * yd.sh;
-    for (int j = threadIdx.x; j < items_up; j += blockDim.x) {
-      const bool live = j < items;
-      const int w = j >> lg;
-      float acc[PW_MAX_COUT] = {0.f, 0.f, 0.f, 0.f};
-      if (live) {
-        float v[8];
-        ld8(xrow + (long long)w * xd.sw, v);
+    // two independent 16-byte loads in flight per thread and trip
+    for (int j0 = threadIdx.x; j0 < items_up; j0 += 2 * step) {
+      const int j1 = j0 + step;
+      const bool live0 = j0 < items, live1 = j1 < items;
+      const bool run1 = j1 < items_up;                              // warp-uniform
+      const int w0 = j0 >> lg, w1 = j1 >> lg;
+      float v0[8], v1[8];
+      if (live0) ld8(xrow + (long long)w0 * xd.sw, v0);
+      if (live1) ld8(xrow + (long long)w1 * xd.sw, v1);
+      float a0[COUT], a1[COUT];
 #pragma unroll
-        for (int co = 0; co < PW_MAX_COUT; ++co)
+      for (int co = 0; co < COUT; ++co) { a0[co] = 0.f; a1[co] = 0.f; }
+      if (live0) {
 #pragma unroll
-          for (int k = 0; k < 8; ++k) acc[co] = fmaf(v[k], wr[co][k], acc[co]);
+        for (int co = 0; co < COUT; ++co)
+#pragma unroll
+          for (int k = 0; k < 8; ++k) a0[co] = fmaf(v0[k], wr[co][k], a0[co]);
       }
-      for (int o = cg >> 1; o > 0; o >>= 1)
+      if (live1) {
 #pragma unroll
-        for (int co = 0; co < PW_MAX_COUT; ++co)
-          if (co < pw.cout) acc[co] += __shfl_xor_sync(0xffffffffu, acc[co], o);
-      if (live && cgi == 0) {
-        for (int co = 0; co < pw.cout; ++co)
-          stf(yrow + co * yd.sc + (long long)w * yd.sw, act_apply(acc[co] + br[co], act, slope));
+        for (int co = 0; co < COUT; ++co)
+#pragma unroll
+          for (int k = 0; k < 8; ++k) a1[co] = fmaf(v1[k], wr[co][k], a1[co]);
+      }
+      for (int o = cg >> 1; o > 0; o >>= 1) {
+#pragma unroll
+        for (int co = 0; co < COUT; ++co) a0[co] += __shfl_xor_sync(0xffffffffu, a0[co], o);
+        if (run1) {
+#pragma unroll
+          for (int co = 0; co < COUT; ++co) a1[co] += __shfl_xor_sync(0xffffffffu, a1[co], o);
+        }
+      }
+      if (cgi == 0) {
+        if (live0) {
+#pragma unroll
+          for (int co = 0; co < COUT; ++co) stf(yrow + co * yd.sc + (long long)w0 * yd.sw, act_apply(a0[co] + br[co], act, slope));
+        }
+        if (live1) {
+#pragma unroll
+          for (int co = 0; co < COUT; ++co) stf(yrow + co * yd.sc + (long long)w1 * yd.sw, act_apply(a1[co] + br[co], act, slope));
+        }
       }
     }
   }
@@ -152,7 +175,13 @@ int rg_pw_conv_fprop(const rg_tensor5* xd, const void* x, const float* w, const 
   if (total == 0) return RG_OK;
   cudaStream_t st = (cudaStream_t)stream;
   RG_DISPATCH_FLOAT(yd->dtype, TY, {
-    pw_fprop_kernel<TY><<<grid_for(xd->n * xd->d * xd->h, 1, 148 * 32), 256, 0, st>>>(pw, view(xd), (const __nv_bfloat16*)x, view(yd), (TY*)y, act, slope);
+    const int grid = grid_for(xd->n * xd->d * xd->h, 1, 148 * 32);
+    switch (pw.cout) {
+      case 1: pw_fprop_kernel<TY, 1><<<grid, 256, 0, st>>>(pw, view(xd), (const __nv_bfloat16*)x, view(yd), (TY*)y, act, slope); break;
+      case 2: pw_fprop_kernel<TY, 2><<<grid, 256, 0, st>>>(pw, view(xd), (const __nv_bfloat16*)x, view(yd), (TY*)y, act, slope); break;
+      case 3: pw_fprop_kernel<TY, 3><<<grid, 256, 0, st>>>(pw, view(xd), (const __nv_bfloat16*)x, view(yd), (TY*)y, act, slope); break;
+      default: pw_fprop_kernel<TY, 4><<<grid, 256, 0, st>>>(pw, view(xd), (const __nv_bfloat16*)x, view(yd), (TY*)y, act, slope); break;
+    }
   })
   RG_LAUNCH_CHECK("rg_pw_conv_fprop");
   return RG_OK;

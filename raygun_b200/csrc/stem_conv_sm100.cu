@@ -22,8 +22,11 @@ constexpr int ST_TH = 16, ST_TW = 8;
 constexpr int ST_STAGES = 6;                 // A tiles in flight (16 KB each)
 constexpr int ST_A_BYTES = 128 * 128;
 constexpr int ST_MAX_COUT = 256;
+constexpr int ST_STAGE_OUT = 32 * 64;          // epilogue staging: 32 voxels x 32 channels bf16, two buffers per warp
+constexpr int ST_OUT_BYTES = 8 * 2 * ST_STAGE_OUT;
 
-struct StemParams {
+struct alignas(64) StemParams {
+  CUtensorMap y_map;                         // 5-D {Cout, W, H, D, N} view of y; box {32, 8, 4, 1, 1}, 64B swizzle
   const __nv_bfloat16* x;
   long long xs_n, xs_c, xs_d, xs_h, xs_w;    // element strides of the input (any layout)
   int cin, kd, kh, kw, pd, ph, pw, K;
@@ -35,8 +38,6 @@ struct StemParams {
   int cout;
   const float* bias;
   int act; float slope;
-  __nv_bfloat16* y;
-  long long ys_n, ys_d, ys_h, ys_w;          // channels innermost
 };
 
 __device__ __forceinline__ void stem_tile_coords(const StemParams& p, long long t, int& n, int& d, int& h0, int& w0) {
@@ -58,7 +59,8 @@ __global__ void __launch_bounds__(ST_THREADS, 1) stem_conv_kernel(const __grid_c
   const uint32_t smem_a = base;
   const uint32_t smem_w = base + ST_STAGES * ST_A_BYTES;
   uint8_t* w_ptr = base_ptr + ST_STAGES * ST_A_BYTES;
-  uint8_t* tail = w_ptr + ST_MAX_COUT * 128;
+  uint8_t* out_stage = w_ptr + ST_MAX_COUT * 128;            // 1024-aligned
+  uint8_t* tail = out_stage + ST_OUT_BYTES;
   uint64_t* bars = reinterpret_cast<uint64_t*>(tail);      // afull[S] aempty[S] tfull[2] tempty[2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tail + 8 * (2 * ST_STAGES + 4));
   float* bias_s = reinterpret_cast<float*>(tail + 8 * (2 * ST_STAGES + 4) + 64);      // [ST_MAX_COUT]
@@ -73,6 +75,7 @@ __global__ void __launch_bounds__(ST_THREADS, 1) stem_conv_kernel(const __grid_c
     for (int s = 0; s < ST_STAGES; ++s) { ptx::mbar_init(afull(s), 128); ptx::mbar_init(aempty(s), 1); }
     for (int s = 0; s < 2; ++s) { ptx::mbar_init(tfull(s), 1); ptx::mbar_init(tempty(s), 256); }
     ptx::fence_mbar_init();
+    ptx::prefetch_tmap(&p.y_map);
   }
   if (warp == 0) ptx::tmem_alloc<512>(ptx::smem_u32(tmem_slot));
   // weights -> smem, K-major rows of 128 B with the 128B swizzle (16-byte chunk j of row r lands at chunk j ^ (r & 7))
@@ -215,10 +218,14 @@ __global__ void __launch_bounds__(ST_THREADS, 1) stem_conv_kernel(const __grid_c
     // ================= epilogue: thread = TMEM lane = output voxel; warp pair (quad, half) splits the channels ======
     const int quad = warp & 3;
     const int half = (warp - 9) >> 2;
-    const int v = quad * 32 + lane;
-    const int vh = v >> 3, vw = v & 7;
     const int act = p.act;
     const float slope = p.slope;
+    // a warp owns 4 (h) x 8 (w) voxels: 64 bytes per voxel and column group go through a 64B-swizzled staging
+    // buffer and one TMA store (full segments, clipped at the tensor edge) instead of per-lane scattered stores
+    uint8_t* my_stage = out_stage + (warp - 9) * 2 * ST_STAGE_OUT;
+    const uint32_t my_stage_u32 = ptx::smem_u32(my_stage);
+    const uint32_t row_off = (uint32_t)(lane * 64), sw = (uint32_t)((lane >> 1) & 3);
+    uint32_t gcount = 0;
     long long i = 0;
     for (long long t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++i) {
       int n, d, h0, w0;
@@ -226,17 +233,20 @@ __global__ void __launch_bounds__(ST_THREADS, 1) stem_conv_kernel(const __grid_c
       const int acc = (int)(i & 1);
       ptx::mbar_wait_backoff(tfull(acc), (uint32_t)((i >> 1) & 1));
       ptx::tc_fence_after();
-      const int h = h0 + vh, w = w0 + vw;
-      const bool valid = h < p.out_h && w < p.out_w;
-      __nv_bfloat16* dst = p.y + (long long)n * p.ys_n + (long long)d * p.ys_d + (long long)h * p.ys_h + (long long)w * p.ys_w;
       const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)acc * acc_cols;
-      for (int cb = half * 32; cb < p.cout; cb += 64) {
+      for (int cb = half * 32; cb < p.cout; cb += 64, ++gcount) {
         uint32_t r[32];
         ptx::tmem_ld_32x32(taddr + (uint32_t)cb, r);
+        if (lane == 0) ptx::tma_store_wait_read<1>();       // the store issued two groups ago has read this buffer
+        __syncwarp();
         ptx::tmem_ld_wait();
         float f[32];
 #pragma unroll
-        for (int c = 0; c < 32; ++c) f[c] = __uint_as_float(r[c]) + bias_s[cb + c];       // smem broadcast
+        for (int c = 0; c < 32; c += 4) {
+          const float4 b4 = *reinterpret_cast<const float4*>(bias_s + cb + c);
+          f[c] = __uint_as_float(r[c]) + b4.x; f[c + 1] = __uint_as_float(r[c + 1]) + b4.y;
+          f[c + 2] = __uint_as_float(r[c + 2]) + b4.z; f[c + 3] = __uint_as_float(r[c + 3]) + b4.w;
+        }
         if (act == RG_ACT_RELU) {
 #pragma unroll
           for (int c = 0; c < 32; ++c) f[c] = fmaxf(f[c], 0.f);
@@ -247,22 +257,28 @@ __global__ void __launch_bounds__(ST_THREADS, 1) stem_conv_kernel(const __grid_c
 #pragma unroll
           for (int c = 0; c < 32; ++c) f[c] = act_apply(f[c], act, slope);
         }
-        if (valid) {
+        uint8_t* dst = my_stage + (gcount & 1u) * ST_STAGE_OUT + row_off;
 #pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            uint32_t q[4];
+        for (int e = 0; e < 4; ++e) {
+          uint32_t q[4];
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-              const __nv_bfloat162 h2 = __floats2bfloat162_rn(f[8 * e + 2 * k], f[8 * e + 2 * k + 1]);
-              q[k] = *reinterpret_cast<const uint32_t*>(&h2);
-            }
-            reinterpret_cast<uint4*>(dst + cb)[e] = make_uint4(q[0], q[1], q[2], q[3]);
+          for (int k = 0; k < 4; ++k) {
+            const __nv_bfloat162 h2 = __floats2bfloat162_rn(f[8 * e + 2 * k], f[8 * e + 2 * k + 1]);
+            q[k] = *reinterpret_cast<const uint32_t*>(&h2);
           }
+          *reinterpret_cast<uint4*>(dst + (((uint32_t)e ^ sw) << 4)) = make_uint4(q[0], q[1], q[2], q[3]);
+        }
+        ptx::fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) {
+          ptx::tma_store_5d(&p.y_map, my_stage_u32 + (gcount & 1u) * ST_STAGE_OUT, cb, w0, h0 + quad * 4, d, n);
+          ptx::tma_store_commit();
         }
       }
       ptx::tc_fence_before();
       ptx::mbar_arrive(tempty(acc));
     }
+    if (lane == 0) ptx::tma_store_wait_all<0>();
   }
   ptx::tc_fence_before();
   __syncthreads();
@@ -350,9 +366,28 @@ int rg_stem_conv_run(const rg_igemm_desc* d, const void* x, long long x_channel_
   p.cout = d->cout;
   p.bias = d->has_bias ? bias : nullptr;
   p.act = d->act; p.slope = d->slope;
-  p.y = (__nv_bfloat16*)y;
-  p.ys_n = d->y_strides[0]; p.ys_d = d->y_strides[1]; p.ys_h = d->y_strides[2]; p.ys_w = d->y_strides[3];
-  const size_t smem = 1024 + (size_t)ST_STAGES * ST_A_BYTES + ST_MAX_COUT * 128 + 8 * (2 * ST_STAGES + 4) + 64 + ST_MAX_COUT * 4;
+  {
+    typedef CUresult (*EncFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                              const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                              CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    static EncFn enc = nullptr;
+    if (!enc) {
+      void* q = nullptr;
+      cudaDriverEntryPointQueryResult r;
+      if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &q, cudaEnableDefault, &r) == cudaSuccess && r == cudaDriverEntryPointSuccess)
+        enc = (EncFn)q;
+    }
+    if (!enc) { set_error("cuTensorMapEncodeTiled unavailable"); return RG_E_CUDA; }
+    cuuint64_t dims[5] = {(cuuint64_t)d->cout, (cuuint64_t)d->out_dhw[2], (cuuint64_t)d->out_dhw[1], (cuuint64_t)d->out_dhw[0], (cuuint64_t)d->n};
+    cuuint64_t gs[4] = {(cuuint64_t)(d->y_strides[3] * 2), (cuuint64_t)(d->y_strides[2] * 2), (cuuint64_t)(d->y_strides[1] * 2),
+                        (cuuint64_t)(d->y_strides[0] * 2)};
+    cuuint32_t bx[5] = {32, ST_TW, 4, 1, 1};
+    cuuint32_t es[5] = {1, 1, 1, 1, 1};
+    CUresult r = enc(&p.y_map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, y, dims, gs, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { set_error("stem conv: cuTensorMapEncodeTiled (output) failed: %d", (int)r); return RG_E_CUDA; }
+  }
+  const size_t smem = 1024 + (size_t)ST_STAGES * ST_A_BYTES + ST_MAX_COUT * 128 + ST_OUT_BYTES + 8 * (2 * ST_STAGES + 4) + 64 + ST_MAX_COUT * 4;
   const int grid = (int)(p.total_tiles < stem_num_sms() ? p.total_tiles : stem_num_sms());
   cudaStream_t st = (cudaStream_t)stream;
   const int ksteps = (p.K + 15) / 16;

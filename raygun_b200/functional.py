@@ -156,8 +156,11 @@ class _ConvTranspose3d(torch.autograd.Function):
         n, cin, d, h, wd_ = x.shape
         k = w.shape[2:]
         osz = [(i - 1) * s - 2 * p + kk + op for i, s, p, kk, op in zip((d, h, wd_), stride, pad, k, out_pad)]
-        y, s, q = CV.conv_dgrad(x, w, (n, w.shape[1], *osz), stride, pad, 1, bias=bias, act=act, slope=slope,
-                                want_stats=want_stats, out=out)
+        if CV.upconv2_ok(x, w, stride, pad, out_pad, want_stats):
+            y, s, q = CV.upconv2_fprop(x, w, bias, act, slope, out=out), None, None      # k = s = 2: one fused launch
+        else:
+            y, s, q = CV.conv_dgrad(x, w, (n, w.shape[1], *osz), stride, pad, 1, bias=bias, act=act, slope=slope,
+                                    want_stats=want_stats, out=out)
         ctx.geom = (stride, pad, act, slope)
         ctx.has_bias = bias is not None
         ctx.save_for_backward(x, w, y if act != ACT_NONE else None)
