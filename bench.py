@@ -154,6 +154,22 @@ def run_reference(args):
         return
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
+    if args.workload == "cfg3":
+        step, vox = cyclegan_cpu_fn(32)
+        step()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            step()
+        dt = (time.perf_counter() - t0) / args.steps
+        val = 1.0 / (dt * 8 * (64 ** 3 / vox))
+        sample = "one oracle CycleStep on one 1x32^3 sample pair per step, scaled x64 to the global batch of 8 x 64^3"
+        print(json.dumps(dict(metric="cyclegan_train_steps_per_sec", value=val, unit="steps/s", impl="reference",
+                              n_gpus=args.gpus, steps=args.steps, warmup=1, ms_per_step=1e3 / val, higher_is_better=True,
+                              scaling="strong", vs_baseline=None, dtype="f32", data="synthetic",
+                              config=dict(workload="cfg3: CycleGAN step, CPU oracle port", sample=sample),
+                              cpu_baseline=dict(value=val, unit="steps/s", cores=cores, kind="port", sample=sample),
+                              e2e=dict(value=val, unit="steps/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0))))
+        return
     if args.workload == "cfg4":
         step, vox = unet_cpu_fn(64)
         step()
@@ -425,13 +441,16 @@ def run_predict(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     rb.set_precision("bf16")
-    R, W = 256, 208                                    # read / write block (halo 24 >= 22, origins = 0 mod 4: SURVEY 8c)
+    R = int(args.read)                                 # read block; write block W = R - 48 (halo 24 >= 22, origins = 0 mod 4:
+    W = R - 48                                         # SURVEY 8c); recompute overhead (R/W)^3 = 1.41 at R = 448
     nb = (4, 4, 2)                                     # write blocks per axis: 32 blocks, a 880 x 880 x 464 volume
     shape = tuple(n * W + (R - W) for n in nb)
     torch.manual_seed(42)
     with contextlib.redirect_stdout(sys.stderr):
         g = make_generator("unet", dict(input_nc=1, output_nc=1, ngf=64, fmap_inc_factor=2, num_downs=3,
                                         padding_type="same", final_activation="Tanh")).to(dev).eval()
+    if R % 16 or R < 96:
+        raise SystemExit("--read must be a multiple of 16, >= 96")
     tile = em_like_u8((232, 220, 220), seed=42)        # synthetic EM-like texture, mirrored-tiled to the volume size
     reps = [-(-s // t) for s, t in zip(shape, tile.shape)]
     vol_np = np.tile(np.concatenate([tile, tile[::-1]], 0), (reps[0], 1, 1))[: shape[0]]
@@ -511,19 +530,167 @@ def run_predict(args):
         dist.destroy_process_group()
 
 
+# ---------------------------------------------------------------------------------------------
+# cfg3: full CycleGAN training step (2 x G-UNet + 2 x NLayerDiscriminator, LSGAN + SmoothL1 cycle loss, Adam),
+# global batch 8 of 1x64^3 patches per domain, data-parallel over batch with one gradient all-reduce per optimizer
+# ---------------------------------------------------------------------------------------------
+CYCLE_FLOP_PER_SAMPLE = 5.92e12        # 12 G-UNet passes + 16 D passes, algorithmic
+G_KW = dict(input_nc=1, output_nc=1, ngf=64, fmap_inc_factor=2, num_downs=3, padding_type="same", final_activation="Tanh")
+D_KW = dict(input_nc=1, ngf=64, n_layers=3, kw=3, downsampling_kw=2)
+
+
+def cyclegan_cpu_fn(side=32):
+    """One oracle CycleStep (reference LinkCycleLoss semantics, oracle/restate.py) on one sample pair, host cores."""
+    import functools
+    from oracle import restate as O
+    import raygun_b200.networks as N
+    from raygun_b200.cyclegan import make_generator
+    torch.manual_seed(42)
+    IN = functools.partial(torch.nn.InstanceNorm3d, affine=False, track_running_stats=False)
+    with contextlib.redirect_stdout(sys.stderr):
+        gs = [make_generator("unet", dict(G_KW)) for _ in range(2)]
+        ds = [N.NLayerDiscriminator(3, norm_layer=IN, **D_KW) for _ in range(2)]
+        for d in ds:
+            N.init_weights(d, "kaiming")
+    sds = [{k: v.detach().clone() for k, v in m.state_dict().items()} for m in gs + ds]
+    uspec = O.unet_spec(input_nc=1, ngf=64, fmap_inc_factor=2, downsample_factors=[(2, 2, 2)] * 2, padding_type="same")
+    dspec = O.nld_spec(input_nc=1, ngf=64, n_layers=3, norm=dict(kind="instance", affine=False), kw=3, downsampling_kw=2)
+    cs = O.CycleStep(*sds, g_fwd=lambda sd, x: O.generator_forward(sd, "unet", uspec, x, final_activation="Tanh"),
+                     d_fwd=lambda sd, x: O.nld3d_forward(sd, dspec, x))
+    a = O.u8_normalise(synth_batch(1, side, 42))
+    b = O.u8_normalise(synth_batch(1, side, 43))
+    return (lambda: cs.step(a, b)), side ** 3
+
+
+def run_cyclegan(args):
+    import functools
+    import torch.distributed as dist
+
+    import raygun_b200 as rb
+    from raygun_b200 import _C
+    from raygun_b200 import conv as CV
+    from raygun_b200 import kernels as K
+    from raygun_b200 import networks as N
+    from raygun_b200.cyclegan import CycleGANStep, make_generator
+    from raygun_b200.dist import GradSync
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (raygun_b200 has no CPU path; use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    rb.set_precision("bf16")
+    GLOBAL_BATCH, SIDE = 8, 64
+    if GLOBAL_BATCH % world:
+        raise SystemExit("cfg3: the global batch of 8 must divide over the ranks")
+    per = GLOBAL_BATCH // world
+    torch.manual_seed(42)                       # identical initial weights on every rank
+    IN = functools.partial(torch.nn.InstanceNorm3d, affine=False, track_running_stats=False)
+    with contextlib.redirect_stdout(sys.stderr):
+        g1, g2 = (make_generator("unet", dict(G_KW)).to(dev) for _ in range(2))
+        d1, d2 = (N.NLayerDiscriminator(3, norm_layer=IN, **D_KW).to(dev) for _ in range(2))
+        for d in (d1, d2):
+            N.init_weights(d, "kaiming")
+    sync = GradSync({"G": list(g1.parameters()) + list(g2.parameters()),
+                     "D": list(d1.parameters()) + list(d2.parameters())}) if world > 1 else None
+    step = CycleGANStep(g1, g2, d1, d2, lr=1e-5, grad_sync=sync)
+    host_a = synth_batch(per, SIDE, 42 + 100 * rank).pin_memory()
+    host_b = synth_batch(per, SIDE, 43 + 100 * rank).pin_memory()
+    dev_a = K.u8_normalise(host_a.to(dev), dtype=torch.bfloat16)
+    dev_b = K.u8_normalise(host_b.to(dev), dtype=torch.bfloat16)
+
+    def resident():
+        return step.step(dev_a, dev_b)
+
+    def e2e():
+        a = K.u8_normalise(host_a.to(dev, non_blocking=True), dtype=torch.bfloat16)
+        b = K.u8_normalise(host_b.to(dev, non_blocking=True), dtype=torch.bfloat16)
+        out = step.step(a, b)
+        return float(out["G1"])                 # D2H of a loss every step, as the reference's logging does
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            r = fn()
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1) / steps
+        if world > 1:
+            t = torch.tensor([ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t)
+        return ms, r
+
+    for _ in range(max(3, args.warmup)):
+        resident()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = _C.launch_count
+    ms, losses = timed(resident, args.steps)
+    launches = (_C.launch_count - l0) // args.steps
+    clocks = sampler.stop() if rank == 0 else None
+    ms_e2e, _ = timed(e2e, args.steps)
+    if rank == 0:
+        peaks = load_peaks()
+        alg = GLOBAL_BATCH * CYCLE_FLOP_PER_SAMPLE / (ms * 1e-3) / 1e12
+        cores = os.cpu_count() or 1
+        torch.set_num_threads(cores)
+        cstep, cvox = cyclegan_cpu_fn(32)
+        cstep()
+        t0 = time.perf_counter()
+        cstep()
+        cdt = time.perf_counter() - t0
+        cpu_steps = 1.0 / (cdt * GLOBAL_BATCH * (SIDE ** 3 / cvox))      # scaled to 8 samples of 64^3 (fully convolutional)
+        line = dict(metric="cyclegan_train_steps_per_sec", value=1e3 / ms, unit="steps/s", n_gpus=world, steps=args.steps,
+                    warmup=max(3, args.warmup), ms_per_step=ms, higher_is_better=True, scaling="strong", vs_baseline=None,
+                    dtype="bf16", data="synthetic",
+                    config=dict(workload="cfg3: CycleGAN step, 2 x G-UNet + 2 x NLayerDiscriminator(n_layers 3, kw 3), LSGAN + "
+                                         "SmoothL1 cycle loss (lambda 10/0/1), Adam lr 1e-5, global batch 8 of 1x64^3 per domain",
+                                per_gpu_batch=per, l2="activations of one step (GBs) >> 126 MB L2; no explicit flush",
+                                parallelism=f"dp{world}: one gradient all-reduce per optimizer step (G1+G2, D1+D2)"),
+                    e2e=dict(value=1e3 / ms_e2e, unit="steps/s", ms_per_step=ms_e2e,
+                             h2d_bytes_per_step=int(2 * per * SIDE ** 3), d2h_bytes_per_step=4),
+                    gpu_launches=int(launches),
+                    roofline=dict(bound="tensor", kernel="whole step (ring_conv_kernel / halo_wgrad_kernel dominant)", achieved=alg,
+                                  peak=peaks["tf_sustained"], unit="TFLOP/s", frac=alg / peaks["tf_sustained"],
+                                  peak_kind=f"{peaks['source']} sustained bf16 (burst {peaks['tf_burst']})", traffic=None,
+                                  algorithmic_tflop_per_step=GLOBAL_BATCH * CYCLE_FLOP_PER_SAMPLE / 1e12),
+                    cpu_baseline=dict(value=cpu_steps, unit="steps/s", cores=cores, kind="port",
+                                      sample="one oracle CycleStep on one 1x32^3 sample pair, scaled x64 to 8 samples of 64^3"),
+                    clocks=clocks, losses={k: float(v) for k, v in losses.items()}, conv_paths=dict(CV.stats))
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS) + ["cfg4"])
+    ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS) + ["cfg3", "cfg4"])
+    ap.add_argument("--read", type=int, default=448, help="cfg4: read block size (multiple of 16; write block = read - 48)")
     ap.add_argument("--no-graph", action="store_true", help="launch every kernel eagerly instead of replaying one CUDA graph")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
     elif args.workload == "cfg4":
         run_predict(args)
+    elif args.workload == "cfg3":
+        run_cyclegan(args)
     else:
         run_ours(args)
 

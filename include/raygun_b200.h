@@ -164,6 +164,11 @@ int rg_halo_wgrad(const rg_igemm_desc* desc, const void* x, const void* dy, floa
 int rg_pw_conv_fprop(const rg_tensor5* xd, const void* x, const float* w, const float* bias, int act, float slope,
                      const rg_tensor5* yd, void* y, void* stream);
 int rg_pw_conv_dgrad(const rg_tensor5* dyd, const void* dy, const float* w, const rg_tensor5* dxd, void* dx, void* stream);
+/* Data gradient of a convolution with <= 4 input channels and any kernel / stride / padding (the discriminator's first
+ * layer when the generator loss back-propagates through it, NLayerDiscriminator.py:137-145): dy bf16 channels
+ * innermost (Cout % 8 == 0), w fp32 [Cout][Cin][kD][kH][kW], dx any layout / dtype.                               */
+int rg_smallcin_dgrad(const rg_tensor5* dyd, const void* dy, const float* w, const rg_tensor5* dxd, void* dx,
+                      const rg_conv_geom* g, void* stream);
 int rg_pw_conv_wgrad(const rg_tensor5* xd, const void* x, const rg_tensor5* dyd, const void* dy, float* dw, float* dbias,
                      void* stream);
 

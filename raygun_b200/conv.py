@@ -448,6 +448,16 @@ def conv_dgrad(dy, w, x_shape, stride, pad, groups=1, bias=None, act=ACT_NONE, s
         count_launch()
         stats["pointwise"] = stats.get("pointwise", 0) + 1
         return dx, None, None
+    if (cin_t <= 4 and cout_t % 8 == 0 and groups == 1 and bias is None and act == ACT_NONE and K.channels_inner_bf16(dy)
+            and cin_t * cout_t * kernel[0] * kernel[1] * kernel[2] * 4 <= 48 * 1024):
+        # few input channels (discriminator stem under the generator loss): streaming kernel instead of the tiled GEMM
+        dx = K.empty5(tuple(x_shape), cdt, dy.device)
+        wc = w.detach().float().contiguous()
+        check(lib().rg_smallcin_dgrad(C.byref(t5(dy)), ptr(dy), ptr(wc), C.byref(t5(dx)), ptr(dx),
+                                      C.byref(_geom(kernel, stride, pad, groups)), stream_ptr(dy.device)), "rg_smallcin_dgrad")
+        count_launch()
+        stats["smallcin_dgrad"] = stats.get("smallcin_dgrad", 0) + 1
+        return dx, None, None
     dx = K.empty5(tuple(x_shape), cdt, dy.device)
     g = _geom(kernel, stride, pad, groups, act, slope)
     wc = w.detach()

@@ -159,6 +159,63 @@ static bool pw_shape_ok(int cin, int cout) {
   return cin % 8 == 0 && cg >= 1 && cg <= 32 && (cg & (cg - 1)) == 0 && cout >= 1 && cout <= PW_MAX_COUT;
 }
 
+
+// Data gradient of a convolution with <= 4 input channels (the discriminator's first layer, 1 -> ngf, k2 s2 p1,
+// NLayerDiscriminator.py:137-145, reached by the generator loss): dx[n,ci,i] = sum_{tap, co} dy[n,co,(i+p-k)/s] w[co,ci,k].
+// One thread per input voxel; dy rows (channels innermost, bf16) are read as 16-byte vectors; the weights sit in
+// shared memory as [tap][ci][co].  HBM-bound: Cout*2 bytes read per contributing tap.
+struct SmallDgradP { int cin, cout, kd, kh, kw, sd, sh, sw, pd, ph, pw; };
+
+template <typename TD>
+__global__ void __launch_bounds__(256) smallcin_dgrad_kernel(SmallDgradP g, T5 yd, const __nv_bfloat16* __restrict__ dy,
+                                                             const float* __restrict__ w, T5 xd, TD* __restrict__ dx) {
+  extern __shared__ float ws[];                       // [taps][cin][cout]
+  const int taps = g.kd * g.kh * g.kw;
+  for (int i = threadIdx.x; i < taps * g.cin * g.cout; i += blockDim.x) {
+    const int co = i % g.cout, ci = (i / g.cout) % g.cin, t = i / (g.cout * g.cin);
+    ws[i] = w[((long long)co * g.cin + ci) * taps + t];
+  }
+  __syncthreads();
+  const long long vox = xd.d * xd.h * xd.w, total = xd.n * vox;
+  for (long long v = blockIdx.x * (long long)blockDim.x + threadIdx.x; v < total; v += (long long)gridDim.x * blockDim.x) {
+    const long long n = v / vox;
+    long long r = v - n * vox;
+    const int iw = (int)(r % xd.w); r /= xd.w;
+    const int ih = (int)(r % xd.h), id = (int)(r / xd.h);
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+    for (int a = 0; a < g.kd; ++a) {
+      const int td = id + g.pd - a;
+      if (td < 0 || td % g.sd) continue;
+      const int od = td / g.sd;
+      if (od >= yd.d) continue;
+      for (int b = 0; b < g.kh; ++b) {
+        const int th = ih + g.ph - b;
+        if (th < 0 || th % g.sh) continue;
+        const int oh = th / g.sh;
+        if (oh >= yd.h) continue;
+        for (int c = 0; c < g.kw; ++c) {
+          const int tw = iw + g.pw - c;
+          if (tw < 0 || tw % g.sw) continue;
+          const int ow = tw / g.sw;
+          if (ow >= yd.w) continue;
+          const __nv_bfloat16* row = dy + n * yd.sn + od * yd.sd + oh * yd.sh + ow * yd.sw;
+          const float* wt = ws + ((a * g.kh + b) * g.kw + c) * g.cin * g.cout;
+          for (int c8 = 0; c8 < g.cout; c8 += 8) {
+            float q[8];
+            ld8(row + c8, q);
+            for (int ci = 0; ci < g.cin; ++ci) {
+              const float* wc = wt + ci * g.cout + c8;
+#pragma unroll
+              for (int k = 0; k < 8; ++k) acc[ci] = fmaf(q[k], wc[k], acc[ci]);
+            }
+          }
+        }
+      }
+    }
+    for (int ci = 0; ci < g.cin; ++ci) stf(dx + xd.off(n, ci, id, ih, iw), acc[ci]);
+  }
+}
+
 }  // namespace rg
 
 using namespace rg;
@@ -221,5 +278,26 @@ int rg_pw_conv_wgrad(const rg_tensor5* xd, const void* x, const rg_tensor5* dyd,
   RG_LAUNCH_CHECK("rg_pw_conv_wgrad");
   return RG_OK;
 }
+
+int rg_smallcin_dgrad(const rg_tensor5* dyd, const void* dy, const float* w, const rg_tensor5* dxd, void* dx,
+                      const rg_conv_geom* g, void* stream) {
+  RG_CHECK_ARG(dyd && dy && w && dxd && dx && g, "rg_smallcin_dgrad: null argument");
+  RG_UNSUPPORTED(dxd->c < 1 || dxd->c > 4 || dyd->c % 8 != 0 || g->groups != 1, "rg_smallcin_dgrad: needs Cin <= 4, Cout % 8 == 0");
+  RG_UNSUPPORTED(dyd->dtype != RG_BF16 || !vec_ok(dyd, dy), "rg_smallcin_dgrad: dy must be bf16 with channels innermost");
+  const int taps = g->kernel[0] * g->kernel[1] * g->kernel[2];
+  const size_t smem = (size_t)taps * dxd->c * dyd->c * sizeof(float);
+  RG_UNSUPPORTED(smem > 48 * 1024, "rg_smallcin_dgrad: weights do not fit shared memory");
+  SmallDgradP p{(int)dxd->c, (int)dyd->c, g->kernel[0], g->kernel[1], g->kernel[2], g->stride[0], g->stride[1], g->stride[2],
+                g->pad[0], g->pad[1], g->pad[2]};
+  const long long total = dxd->n * dxd->d * dxd->h * dxd->w;
+  if (total == 0) return RG_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  RG_DISPATCH_FLOAT(dxd->dtype, TD, {
+    smallcin_dgrad_kernel<TD><<<grid_for(total, 256), 256, smem, st>>>(p, view(dyd), (const __nv_bfloat16*)dy, w, view(dxd), (TD*)dx);
+  })
+  RG_LAUNCH_CHECK("rg_smallcin_dgrad");
+  return RG_OK;
+}
+
 
 }  // extern "C"

@@ -55,8 +55,31 @@ class _Conv3d(torch.autograd.Function):
     Returns (y, sum, sqsum): the statistics feed the following norm layer (non-differentiable)."""
 
     @staticmethod
+    def _narrow_out(x, w, stride, groups, want_stats):
+        """Few produced channels over a wide reduction (the discriminator's last conv, 512 -> 1, 3^3,
+        NLayerDiscriminator.py:166-174): run it on the tensor cores with the produced channels zero-padded to 64
+        instead of the CUDA-core kernel (64x the FLOPs of a 5832-voxel layer is still microseconds)."""
+        cout, cin = w.shape[0], w.shape[1]
+        return (cout < 64 and cin % 64 == 0 and groups == 1 and tuple(stride) == (1, 1, 1) and not want_stats
+                and w.shape[2] * w.shape[3] * w.shape[4] > 1 and K.compute_dtype() == torch.bfloat16
+                and K.use_tensor_cores() and x.is_cuda)
+
+    @staticmethod
     def forward(ctx, x, w, bias, stride, pad, groups, act, slope, want_stats, out=None):
-        y, s, q = CV.conv_fprop(x, w, bias, stride, pad, groups, act, slope, want_stats, out=out)
+        ctx.narrow = _Conv3d._narrow_out(x, w, stride, groups, want_stats)
+        if ctx.narrow:
+            cout = w.shape[0]
+            wp = torch.zeros(64, *w.shape[1:], dtype=w.dtype, device=w.device)
+            wp[:cout] = w.detach()
+            bp = None
+            if bias is not None:
+                bp = torch.zeros(64, dtype=torch.float32, device=w.device)
+                bp[:cout] = bias.detach()
+            yp, _, _ = CV.conv_fprop(x, wp, bp, stride, pad, groups, act, slope, False)
+            y = K.copy_into(K.empty5((yp.shape[0], cout, *yp.shape[2:]), yp.dtype, yp.device), yp[:, :cout])
+            s = q = None
+        else:
+            y, s, q = CV.conv_fprop(x, w, bias, stride, pad, groups, act, slope, want_stats, out=out)
         ctx.geom = (stride, pad, groups, act, slope)
         ctx.has_bias = bias is not None
         ctx.save_for_backward(x, w, y if act != ACT_NONE else None)
@@ -72,6 +95,20 @@ class _Conv3d(torch.autograd.Function):
         if act != ACT_NONE:
             dy = K.act_bwd(y, dy, act, slope)
         dx = dw = db = None
+        if ctx.narrow:
+            cout = w.shape[0]
+            dyp = torch.zeros(dy.shape[0], 64, *dy.shape[2:], dtype=torch.bfloat16, device=dy.device).contiguous(
+                memory_format=torch.channels_last_3d)
+            K.copy_into(dyp[:, :cout], dy)
+            wp = torch.zeros(64, *w.shape[1:], dtype=w.dtype, device=w.device)
+            wp[:cout] = w.detach()
+            if ctx.needs_input_grad[0]:
+                dx, _, _ = CV.conv_dgrad(dyp, wp, x.shape, stride, pad, groups, out_dtype=x.dtype)
+            if ctx.needs_input_grad[1] or (ctx.has_bias and ctx.needs_input_grad[2]):
+                dwp, dbp = CV.conv_wgrad(x, dyp, wp.shape, stride, pad, groups, want_bias=ctx.has_bias)
+                dw = dwp[:cout].contiguous() if ctx.needs_input_grad[1] else None
+                db = dbp[:cout].contiguous() if dbp is not None else None
+            return dx, dw, db, None, None, None, None, None, None, None
         if ctx.needs_input_grad[0]:
             dx, _, _ = CV.conv_dgrad(dy, w, x.shape, stride, pad, groups, out_dtype=x.dtype)
         if ctx.needs_input_grad[1] or (ctx.has_bias and ctx.needs_input_grad[2]):

@@ -165,3 +165,34 @@ def test_unet_inference_arena_path_equals_copy_path(monkeypatch):
     rel_rms = float((y_arena - y32).norm() / y32.norm())
     assert rel_rms <= 2e-2, rel_rms
     assert float((y_arena - y32).abs().max()) <= 4e-2 * max(1.0, float(y32.abs().max()))
+
+
+def test_blockwise_prediction_is_independent_of_the_block_size_at_large_blocks():
+    """Full-size property for cfg4: with halo 24 (>= 22) and block origins = 0 mod 4 the written voxels do not depend on
+    the block geometry, so one 384^3 read block (64-bit offsets, > 2^31-element tensors, many waves of tiles in every
+    kernel) must reproduce what eight 192^3 read blocks write on the region both cover."""
+    import contextlib
+    import sys
+    import raygun_b200 as rb
+    from raygun_b200 import predict as P
+    from raygun_b200.cyclegan import make_generator
+    from raygun_b200.synth import em_like_u8
+    torch.manual_seed(42)
+    with rb.precision("bf16"):
+        with contextlib.redirect_stdout(sys.stderr):
+            g = make_generator("unet", dict(input_nc=1, output_nc=1, ngf=64, fmap_inc_factor=2, num_downs=3,
+                                            padding_type="same", final_activation="Tanh")).to(DEV).eval()
+        vol = torch.from_numpy(em_like_u8((384, 384, 384), seed=7)).to(DEV)
+        big, nb_big, _ = P.predict_volume(g, vol, (384,) * 3, (336,) * 3, out=torch.zeros_like(vol), dtype=torch.bfloat16)
+        small, nb_small, _ = P.predict_volume(g, vol, (192,) * 3, (144,) * 3, out=torch.zeros_like(vol), dtype=torch.bfloat16)
+    assert nb_big == 1 and nb_small == 8
+    a = big[24:312, 24:312, 24:312].int()
+    b = small[24:312, 24:312, 24:312].int()
+    diff = (a - b).abs()
+    # Not bit-identical by design: which input slices of a 3^3 conv share a slice group of the ring kernel depends on
+    # the block's depth partition, so the fp32 accumulation ORDER of a voxel (not its terms) varies with the geometry;
+    # one bf16 ulp of the tanh output is up to one uint8 level.  Wrong addressing at these sizes would be garbage.
+    assert int(diff.max()) <= 2, int(diff.max())
+    assert float((diff > 1).float().mean()) <= 1e-4
+    assert float(diff.float().mean()) <= 0.25
+    assert float(a.float().std()) > 1.0                               # not a constant image

@@ -382,3 +382,43 @@ def test_strided_channel_inner_views_are_conv_operands_in_place():
         a, _, _ = CV.conv_fprop(x, w3, None, (1, 1, 1), (1, 1, 1), 1, 0, 0.0)
         b, _, _ = CV.conv_fprop(xd, w3, None, (1, 1, 1), (1, 1, 1), 1, 0, 0.0)
         assert torch.equal(a.float(), b.float())
+
+
+def test_discriminator_edge_layers_leave_the_cuda_core_gemm():
+    """NLayerDiscriminator edge layers in bf16 mode: the 1 -> 64 k2 s2 p1 stem's data gradient (streaming small-Cin
+    kernel) and the 512 -> 1 3^3 head (tensor cores with the produced channel zero-padded to 64) against autograd."""
+    import raygun_b200 as rb
+    from raygun_b200 import conv as CV, functional as F
+    torch.manual_seed(8)
+    q = lambda t: t.bfloat16().float()
+    # stem: conv 1 -> 64, kernel 2, stride 2, padding 1 on 16^3 (-> 9^3); gradient w.r.t. the image
+    x = q(torch.randn(2, 1, 16, 16, 16)).requires_grad_(True)
+    w = q(torch.randn(64, 1, 2, 2, 2) * 0.3)
+    y = TF.conv3d(x, w, None, stride=2, padding=1)
+    dy = q(torch.randn_like(y))
+    (ref,) = torch.autograd.grad(y, x, dy)
+    with rb.precision("bf16"):
+        before = CV.stats.get("smallcin_dgrad", 0)
+        dyg = dy.to(DEV).bfloat16().contiguous(memory_format=torch.channels_last_3d)
+        dx, _, _ = CV.conv_dgrad(dyg, w.to(DEV), (2, 1, 16, 16, 16), (2, 2, 2), (1, 1, 1))
+        assert CV.stats.get("smallcin_dgrad", 0) == before + 1
+    assert float((dx.float().cpu() - ref).abs().max()) <= 1e-2 * float(ref.abs().max())
+    # head: conv 512 -> 1, 3^3, padding 1 on 9^3, forward + all three gradients through the functional API
+    conv = torch.nn.Conv3d(512, 1, 3, padding=1)
+    with torch.no_grad():
+        conv.weight.copy_(q(conv.weight))
+    xh = q(torch.randn(2, 512, 9, 9, 9)).requires_grad_(True)
+    yh = conv(xh)
+    g = q(torch.randn_like(yh))
+    rx, rw, rb_ = torch.autograd.grad(yh, [xh, conv.weight, conv.bias], g)
+    with rb.precision("bf16"):
+        d0 = CV.stats["direct"]
+        xg = xh.detach().to(DEV).bfloat16().contiguous(memory_format=torch.channels_last_3d).requires_grad_(True)   # compute storage
+        wg = conv.weight.detach().to(DEV).requires_grad_(True)
+        bg = conv.bias.detach().to(DEV).requires_grad_(True)
+        yg = F.conv3d(xg, wg, bg, 1, 1)
+        yg.backward(g.to(DEV).to(yg.dtype))
+        assert CV.stats["direct"] == d0, "the CUDA-core GEMM ran"
+    rel = lambda a, b: float((a.float().cpu() - b).abs().max()) / max(1e-6, float(b.abs().max()))
+    assert tuple(yg.shape) == tuple(yh.shape) and rel(yg, yh) <= 1e-2
+    assert rel(xg.grad, rx) <= 1e-2 and rel(wg.grad, rw) <= 1e-2 and rel(bg.grad, rb_) <= 1e-2
