@@ -190,7 +190,7 @@ int rg_im2col_hw(const rg_tensor5* xd, const void* x, int kh, int kw, int ph, in
  *      UNet.py:61-69 padding_mode="reflect") and its adjoint ----------------------------*/
 int rg_pad3d_fwd(const rg_tensor5* xd, const void* x, const rg_tensor5* yd, void* y,
                  const int32_t lo[3], int mode, void* stream);
-/* dx (zeroed by caller) += fold(dy) */
+/* dx = fold(dy): the adjoint of rg_pad3d_fwd (every dx element is written; no zero-initialisation needed) */
 int rg_pad3d_bwd(const rg_tensor5* dyd, const void* dy, const rg_tensor5* dxd, void* dx,
                  const int32_t lo[3], int mode, void* stream);
 /* In-place fill of the `margin`-voxel shell of a padded bf16 NDHWC buffer whose interior is already written (the

@@ -448,6 +448,16 @@ def conv_dgrad(dy, w, x_shape, stride, pad, groups=1, bias=None, act=ACT_NONE, s
         count_launch()
         stats["pointwise"] = stats.get("pointwise", 0) + 1
         return dx, None, None
+    if (cin_t < 64 and cout_t % 64 == 0 and groups == 1 and tuple(stride) == (1, 1, 1) and bias is None and act == ACT_NONE
+            and kernel[0] * kernel[1] * kernel[2] > 8 and cdt == torch.bfloat16 and K.use_tensor_cores()
+            and _igemm_ok(64, cout_t, kernel, stride, groups)):
+        # few input channels, many taps (the U-Net stem under a cycle loss, UNet.py:52-87): tensor cores with the
+        # produced channels zero-padded to 64 instead of streaming Cout * taps values per voxel
+        wp = torch.zeros(cout_t, 64, *kernel, dtype=w.dtype, device=w.device)
+        wp[:, :cin_t] = w.detach()
+        dxp, _, _ = conv_dgrad(dy, wp, (n, 64, *x_shape[2:]), stride, pad, groups, out_dtype=torch.bfloat16)
+        dx = K.copy_into(K.empty5(tuple(x_shape), cdt, dy.device), dxp[:, :cin_t])
+        return dx, None, None
     if (cin_t <= 4 and cout_t % 8 == 0 and groups == 1 and bias is None and act == ACT_NONE and K.channels_inner_bf16(dy)
             and cin_t * cout_t * kernel[0] * kernel[1] * kernel[2] * 4 <= 48 * 1024):
         # few input channels (discriminator stem under the generator loss): streaming kernel instead of the tiled GEMM

@@ -107,7 +107,7 @@ __global__ void pad_bwd_kernel(T5 dyd, const TS* __restrict__ dy, T5 dxd, TD* __
       for (int b = 0; b < nh; ++b)
         for (int e = 0; e < nw; ++e) acc += ldf(dy + dyd.off(p.n, p.c, ld[a], lh[b], lw[e]));
     TD* q = dx + dxd.off(p.n, p.c, p.d, p.h, p.w);
-    stf(q, acc + ldf(q));
+    stf(q, acc);
   }
 }
 
@@ -203,9 +203,8 @@ __global__ void vec_pad_bwd_kernel(T5 gd, const __nv_bfloat16* __restrict__ dy, 
     VIdx p = vunravel(i, dxd);
     const int nd = pad_npre(p.d, lo_d, hi_d, dxd.d, mode), nh = pad_npre(p.h, lo_h, hi_h, dxd.h, mode),
               nw = pad_npre(p.w, lo_w, hi_w, dxd.w, mode);
-    float acc[8];
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     __nv_bfloat16* q = dx + voff(dxd, p.n, p.d, p.h, p.w, p.c);
-    ld8(q, acc);
     for (int a = 0; a < nd; ++a) {
       const long long od = pad_pre(p.d, a, lo_d, hi_d, dxd.d, mode);
       for (int b = 0; b < nh; ++b) {
@@ -220,6 +219,45 @@ __global__ void vec_pad_bwd_kernel(T5 gd, const __nv_bfloat16* __restrict__ dy, 
       }
     }
     st8(q, acc);
+  }
+}
+
+// Row-based adjoint of the padding for NDHWC bf16 (the reflect pads of every 'same' ConvPass / ResnetBlock in a
+// training step): one block per dx row (n, d, h).  The (d, h) pre-image rows are found once per block; a thread owns
+// (w, 8 channels) items of the row and adds the <= 3 w pre-images of each source row.  No per-element index division.
+__global__ void __launch_bounds__(256) row_pad_bwd_kernel(T5 gd, const __nv_bfloat16* __restrict__ dy, T5 dxd,
+                                                          __nv_bfloat16* __restrict__ dx, int lo_d, int lo_h, int lo_w, int mode) {
+  const long long hi_d = gd.d - dxd.d - lo_d, hi_h = gd.h - dxd.h - lo_h, hi_w = gd.w - dxd.w - lo_w;
+  const int W = (int)dxd.w, H = (int)dxd.h, D = (int)dxd.d, cg = (int)(dxd.c >> 3);
+  const long long rows = dxd.n * D * H;
+  const int items = W * cg;
+  for (long long row = blockIdx.x; row < rows; row += gridDim.x) {
+    const int h = (int)(row % H);
+    const long long t = row / H;
+    const int d = (int)(t % D);
+    const long long n = t / D;
+    const int nd = pad_npre(d, lo_d, hi_d, D, mode), nh = pad_npre(h, lo_h, hi_h, H, mode);
+    __nv_bfloat16* xrow = dx + n * dxd.sn + d * dxd.sd + h * dxd.sh;
+    for (int j = threadIdx.x; j < items; j += blockDim.x) {
+      const int w = j / cg, c = (j - w * cg) << 3;
+      const int nw = pad_npre(w, lo_w, hi_w, W, mode);
+      float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      for (int a = 0; a < nd; ++a) {
+        const long long od = pad_pre(d, a, lo_d, hi_d, D, mode);
+        for (int b = 0; b < nh; ++b) {
+          const long long oh = pad_pre(h, b, lo_h, hi_h, H, mode);
+          const __nv_bfloat16* srow = dy + n * gd.sn + od * gd.sd + oh * gd.sh + c;
+          for (int e = 0; e < nw; ++e) {
+            const long long ow = pad_pre(w, e, lo_w, hi_w, W, mode);
+            float v[8];
+            ld8(srow + ow * gd.sw, v);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) acc[k] += v[k];
+          }
+        }
+      }
+      st8(xrow + (long long)w * dxd.sw + c, acc);
+    }
   }
 }
 
@@ -381,6 +419,12 @@ int rg_pad3d_bwd(const rg_tensor5* dyd, const void* dy, const rg_tensor5* dxd, v
   long long total = view(dxd).numel();
   if (total == 0) return RG_OK;
   cudaStream_t st = (cudaStream_t)stream;
+  if (vec_ok(dyd, dy) && vec_ok(dxd, dx) && dxd->w * (dxd->c >> 3) >= 64 && dxd->w * (dxd->c >> 3) < (1LL << 30)) {
+    row_pad_bwd_kernel<<<grid_for(dxd->n * dxd->d * dxd->h, 1, 148 * 16), 256, 0, st>>>(view(dyd), (const __nv_bfloat16*)dy, view(dxd),
+                                                                                     (__nv_bfloat16*)dx, lo[0], lo[1], lo[2], mode);
+    RG_LAUNCH_CHECK("rg_pad3d_bwd(row)");
+    return RG_OK;
+  }
   if (vec_ok(dyd, dy) && vec_ok(dxd, dx)) {
     vec_pad_bwd_kernel<<<grid_for(total >> 3, 256), 256, 0, st>>>(view(dyd), (const __nv_bfloat16*)dy, view(dxd), (__nv_bfloat16*)dx, lo[0], lo[1], lo[2], mode);
     RG_LAUNCH_CHECK("rg_pad3d_bwd(vec)");

@@ -203,16 +203,24 @@ __global__ void __launch_bounds__(256) smallcin_dgrad_kernel(SmallDgradP g, T5 y
           for (int c8 = 0; c8 < g.cout; c8 += 8) {
             float q[8];
             ld8(row + c8, q);
-            for (int ci = 0; ci < g.cin; ++ci) {
-              const float* wc = wt + ci * g.cout + c8;
 #pragma unroll
-              for (int k = 0; k < 8; ++k) acc[ci] = fmaf(q[k], wc[k], acc[ci]);
+            for (int ci = 0; ci < 4; ++ci) {          // static indices keep acc[] in registers
+              if (ci < g.cin) {
+                const float4* wc = reinterpret_cast<const float4*>(wt + ci * g.cout + c8);
+                const float4 w0 = wc[0], w1 = wc[1];
+                acc[ci] = fmaf(q[0], w0.x, acc[ci]); acc[ci] = fmaf(q[1], w0.y, acc[ci]);
+                acc[ci] = fmaf(q[2], w0.z, acc[ci]); acc[ci] = fmaf(q[3], w0.w, acc[ci]);
+                acc[ci] = fmaf(q[4], w1.x, acc[ci]); acc[ci] = fmaf(q[5], w1.y, acc[ci]);
+                acc[ci] = fmaf(q[6], w1.z, acc[ci]); acc[ci] = fmaf(q[7], w1.w, acc[ci]);
+              }
             }
           }
         }
       }
     }
-    for (int ci = 0; ci < g.cin; ++ci) stf(dx + xd.off(n, ci, id, ih, iw), acc[ci]);
+#pragma unroll
+    for (int ci = 0; ci < 4; ++ci)
+      if (ci < g.cin) stf(dx + xd.off(n, ci, id, ih, iw), acc[ci]);
   }
 }
 

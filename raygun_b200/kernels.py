@@ -182,8 +182,7 @@ def pad3d(x, lo, hi, mode):
 
 
 def pad3d_bwd(dy, x_shape, lo, mode):
-    dx = empty5(x_shape, dy.dtype, dy.device)
-    dx.zero_()  # memset (driver), not a compute kernel
+    dx = empty5(x_shape, dy.dtype, dy.device)          # fully written by the kernel
     check(lib().rg_pad3d_bwd(C.byref(t5(dy)), ptr(dy), C.byref(t5(dx)), ptr(dx), i3(lo), C.c_int(mode),
                              stream_ptr(dy.device)), "rg_pad3d_bwd")
     count_launch()

@@ -246,10 +246,11 @@ def _ndhwc(t):
 
 @pytest.mark.parametrize("mode", ["reflect", "replicate", "zeros"])
 @pytest.mark.parametrize("lo,hi", [((1, 1, 1), (1, 1, 1)), ((3, 3, 3), (3, 3, 3)), ((0, 2, 1), (2, 0, 1))])
-def test_vec_pad_and_adjoint_bf16_ndhwc(mode, lo, hi):
+@pytest.mark.parametrize("c", [16, 64])          # 64 channels x 9 voxels per row: the row-based adjoint kernel
+def test_vec_pad_and_adjoint_bf16_ndhwc(mode, lo, hi, c):
     from raygun_b200 import functional as F
     torch.manual_seed(21)
-    x = _bf(torch.randn(2, 16, 5, 6, 7)).requires_grad_(True)
+    x = _bf(torch.randn(2, c, 5, 6, 9 if c == 64 else 7)).requires_grad_(True)
     pads = (lo[2], hi[2], lo[1], hi[1], lo[0], hi[0])
     y_ref = TF.pad(x, pads, mode={"zeros": "constant"}.get(mode, mode))
     r = _bf(torch.randn_like(y_ref))
