@@ -519,9 +519,9 @@ def run_predict(args):
                                  h2d_bytes_per_step=int(nblk_all * R ** 3), d2h_bytes_per_step=int(vox_all)),
                         gpu_launches=int(launches),
                         roofline=dict(bound="tensor", kernel="whole block pipeline (ring_conv_kernel dominant)", achieved=alg,
-                                      executed_incl_halo=exe, peak=peaks["tf_sustained"], unit="TFLOP/s",
-                                      frac=alg / peaks["tf_sustained"], frac_executed=exe / peaks["tf_sustained"],
-                                      peak_kind=f"{peaks['source']} sustained bf16 (burst {peaks['tf_burst']})", traffic=None),
+                                      executed_incl_halo=exe, peak=peaks["tf_sustained"] * world, unit="TFLOP/s",
+                                      frac=alg / (peaks["tf_sustained"] * world), frac_executed=exe / (peaks["tf_sustained"] * world),
+                                      peak_kind=f"{peaks['source']} sustained bf16 x {world} GPUs (burst {peaks['tf_burst']})", traffic=None),
                         cpu_baseline=dict(value=cvox / cdt, unit="voxels/s", cores=cores, kind="port",
                                           sample="cfg1: G-UNet forward on 1x1x64^3, fp32, oracle/restate.py, 1 warm-up + 1 timed"),
                         clocks=clocks, conv_paths=dict(CV.stats))
@@ -664,8 +664,8 @@ def run_cyclegan(args):
                              h2d_bytes_per_step=int(2 * per * SIDE ** 3), d2h_bytes_per_step=4),
                     gpu_launches=int(launches),
                     roofline=dict(bound="tensor", kernel="whole step (ring_conv_kernel / halo_wgrad_kernel dominant)", achieved=alg,
-                                  peak=peaks["tf_sustained"], unit="TFLOP/s", frac=alg / peaks["tf_sustained"],
-                                  peak_kind=f"{peaks['source']} sustained bf16 (burst {peaks['tf_burst']})", traffic=None,
+                                  peak=peaks["tf_sustained"] * world, unit="TFLOP/s", frac=alg / (peaks["tf_sustained"] * world),
+                                  peak_kind=f"{peaks['source']} sustained bf16 x {world} GPUs (burst {peaks['tf_burst']})", traffic=None,
                                   algorithmic_tflop_per_step=GLOBAL_BATCH * CYCLE_FLOP_PER_SAMPLE / 1e12),
                     cpu_baseline=dict(value=cpu_steps, unit="steps/s", cores=cores, kind="port",
                                       sample="one oracle CycleStep on one 1x32^3 sample pair, scaled x64 to 8 samples of 64^3"),
