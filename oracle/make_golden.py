@@ -159,13 +159,46 @@ def make_cycle(R):
     np.savez_compressed(os.path.join(OUT, "cycle_step.npz"), **out)
 
 
+def make_split_cycle(R):
+    """Three SplitCycleLoss steps (CycleModel(split=True), one optimizer per generator) from the SAME initial weights
+    and batches as cycle_step.npz: only the reference losses are stored (split_cycle_step.npz)."""
+    z = np.load(os.path.join(OUT, "cycle_step.npz"))
+    spec = json.loads(bytes(z["spec"]).decode())
+    gkw, dkw = spec["gkw"], spec["dkw"]
+    mk_g = lambda: torch.nn.Sequential(R.ResNet(3, **gkw), torch.nn.Conv3d(4, 1, 1), torch.nn.Tanh())
+    mk_d = lambda: R.NLayerDiscriminator(3, norm_layer=_norm_layer(IN3), **dkw)
+    nets = [mk_g(), mk_g(), mk_d(), mk_d()]
+    for nm, n in zip(("g1", "g2", "d1", "d2"), nets):
+        pre = f"sd/{nm}/"
+        n.load_state_dict({k[len(pre):]: torch.from_numpy(z[k]).clone() for k in z.files if k.startswith(pre)})
+    G1, G2, D1, D2 = nets
+    oG1 = torch.optim.Adam(G1.parameters(), lr=1e-3)
+    oG2 = torch.optim.Adam(G2.parameters(), lr=1e-3)
+    oD = torch.optim.Adam(itertools.chain(D1.parameters(), D2.parameters()), lr=1e-3)
+    model = R.CycleModel(G1, G2, split=True)
+    loss = R.SplitCycleLoss(D1, G1, D2, G2, oG1, oG2, oD, 3)
+    losses = []
+    for it in range(3):
+        a, b = torch.from_numpy(z[f"a{it}"]), torch.from_numpy(z[f"b{it}"])
+        fb, cb, fa, ca = model(a, b)
+        loss(a, fa, ca, b, fb, cb)
+        losses.append([loss.loss_dict[f"Total_Loss/{k}"] for k in ("G1", "G2", "D1", "D2")])
+    np.savez_compressed(os.path.join(OUT, "split_cycle_step.npz"), losses=np.asarray(losses, dtype=np.float64))
+    return losses
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     R = ref_loader.load()
+    import sys
+    if "--only-split" in sys.argv:          # add the SplitCycleLoss fixture without regenerating the others
+        print(make_split_cycle(R))
+        return
     for name, (kind, kw, shape) in CASES.items():
         nb = make_case(R, name, kind, kw, shape)
         print(f"{name}: {nb / 1e6:.2f} MB raw")
     make_cycle(R)
+    make_split_cycle(R)
     # structural constants the reference's own tests assert (SURVEY 8c)
     d = R.NLayerDiscriminator(3)
     consts = dict(

@@ -334,6 +334,45 @@ class LinkCycleLoss(tnn.Module):
         return total
 
 
+class SplitCycleLoss(LinkCycleLoss):
+    """losses/SplitCycleLoss.py:10-194: the two generators are optimised one after the other with their own optimizers
+    (used with ``CycleModel(split=True)``, whose second traversal sees the detached fake, CycleModel.py:52-57,75-80):
+    G1 loss -> backward -> optimizer_G1.step; G2 loss -> backward -> optimizer_G2.step; then the discriminators as in
+    LinkCycleLoss.  ``grad_sync`` is called with "G1", "G2" and "D"."""
+
+    def __init__(self, netD1, netG1, netD2, netG2, optimizer_G1, optimizer_G2, optimizer_D, dims, l1_loss=None,
+                 g_lambda_dict=None, d_lambda_dict=None, gan_mode="lsgan", grad_sync=None, **kwargs):
+        super().__init__(netD1, netG1, netD2, netG2, None, optimizer_D, dims, l1_loss=l1_loss, g_lambda_dict=g_lambda_dict,
+                         d_lambda_dict=d_lambda_dict, gan_mode=gan_mode, grad_sync=grad_sync, **kwargs)
+        self.optimizer_G1, self.optimizer_G2 = optimizer_G1, optimizer_G2
+
+    def backward_G(self, side, gnet, dnet, data_dict):
+        loss = self._g_loss(side, gnet, dnet, data_dict)
+        loss.backward()                                           # SplitCycleLoss.py:116 (no retain_graph)
+        return loss
+
+    def backward_Gs(self, data_dict):
+        self.set_requires_grad([self.netD1, self.netD2], False)
+        # G1 first (SplitCycleLoss.py:125-137)
+        self.set_requires_grad([self.netG1], True)
+        self.set_requires_grad([self.netG2], False)
+        self.optimizer_G1.zero_grad(set_to_none=True)
+        loss_G1 = self.backward_G("B", self.netG1, self.netD1, data_dict["B"])
+        if self.grad_sync is not None:
+            self.grad_sync("G1")
+        self.optimizer_G1.step()
+        # then G2 (SplitCycleLoss.py:139-151)
+        self.set_requires_grad([self.netG2], True)
+        self.set_requires_grad([self.netG1], False)
+        self.optimizer_G2.zero_grad(set_to_none=True)
+        loss_G2 = self.backward_G("A", self.netG2, self.netD2, data_dict["A"])
+        if self.grad_sync is not None:
+            self.grad_sync("G2")
+        self.optimizer_G2.step()
+        self.set_requires_grad([self.netG1, self.netD1, self.netD2], True)
+        return loss_G1, loss_G2
+
+
 # ---------------------------------------------------------------------------------------------
 # the training step harness (what gp.torch.Train does around model + loss)
 # ---------------------------------------------------------------------------------------------

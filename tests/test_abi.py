@@ -144,3 +144,20 @@ def test_arena_scope_hands_the_callers_grad_mode_down():
         assert not K.arena_enabled()
     with rb.precision("fp32"), torch.no_grad():
         assert not K.arena_enabled()
+
+
+def test_split_cycle_loss_surface_mirrors_the_reference():
+    """SplitCycleLoss.py:13-41: constructor order (netD1, netG1, netD2, netG2, optimizer_G1, optimizer_G2, optimizer_D,
+    dims), class-default lambdas, and the three gradient-sync phases a data-parallel run hooks into."""
+    import inspect
+    from raygun_b200.cyclegan import LinkCycleLoss, SplitCycleLoss
+    names = list(inspect.signature(SplitCycleLoss.__init__).parameters)[1:9]
+    assert names == ["netD1", "netG1", "netD2", "netG2", "optimizer_G1", "optimizer_G2", "optimizer_D", "dims"]
+    assert issubclass(SplitCycleLoss, LinkCycleLoss)
+    import torch
+    lin = lambda: torch.nn.Linear(1, 1)
+    nets = [lin() for _ in range(4)]
+    opt = lambda *ms: torch.optim.SGD([p for m in ms for p in m.parameters()], lr=0.1)
+    loss = SplitCycleLoss(nets[0], nets[1], nets[2], nets[3], opt(nets[1]), opt(nets[3]), opt(nets[0], nets[2]), 3)
+    assert loss.g_lambda_dict["A"]["l1_loss"] == {"cycled": 10, "identity": 0} and loss.d_lambda_dict["B"]["fake"] == 1
+    assert loss.optimizer_G is None and loss.gan_mode == "lsgan"

@@ -196,3 +196,37 @@ def test_blockwise_prediction_is_independent_of_the_block_size_at_large_blocks()
     assert float((diff > 1).float().mean()) <= 1e-4
     assert float(diff.float().mean()) <= 0.25
     assert float(a.float().std()) > 1.0                               # not a constant image
+
+
+def test_split_cyclegan_training_steps_match_reference_losses():
+    """Three SplitCycleLoss steps (CycleModel(split=True), one optimizer per generator, SplitCycleLoss.py:120-157) in the
+    fp32 parity mode vs the losses the REFERENCE produced from the same weights and batches (split_cycle_step.npz,
+    generated by oracle/make_golden.py --only-split)."""
+    import itertools
+    import os
+    import numpy as np
+    import raygun_b200 as rb
+    from raygun_b200 import networks as N
+    from raygun_b200.cyclegan import CycleModel, SplitCycleLoss, make_generator
+    from tests._golden import GOLDEN
+    c = load_cycle()
+    ref = np.load(os.path.join(GOLDEN, "split_cycle_step.npz"))["losses"]
+    IN = functools.partial(torch.nn.InstanceNorm3d, affine=False, track_running_stats=False)
+    g1 = make_generator("resnet", dict(c["spec"]["gkw"]), output_nc=1, final_activation="Tanh").to(DEV)
+    g2 = make_generator("resnet", dict(c["spec"]["gkw"]), output_nc=1, final_activation="Tanh").to(DEV)
+    d1 = N.NLayerDiscriminator(3, norm_layer=IN, **c["spec"]["dkw"]).to(DEV)
+    d2 = N.NLayerDiscriminator(3, norm_layer=IN, **c["spec"]["dkw"]).to(DEV)
+    for net, nm in ((g1, "g1"), (g2, "g2"), (d1, "d1"), (d2, "d2")):
+        net.load_state_dict(c["sds"][nm])
+    lr = c["spec"]["lr"]
+    with rb.precision("fp32"):
+        model = CycleModel(g1, g2, split=True)
+        loss = SplitCycleLoss(d1, g1, d2, g2, torch.optim.Adam(g1.parameters(), lr=lr), torch.optim.Adam(g2.parameters(), lr=lr),
+                              torch.optim.Adam(itertools.chain(d1.parameters(), d2.parameters()), lr=lr), 3)
+        for it, (a, b) in enumerate(c["batches"]):
+            a, b = a.to(DEV), b.to(DEV)
+            fb, cb, fa, ca = model(a, b)
+            loss(a, fa, ca, b, fb, cb)
+            got = [loss.loss_dict[f"Total_Loss/{k}"] for k in ("G1", "G2", "D1", "D2")]
+            for gv, rv in zip(got, ref[it]):
+                assert abs(gv - rv) <= 2e-3 * max(1.0, abs(rv)), (it, got, ref[it].tolist())
