@@ -53,6 +53,51 @@ __global__ void __launch_bounds__(256) vec_maxpool_fwd_kernel(T5 xd, const __nv_
   }
 }
 
+// Row-based NDHWC bf16 backward: one block per dy row (n, d, h), a thread owns (w, 8 channels) windows; two passes
+// over the window (find the first maximal element in ATen order d,h,w -- NaN wins -- then write dy or 0).
+__global__ void __launch_bounds__(256) vec_maxpool_bwd_kernel(T5 xd, const __nv_bfloat16* __restrict__ x, T5 gd,
+                                                              const __nv_bfloat16* __restrict__ dy, T5 dxd,
+                                                              __nv_bfloat16* __restrict__ dx, int fd, int fh, int fw) {
+  const int cg = (int)(gd.c >> 3), W = (int)gd.w, H = (int)gd.h, D = (int)gd.d;
+  const long long rows = gd.n * D * H;
+  for (long long row = blockIdx.x; row < rows; row += gridDim.x) {
+    const int h = (int)(row % H);
+    const long long t = row / H;
+    const int d = (int)(t % D), n = (int)(t / D);
+    const __nv_bfloat16* xrow = x + n * xd.sn + (long long)d * fd * xd.sd + (long long)h * fh * xd.sh;
+    __nv_bfloat16* dxrow = dx + n * dxd.sn + (long long)d * fd * dxd.sd + (long long)h * fh * dxd.sh;
+    const __nv_bfloat16* grow = dy + n * gd.sn + d * gd.sd + h * gd.sh;
+    for (int j = threadIdx.x; j < W * cg; j += blockDim.x) {
+      const int w = j / cg, c = (j - w * cg) << 3;
+      float m[8];
+      int best[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) { m[k] = -INFINITY; best[k] = -1; }
+      int idx = 0;
+      for (int a = 0; a < fd; ++a)
+        for (int b = 0; b < fh; ++b)
+          for (int e = 0; e < fw; ++e, ++idx) {
+            float v[8];
+            ld8(xrow + a * xd.sd + b * xd.sh + (long long)(w * fw + e) * xd.sw + c, v);
+#pragma unroll
+            for (int k = 0; k < 8; ++k)
+              if (best[k] < 0 || v[k] > m[k] || (v[k] != v[k] && m[k] == m[k])) { m[k] = v[k]; best[k] = idx; }
+          }
+      float g[8];
+      ld8(grow + (long long)w * gd.sw + c, g);
+      idx = 0;
+      for (int a = 0; a < fd; ++a)
+        for (int b = 0; b < fh; ++b)
+          for (int e = 0; e < fw; ++e, ++idx) {
+            float o[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) o[k] = best[k] == idx ? g[k] : 0.f;
+            st8(dxrow + a * dxd.sd + b * dxd.sh + (long long)(w * fw + e) * dxd.sw + c, o);
+          }
+    }
+  }
+}
+
 // backward: one thread per OUTPUT window; the first maximal element (ATen order d,h,w) gets dy.
 // Windows are disjoint (stride == kernel) so plain stores are race-free.
 template <typename TS, typename TD>
@@ -242,6 +287,12 @@ int rg_maxpool3d_bwd(const rg_tensor5* xd, const void* x, const rg_tensor5* yd, 
   long long total = view(dyd).numel();
   if (total == 0) return RG_OK;
   cudaStream_t st = (cudaStream_t)stream;
+  if (vec_ok(xd, x) && vec_ok(dyd, dy) && vec_ok(dxd, dx)) {
+    vec_maxpool_bwd_kernel<<<grid_for(dyd->n * dyd->d * dyd->h, 1, 148 * 32), 256, 0, st>>>(
+        view(xd), (const __nv_bfloat16*)x, view(dyd), (const __nv_bfloat16*)dy, view(dxd), (__nv_bfloat16*)dx, f[0], f[1], f[2]);
+    RG_LAUNCH_CHECK("rg_maxpool3d_bwd(vec)");
+    return RG_OK;
+  }
   int grid = grid_for(total, 256);
   bool ci = channels_inner(dyd);
   RG_DISPATCH_FLOAT(xd->dtype, TS, RG_DISPATCH_FLOAT(dxd->dtype, TD, {

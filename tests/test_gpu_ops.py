@@ -344,6 +344,23 @@ def test_vectorised_maxpool_matches_torch_on_strided_ndhwc_views():
         assert torch.equal(K.maxpool_fwd(sl, f).float().cpu(), ref[:, 8:24])
 
 
+def test_vectorised_maxpool_backward_matches_autograd_including_ties():
+    """Row-based NDHWC bf16 backward: the first maximal element in (d, h, w) order gets the gradient (ties are common
+    after ReLU), remainder voxels outside any window get zero."""
+    from raygun_b200 import kernels as K
+    torch.manual_seed(7)
+    x = torch.relu(torch.randn(2, 24, 9, 10, 12)).bfloat16()             # many exact zeros -> ties
+    xg = x.to(DEV).contiguous(memory_format=torch.channels_last_3d)
+    for f in ((2, 2, 2), (1, 2, 3), (3, 2, 1)):
+        xr = x.float().requires_grad_(True)
+        y = torch.nn.functional.max_pool3d(xr, f, f)
+        g = torch.randn_like(y).bfloat16().float()
+        (ref,) = torch.autograd.grad(y, xr, g)
+        gg = g.bfloat16().to(DEV).contiguous(memory_format=torch.channels_last_3d)
+        dx = K.maxpool_bwd(xg, gg, f)
+        assert torch.equal(dx.float().cpu(), ref), f
+
+
 def test_training_conv_outputs_stay_dense_and_inference_uses_arenas():
     """autograd.Function.forward always runs with grad mode off: the caller's grad mode has to be handed down, or
     training silently gets the margin-allocated inference layout (strided outputs -> slow norm kernels)."""
