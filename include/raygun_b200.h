@@ -226,6 +226,12 @@ int rg_act_fwd(const rg_tensor5* xd, const void* x, int act, float slope, const 
 int rg_act_bwd(const rg_tensor5* yd, const void* y, const rg_tensor5* dyd, const void* dy, int act,
                float slope, const rg_tensor5* dxd, void* dx, void* stream);
 
+/* dx = dy * act'(y) and bias_sum[c] += sum_{n,voxels} dx in one pass (the activation derivative and the bias gradient of
+ * a Conv3d + activation layer read the same dy): dense NDHWC bf16 only (RG_E_UNSUPPORTED otherwise); bias_sum fp32 [C],
+ * zeroed by the caller.                                                                                            */
+int rg_act_bwd_bias(const rg_tensor5* yd, const void* y, const rg_tensor5* dyd, const void* dy, int act, float slope,
+                    const rg_tensor5* dxd, void* dx, float* bias_sum, void* stream);
+
 /* ---- pooling / nearest up-sampling (UNet.py:209-218 MaxPool3d; UNet.py:273 nn.Upsample) --*/
 int rg_maxpool3d_fwd(const rg_tensor5* xd, const void* x, const int32_t f[3], const rg_tensor5* yd, void* y,
                      void* stream);

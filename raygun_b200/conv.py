@@ -480,8 +480,8 @@ def conv_dgrad(dy, w, x_shape, stride, pad, groups=1, bias=None, act=ACT_NONE, s
     return dx, None, None
 
 
-def conv_wgrad(x, dy, w_shape, stride, pad, groups=1, want_bias=False):
-    """dw (fp32, conv layout) and optionally dbias = sum(dy)."""
+def conv_wgrad(x, dy, w_shape, stride, pad, groups=1, want_bias=False, db=None):
+    """dw (fp32, conv layout) and optionally dbias = sum(dy) (`db`: already computed by the caller's activation pass)."""
     require_device(x)
     cout, cin_g = w_shape[0], w_shape[1]
     kernel = tuple(w_shape[2:])
@@ -499,7 +499,7 @@ def conv_wgrad(x, dy, w_shape, stride, pad, groups=1, want_bias=False):
             count_launch(2)
             stats["igemm"] += 1
             stats["halo_wgrad"] = stats.get("halo_wgrad", 0) + 1
-            db = K.norm_stats(dyb, _C.NORM_BATCH)[0] if want_bias else None
+            db = (db if db is not None else K.norm_stats(dyb, _C.NORM_BATCH)[0]) if want_bias else None
             return dw, db
         plan = _get_plan(2, n, cin_g, cout, tuple(x.shape[2:]), tuple(dy.shape[2:]), kernel, stride, pad,
                          _sp_strides(xb), _sp_strides(dyb), ACT_NONE, 0.0)
@@ -510,7 +510,7 @@ def conv_wgrad(x, dy, w_shape, stride, pad, groups=1, want_bias=False):
                                            stream_ptr(x.device)), "rg_igemm_wgrad")
             count_launch()
             stats["igemm"] += 1
-            db = K.norm_stats(dyb, _C.NORM_BATCH)[0] if want_bias else None
+            db = (db if db is not None else K.norm_stats(dyb, _C.NORM_BATCH)[0]) if want_bias else None
             return dw, db
     if _pw_ok(cin_g, cout, kernel, stride, pad, groups):
         xb = K.convert(x, torch.bfloat16)

@@ -354,6 +354,43 @@ static int launch_reduce2(const NormCtx& cx, const rg_tensor5* xd, const TX* x, 
   return RG_OK;
 }
 
+// dx = dy * act'(y) AND sum over (n, voxels) of dx per channel in the same pass: the activation derivative and the
+// bias gradient of a Conv3d + activation layer (ConvPass, UNet.py:61-69) need the same read of dy.  Dense NDHWC bf16.
+__global__ void __launch_bounds__(256) dense_act_bwd_sum_kernel(int act, float slope, int C, int cg, int lanes_v, long long vox,
+                                                                long long vox_per_block, const __nv_bfloat16* __restrict__ y,
+                                                                const __nv_bfloat16* __restrict__ dy, __nv_bfloat16* __restrict__ dx,
+                                                                float* __restrict__ sums) {
+  const int cgi = threadIdx.x % cg, lv = threadIdx.x / cg;
+  const int c = cgi << 3;
+  float s[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) s[k] = 0.f;
+  const long long v0 = blockIdx.x * vox_per_block, v1 = min(v0 + vox_per_block, vox);
+#pragma unroll 2
+  for (long long v = v0 + lv; v < v1; v += lanes_v) {
+    const size_t o = (size_t)v * C + c;
+    float g[8], yy[8];
+    ld8(dy + o, g);
+    ld8(y + o, yy);
+    act_grad8(g, yy, act, slope);
+    st8(dx + o, g);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) s[k] += g[k];
+  }
+  __shared__ float red[256];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    red[threadIdx.x] = s[k];
+    __syncthreads();
+    if (threadIdx.x < cg) {
+      float a = 0.f;
+      for (int l = 0; l < lanes_v; ++l) a += red[threadIdx.x + cg * l];
+      atomicAdd(sums + (threadIdx.x << 3) + k, a);
+    }
+    __syncthreads();
+  }
+}
+
 }  // namespace rg
 
 using namespace rg;
@@ -477,6 +514,30 @@ int rg_norm_bwd(const rg_tensor5* xd, const void* x, const rg_tensor5* dyd, cons
     })))
     RG_LAUNCH_CHECK("rg_norm_bwd dx");
   }
+  return RG_OK;
+}
+
+int rg_act_bwd_bias(const rg_tensor5* yd, const void* y, const rg_tensor5* dyd, const void* dy, int act, float slope,
+                    const rg_tensor5* dxd, void* dx, float* bias_sum, void* stream) {
+  RG_CHECK_ARG(yd && dyd && dxd && y && dy && dx && bias_sum, "rg_act_bwd_bias: null argument");
+  RG_CHECK_ARG(same_shape(yd, dyd) && same_shape(yd, dxd), "rg_act_bwd_bias: shape mismatch");
+  const long long per = yd->d * yd->h * yd->w * yd->c;
+  RG_UNSUPPORTED(!dense_ok(yd, y) || !dense_ok(dyd, dy) || !dense_ok(dxd, dx) || !dense_cg_ok(yd) || yd->sn != per ||
+                     dyd->sn != per || dxd->sn != per,
+                 "rg_act_bwd_bias: needs dense NDHWC bf16 tensors");
+  const long long vox = yd->n * yd->d * yd->h * yd->w;
+  if (vox == 0) return RG_OK;
+  const int cg = (int)(yd->c >> 3), lanes_v = 256 / cg;
+  long long blocks = 148LL * 8;
+  long long vpb = (vox + blocks - 1) / blocks;
+  const long long min_vpb = 48LL * lanes_v;                 // fat blocks: a fixed smem + atomics tail per block
+  if (vpb < min_vpb) vpb = min_vpb;
+  vpb = (vpb + lanes_v - 1) / lanes_v * lanes_v;
+  blocks = (vox + vpb - 1) / vpb;
+  dense_act_bwd_sum_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(act, slope, (int)yd->c, cg, lanes_v, vox, vpb,
+                                                                              (const __nv_bfloat16*)y, (const __nv_bfloat16*)dy,
+                                                                              (__nv_bfloat16*)dx, bias_sum);
+  RG_LAUNCH_CHECK("rg_act_bwd_bias");
   return RG_OK;
 }
 

@@ -92,8 +92,12 @@ class _Conv3d(torch.autograd.Function):
     def backward(ctx, dy, _ds, _dq):
         x, w, y = ctx.saved_tensors
         stride, pad, groups, act, slope = ctx.geom
+        db_pre = None
         if act != ACT_NONE:
-            dy = K.act_bwd(y, dy, act, slope)
+            if ctx.has_bias and ctx.needs_input_grad[2] and not ctx.narrow:
+                dy, db_pre = K.act_bwd_bias(y, dy, act, slope)          # activation derivative + bias gradient, one pass
+            else:
+                dy = K.act_bwd(y, dy, act, slope)
         dx = dw = db = None
         if ctx.narrow:
             cout = w.shape[0]
@@ -112,7 +116,7 @@ class _Conv3d(torch.autograd.Function):
         if ctx.needs_input_grad[0]:
             dx, _, _ = CV.conv_dgrad(dy, w, x.shape, stride, pad, groups, out_dtype=x.dtype)
         if ctx.needs_input_grad[1] or (ctx.has_bias and ctx.needs_input_grad[2]):
-            dw, db = CV.conv_wgrad(x, dy, w.shape, stride, pad, groups, want_bias=ctx.has_bias)
+            dw, db = CV.conv_wgrad(x, dy, w.shape, stride, pad, groups, want_bias=ctx.has_bias, db=db_pre)
             if not ctx.needs_input_grad[1]:
                 dw = None
         return dx, dw, db, None, None, None, None, None, None, None
@@ -150,14 +154,18 @@ class _StemConv3d(torch.autograd.Function):
         x, w, y = ctx.saved_tensors
         pad, act, slope, wshape, w2shape = ctx.cfg
         cout, cin, kd, kh, kw = wshape
+        db_pre = None
         if act != ACT_NONE:
-            dy = K.act_bwd(y, dy, act, slope)
+            if ctx.has_bias and ctx.needs_input_grad[2]:
+                dy, db_pre = K.act_bwd_bias(y, dy, act, slope)
+            else:
+                dy = K.act_bwd(y, dy, act, slope)
         dx = dw = db = None
         if ctx.needs_input_grad[0]:
             dx, _, _ = CV.conv_dgrad(dy, w, x.shape, (1, 1, 1), pad, 1, out_dtype=x.dtype)
         if ctx.needs_input_grad[1] or (ctx.has_bias and ctx.needs_input_grad[2]):
             xc = K.im2col_hw(x, kh, kw, pad[1], pad[2], 64)
-            dw2, db = CV.conv_wgrad(xc, dy, w2shape, (1, 1, 1), (pad[0], 0, 0), 1, want_bias=ctx.has_bias)
+            dw2, db = CV.conv_wgrad(xc, dy, w2shape, (1, 1, 1), (pad[0], 0, 0), 1, want_bias=ctx.has_bias, db=db_pre)
             dw = dw2.reshape(cout, 64, kd)[:, : cin * kh * kw].reshape(cout, cin, kh, kw, kd).permute(0, 1, 4, 2, 3)
             dw = dw.contiguous() if ctx.needs_input_grad[1] else None
         return dx, dw, db, None, None, None, None, None

@@ -211,6 +211,19 @@ def act_bwd(y, dy, act, slope=0.0):
     return dx
 
 
+def act_bwd_bias(y, dy, act, slope=0.0):
+    """(dy * act'(y), per-channel sum of it) in one pass when everything is dense NDHWC bf16, else (act_bwd, None)."""
+    if (y.dtype == torch.bfloat16 and dy.dtype == torch.bfloat16 and is_ndhwc(y) and is_ndhwc(dy) and y.shape[1] % 8 == 0
+            and y.shape[1] <= 2048 and 256 % (y.shape[1] // 8) == 0):
+        dx = empty5(y.shape, y.dtype, y.device)
+        db = torch.zeros(y.shape[1], dtype=torch.float32, device=y.device)
+        check(lib().rg_act_bwd_bias(C.byref(t5(y)), ptr(y), C.byref(t5(dy)), ptr(dy), C.c_int(act), C.c_float(slope),
+                                    C.byref(t5(dx)), ptr(dx), ptr(db), stream_ptr(y.device)), "rg_act_bwd_bias")
+        count_launch()
+        return dx, db
+    return act_bwd(y, dy, act, slope), None
+
+
 def maxpool_fwd(x, f):
     require_device(x)
     n, c, d, h, w = x.shape

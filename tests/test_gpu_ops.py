@@ -440,3 +440,45 @@ def test_discriminator_edge_layers_leave_the_cuda_core_gemm():
     rel = lambda a, b: float((a.float().cpu() - b).abs().max()) / max(1e-6, float(b.abs().max()))
     assert tuple(yg.shape) == tuple(yh.shape) and rel(yg, yh) <= 1e-2
     assert rel(xg.grad, rx) <= 1e-2 and rel(wg.grad, rw) <= 1e-2 and rel(bg.grad, rb_) <= 1e-2
+
+
+@pytest.mark.parametrize("act", [1, 2, 3])
+def test_fused_activation_backward_and_bias_gradient(act):
+    """rg_act_bwd_bias: dx identical to rg_act_bwd, bias sum equal to the fp32 sum of the bf16 dx; and a
+    Conv3d + ReLU layer's bias gradient through the functional API matches autograd."""
+    from raygun_b200 import kernels as K
+    torch.manual_seed(9)
+    y = torch.randn(2, 64, 9, 10, 11, device=DEV).bfloat16().contiguous(memory_format=torch.channels_last_3d)
+    if act == 3:
+        y = torch.tanh(y.float()).bfloat16().contiguous(memory_format=torch.channels_last_3d)
+    dy = torch.randn(2, 64, 9, 10, 11, device=DEV).bfloat16().contiguous(memory_format=torch.channels_last_3d)
+    ref = K.act_bwd(y, dy, act, 0.2)
+    dx, db = K.act_bwd_bias(y, dy, act, 0.2)
+    assert db is not None and torch.equal(dx, ref)
+    want = ref.float().sum(dim=(0, 2, 3, 4))
+    assert float((db - want).abs().max()) <= 2e-3 * float(want.abs().max())
+    # a strided (non-dense) operand falls back to the two-kernel path
+    dx2, db2 = K.act_bwd_bias(y[:, :32], dy[:, :32], act, 0.2)
+    assert db2 is None and torch.equal(dx2, ref[:, :32])
+
+
+def test_conv_relu_bias_gradient_through_the_fused_pass():
+    import raygun_b200 as rb
+    from raygun_b200 import functional as F
+    torch.manual_seed(10)
+    q = lambda t: t.bfloat16().float()
+    conv = torch.nn.Conv3d(64, 64, 3, padding=1)
+    with torch.no_grad():
+        conv.weight.copy_(q(conv.weight))
+    x = q(torch.randn(2, 64, 8, 8, 8))
+    yr = TF.relu(conv(x))
+    g = q(torch.randn_like(yr))
+    rw, rb_ = torch.autograd.grad(yr, [conv.weight, conv.bias], g)
+    with rb.precision("bf16"):
+        xg = x.to(DEV).bfloat16().contiguous(memory_format=torch.channels_last_3d)
+        wg = conv.weight.detach().to(DEV).requires_grad_(True)
+        bg = conv.bias.detach().to(DEV).requires_grad_(True)
+        yg = F.conv3d(xg, wg, bg, 1, 1, act=1)
+        yg.backward(g.to(DEV).to(yg.dtype))
+    rel = lambda a, b: float((a.float().cpu() - b).abs().max()) / max(1e-6, float(b.abs().max()))
+    assert rel(bg.grad, rb_) <= 1e-2 and rel(wg.grad, rw) <= 1e-2
