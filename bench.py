@@ -34,7 +34,12 @@ WORKLOADS = {
     # name: (batch, side, n_blocks, ngf)
     "cfg2": (2, 128, 9, 64),
     "cfg2-small": (1, 64, 9, 64),
+    # cfg5 (BASELINE configs[4]): deep G-UNet, 4 down-sampling levels, fmap_inc_factor 3, ngf 64 (1.78 B parameters),
+    # forward + backward on one 1x1x256^3 patch; n_blocks = 0 selects the U-Net branch of run_ours
+    "cfg5": (1, 256, 0, 64),
 }
+DEEP_KW = dict(input_nc=1, output_nc=1, ngf=64, fmap_inc_factor=3, num_downs=5, padding_type="same",
+               final_activation="Tanh")
 
 
 def conv_flops_resnet(batch, side, n_blocks, ngf, n_down=2):
@@ -124,7 +129,31 @@ def synth_batch(batch, side, seed):
 # reference arm / CPU baseline: the oracle port (the reference's algorithm restated over plain
 # torch.nn.functional, oracle/restate.py) on the host cores
 # ---------------------------------------------------------------------------------------------
+def deep_unet_cpu_fn(side=32):
+    """cfg5 on the host cores: the oracle's G-UNet forward + SmoothL1 + all gradients on one 1x1x32^3 patch."""
+    from oracle import restate as O
+    from raygun_b200.cyclegan import make_generator
+    torch.manual_seed(42)
+    with contextlib.redirect_stdout(sys.stderr):
+        g = make_generator("unet", dict(DEEP_KW))
+    sd = {k: v.detach().requires_grad_(v.is_floating_point()) for k, v in g.state_dict().items()}
+    spec = O.unet_spec(input_nc=1, ngf=64, fmap_inc_factor=3, downsample_factors=[(2, 2, 2)] * 4, padding_type="same")
+    x = O.u8_normalise(synth_batch(1, side, 42))
+    tgt = O.u8_normalise(synth_batch(1, side, 43))
+    leaves = [v for v in sd.values() if v.requires_grad]
+
+    def step():
+        y = O.generator_forward(sd, "unet", spec, x, final_activation="Tanh")
+        loss = O.smooth_l1(tgt, y)
+        torch.autograd.grad(loss, leaves, allow_unused=True)
+        return float(loss.detach())
+
+    return step, side ** 3
+
+
 def cpu_step_fn(n_blocks, ngf, side, batch=1):
+    if n_blocks == 0:
+        return deep_unet_cpu_fn(32)
     from oracle import restate as O
     import raygun_b200.networks as N  # constructors only (parameter shapes / init); arithmetic is the oracle's
     torch.manual_seed(42)
@@ -186,7 +215,7 @@ def run_reference(args):
                               e2e=dict(value=vox / dt, unit="voxels/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0))))
         return
     batch, side, n_blocks, ngf = WORKLOADS[args.workload]
-    sample_side = 48 if side >= 128 else 32
+    sample_side = 32 if n_blocks == 0 else (48 if side >= 128 else 32)
     step, vox = cpu_step_fn(n_blocks, ngf, sample_side)
     for _ in range(max(1, min(args.warmup, 1))):
         step()
@@ -199,7 +228,8 @@ def run_reference(args):
     out = dict(metric="generator_train_voxels_per_sec", value=val, unit="voxels/s", impl="reference", n_gpus=args.gpus,
                steps=args.steps, warmup=args.warmup, ms_per_step=dt * 1e3, higher_is_better=True, scaling="weak",
                vs_baseline=None, dtype="f32", data="synthetic",
-               config=dict(workload=f"{args.workload}: G-ResNet{n_blocks} fwd+bwd+SmoothL1, CPU oracle port", sample=sample),
+               config=dict(workload=f"{args.workload}: {'deep G-UNet' if n_blocks == 0 else f'G-ResNet{n_blocks}'} "
+                                    "fwd+bwd+SmoothL1, CPU oracle port", sample=sample),
                cpu_baseline=dict(value=val, unit="voxels/s", cores=cores, kind="port", sample=sample),
                e2e=dict(value=val, unit="voxels/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0))
     print(json.dumps(out))
@@ -232,8 +262,13 @@ def run_ours(args):
 
     torch.manual_seed(42)
     with contextlib.redirect_stdout(sys.stderr):
-        g = make_generator("resnet", dict(input_nc=1, output_nc=1, ngf=ngf, n_blocks=n_blocks, padding_type="same",
-                                          final_activation="Tanh")).to(dev)
+        if n_blocks == 0:
+            g = make_generator("unet", dict(DEEP_KW)).to(dev)
+            args.no_graph = True        # one 450 ms step of ~280 launches: launch gaps are noise, and the graph's
+                                        # private pool would double the 58 GB activation footprint
+        else:
+            g = make_generator("resnet", dict(input_nc=1, output_nc=1, ngf=ngf, n_blocks=n_blocks, padding_type="same",
+                                              final_activation="Tanh")).to(dev)
     params = [p for p in g.parameters()]
     host_x = synth_batch(batch, side, 42 + 10 * rank).pin_memory()
     host_t = synth_batch(batch, side, 43 + 10 * rank).pin_memory()
@@ -367,10 +402,14 @@ def run_ours(args):
 
     if rank == 0:
         vox = batch * side ** 3 * world
-        fwd = conv_flops_resnet(batch, side, n_blocks, ngf)
+        # cfg5: the algorithmic FLOPs of the step = sum over the conv launches (each counts 2 x MACs of its layer)
+        fwd = conv_flops_resnet(batch, side, n_blocks, ngf) if n_blocks else tot_fl / 3
+        net_name = f"G-ResNet{n_blocks} (ngf {ngf}, InstanceNorm, reflect 'same')" if n_blocks else \
+            "deep G-UNet (4 down-sampling levels, fmap_inc_factor 3, ngf 64, 1.78 B parameters, reflect 'same')"
+        csample = 32 if n_blocks == 0 else (48 if side >= 128 else 32)
         cores = os.cpu_count() or 1
         torch.set_num_threads(cores)
-        cstep, cvox = cpu_step_fn(n_blocks, ngf, 48 if side >= 128 else 32)
+        cstep, cvox = cpu_step_fn(n_blocks, ngf, csample)
         cstep()
         t0 = time.perf_counter()
         cstep()
@@ -378,8 +417,8 @@ def run_ours(args):
         out = dict(metric="generator_train_voxels_per_sec", value=vox / (ms * 1e-3), unit="voxels/s", n_gpus=world,
                    steps=args.steps, warmup=max(args.warmup, 3), ms_per_step=ms, higher_is_better=True, scaling="weak",
                    vs_baseline=None, dtype="bf16", data="synthetic",
-                   config=dict(workload=f"{args.workload}: G-ResNet{n_blocks} (ngf {ngf}, InstanceNorm, reflect 'same') "
-                                        f"fwd+bwd+SmoothL1 on {batch}x1x{side}^3 per GPU",
+                   config=dict(workload=f"{args.workload}: {net_name} fwd+bwd+SmoothL1 on {batch}x1x{side}^3 per GPU",
+                               peak_hbm_gb=torch.cuda.max_memory_allocated() / 1e9,
                                l2="activation working set (GBs) >> 126 MB L2; no explicit flush",
                                parallelism=f"dp{world}" if world > 1 else "single", algorithmic_tflop_per_step=3 * fwd / 1e12,
                                cuda_graph=graph is not None),
@@ -388,7 +427,7 @@ def run_ours(args):
                             h2d_bytes_per_step=int(host_x.numel() + host_t.numel()), d2h_bytes_per_step=4),
                    gpu_launches=int(launches), roofline=roofline,
                    cpu_baseline=dict(value=cvox / cdt, unit="voxels/s", cores=cores, kind="port",
-                                     sample=f"1x1x{48 if side >= 128 else 32}^3 fwd+bwd, oracle/restate.py, 1 warm-up + 1 timed"),
+                                     sample=f"1x1x{csample}^3 fwd+bwd, oracle/restate.py, 1 warm-up + 1 timed"),
                    clocks=clocks, conv_paths=dict(CV.stats))
         print(json.dumps(out))
     if world > 1:

@@ -281,7 +281,7 @@ static int hw_geometry(const rg_igemm_desc* d, HwGeom* g, int variant = 0) {
   p.kd = d->kernel[0]; p.kh = d->kernel[1]; p.kw = d->kernel[2];
   p.pd = d->pad[0]; p.ph = d->pad[1]; p.pw = d->pad[2];
   p.cin = d->cin; p.cout = d->cout;
-  g->bn = d->cout % 256 == 0 ? 256 : (d->cout % 128 == 0 ? 128 : 64);
+  g->bn = d->cout % 256 == 0 ? 256 : (d->cout % 192 == 0 ? 192 : (d->cout % 128 == 0 ? 128 : 64));
   p.kd_first = 0; p.kd_step = 1; p.n_kd = p.kd; p.dpair = 0;
   if (variant == 1) { g->bn = 128; p.dpair = 1; p.kd_first = 1; p.kd_step = 2; p.n_kd = p.kd / 2; }
   if (variant == 2) { g->bn = 64; p.kd_first = p.kd - 1; p.n_kd = 1; }
@@ -385,6 +385,7 @@ int rg_halo_wgrad(const rg_igemm_desc* d, const void* x, const void* dy, float* 
     gv.p.x_map = p.x_map; gv.p.dy_map = p.dy_map;
     gv.p.ws = (float*)workspace;
     if (gv.bn == 256) rc = hw_launch<256>(gv, st);
+    else if (gv.bn == 192) rc = hw_launch<192>(gv, st);
     else if (gv.bn == 128) rc = hw_launch<128>(gv, st);
     else rc = hw_launch<64>(gv, st);
     if (rc) return rc;

@@ -51,7 +51,7 @@ struct alignas(64) IgemmParams {
 template <int BN> struct IgemmCfg {
   static constexpr int B_BYTES = BN * BLOCK_K * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int STAGES = (BN >= 256) ? 4 : (BN >= 128 ? 6 : 8);
+  static constexpr int STAGES = (BN >= 192) ? 4 : (BN >= 128 ? 6 : 8);
   static constexpr int TMEM_COLS = (2 * BN <= 32) ? 32 : (2 * BN <= 64 ? 64 : (2 * BN <= 128 ? 128 : (2 * BN <= 256 ? 256 : 512)));
   static constexpr int SMEM_BYTES = 1024 /*align slack*/ + STAGES * STAGE_BYTES + 2 * STAGE_OUT_BYTES + 1024 /*bars+bias*/;
 };
@@ -293,7 +293,7 @@ template <int BN> struct WgradCfg {
   static constexpr int NACC = 512 / BN;                 // accumulators (slab pairs) per CTA
   static constexpr int B_BYTES = (BN / 64) * A_BYTES;   // dY slabs of one voxel chunk
   static constexpr int A_STAGE = 2 * A_BYTES;           // one slab pair
-  static constexpr int A_STAGES = (BN >= 256) ? 3 : (BN >= 128 ? 4 : 5);
+  static constexpr int A_STAGES = (BN >= 256) ? 3 : (BN >= 128 ? 4 : 5);     // BN 192: 96 + 128 KB
   static constexpr int SMEM_BYTES = 1024 + 2 * B_BYTES + A_STAGES * A_STAGE + 256;
 };
 
@@ -600,7 +600,7 @@ int rg_plan_create(const rg_igemm_desc* d, rg_plan** out) {
   rg_plan* pl = new rg_plan();
   pl->d = *d; pl->kc = kc; pl->rows = rows;
   pl->taps = d->kernel[0] * d->kernel[1] * d->kernel[2];
-  pl->bn = rows % 256 == 0 ? 256 : (rows % 128 == 0 ? 128 : 64);
+  pl->bn = rows % 256 == 0 ? 256 : (rows % 192 == 0 ? 192 : (rows % 128 == 0 ? 128 : 64));   // 192: fmap_inc_factor 3 widths
 
   const int nclass = d->mode != 1 ? 1 : d->stride[0] * d->stride[1] * d->stride[2];
   for (int cls = 0; cls < nclass; ++cls) {
@@ -699,6 +699,7 @@ int rg_igemm_run(const rg_plan* pl, const void* in, const void* w_packed, const 
     const long long total = (long long)p.tiles_w * p.tiles_h * p.tiles_d * p.batch * p.n_tiles_n;
     const int grid = (int)(total < num_sms() ? total : num_sms());
     if (pl->bn == 256) rc = launch_bn<256>(p, grid, st);
+    else if (pl->bn == 192) rc = launch_bn<192>(p, grid, st);
     else if (pl->bn == 128) rc = launch_bn<128>(p, grid, st);
     else rc = launch_bn<64>(p, grid, st);
     if (rc) return rc;
@@ -752,6 +753,7 @@ int rg_igemm_wgrad(const rg_plan* pl, const void* x, const void* dy, float* dw, 
   p.dw = dw;
   const int grid = (int)(base_units * p.n_splits);
   if (bn == 256) rc = launch_wgrad<256>(p, grid, st);
+  else if (bn == 192) rc = launch_wgrad<192>(p, grid, st);
   else if (bn == 128) rc = launch_wgrad<128>(p, grid, st);
   else rc = launch_wgrad<64>(p, grid, st);
   if (rc) return rc;

@@ -29,6 +29,10 @@ FPROP = [
     (64, 512, 3, 1, 1, (9, 9, 9), 1),
     (256, 256, 2, 2, 1, (17, 17, 17), 1),
     (64, 192, (1, 3, 3), (1, 2, 1), (0, 1, 1), (4, 9, 8), 1),
+    # fmap_inc_factor 3 widths (Deep-UNet, cfg5): 192-column tiles, 1 / 3 / 9 of them per voxel tile
+    (192, 576, 3, 1, 1, (8, 8, 8), 1),
+    (576, 1728, 3, 1, 1, (5, 6, 4), 1),
+    (64, 384, 3, 2, 1, (9, 9, 9), 2),
 ]
 
 
@@ -63,6 +67,9 @@ DGRAD = [
     (256, 128, 3, 2, 1, (16, 16, 16), 1),
     (128, 64, 2, 2, 1, (9, 9, 9), 0),
     (64, 64, 4, 2, 1, (8, 8, 8), 0),
+    (192, 192, 3, 2, 1, (6, 7, 8), 1),
+    (64, 576, 2, 2, 0, (5, 5, 5), 0),
+    (576, 192, 3, 1, 1, (6, 6, 6), 0),
 ]
 
 
@@ -97,6 +104,10 @@ WGRAD = [
     (192, 64, 1, 1, 0, (5, 6, 7), 2),
     (128, 512, 2, 2, 1, (9, 9, 9), 1),
     (64, 192, 4, 1, 1, (6, 6, 6), 1),
+    (192, 576, 3, 1, 1, (8, 8, 8), 1),
+    (576, 192, 3, 1, 1, (6, 7, 8), 2),
+    (64, 192, 3, 2, 1, (9, 10, 11), 2),
+    (192, 576, 2, 2, 0, (8, 8, 8), 1),
 ]
 
 

@@ -262,3 +262,24 @@ def test_bf16_loss_curves_follow_fp32_over_200_steps():
         assert LC.deviation(a[:10], b[:10], window=1)["per_step_max_rel"] <= 1e-2, k
         d = LC.deviation(a, b)
         assert d["mean_rel"] <= 2e-2 and d["smoothed_max_rel"] <= envelope, (k, d)
+
+
+def test_deep_unet_cfg5_bf16_path_follows_the_fp32_path():
+    """cfg5 architecture (4 down-sampling levels, fmap_inc_factor 3, ngf 64: 64..5184 channels, 1.78 B parameters) on
+    one 32^3 patch: bf16 tensor-core forward within 2e-2 of the fp32 path (north_star), every parameter gradient
+    aligned with its fp32 counterpart, and every conv on a tensor-core kernel (192-column tiles for the x3 widths)."""
+    import importlib.util
+    import os
+    from raygun_b200 import conv as CV
+    from raygun_b200.cyclegan import make_generator
+    spec = importlib.util.spec_from_file_location(
+        "cfg5_deep_unet", os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "scripts", "cfg5_deep_unet.py"))
+    M = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(M)
+    torch.manual_seed(5)
+    g = make_generator("unet", dict(M.DEEP_KW)).to(DEV)
+    assert sum(p.numel() for p in g.parameters()) == 1783620993
+    r = M.deep_unet_check(g, torch.device(DEV))
+    assert r["rel_rms"] <= 2e-2 and r["min_grad_cosine"] >= 0.98 and abs(r["grad_norm_ratio"] - 1) <= 2e-2, r
+    del g
+    torch.cuda.empty_cache()
