@@ -481,7 +481,7 @@ def run_predict(args):
         dist.init_process_group("nccl", device_id=dev)
     rb.set_precision("bf16")
     R = int(args.read)                                 # read block; write block W = R - 48 (halo 24 >= 22, origins = 0 mod 4:
-    W = R - 48                                         # SURVEY 8c); recompute overhead (R/W)^3 = 1.41 at R = 448
+    W = R - 48                                         # SURVEY 8c); recompute overhead (R/W)^3 = 1.34 at R = 512 (88 GiB), 1.30 at R = 576 (125 GiB)
     nb = (4, 4, 2)                                     # write blocks per axis: 32 blocks, a 880 x 880 x 464 volume
     shape = tuple(n * W + (R - W) for n in nb)
     torch.manual_seed(42)
@@ -721,7 +721,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS) + ["cfg3", "cfg4"])
-    ap.add_argument("--read", type=int, default=448, help="cfg4: read block size (multiple of 16; write block = read - 48)")
+    ap.add_argument("--read", type=int, default=512, help="cfg4: read block size (multiple of 16; write block = read - 48)")
     ap.add_argument("--no-graph", action="store_true", help="launch every kernel eagerly instead of replaying one CUDA graph")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -5,10 +5,11 @@
 // input taps) is gathered straight into the 128B-swizzled K-major A tile in shared memory, so HBM sees the
 // 1-channel input once and the output once: the kernel is HBM-write bound (128 B per voxel for 64 channels).
 //
-// Warp roles (544 threads): warp 0 = MMA issuer (one elected thread), warps 1-8 = A-tile builders (two groups of
-// 128 threads that alternate tiles, thread = output voxel), warps 9-16 = epilogue (thread = TMEM lane = voxel, two
+// Warp roles (544 threads): warp 0 = MMA issuer (one elected thread), warps 1-8 = A-tile builders (3^3 single-channel
+// stems: one warp per 4 x 32 tile through a shared-memory input patch; other shapes: two groups of 128 threads that
+// alternate 16 x 8 tiles, thread = output voxel), warps 9-16 = epilogue (thread = TMEM lane = voxel, two
 // warps per lane quadrant that split the produced channels in groups of 32).
-// Tile = 16 (h) x 8 (w) output voxels of one depth plane; persistent CTAs walk the tiles round-robin.
+// Tile = 4 x 32 or 16 (h) x 8 (w) output voxels of one depth plane; persistent CTAs walk the tiles round-robin.
 #include <cuda.h>
 #include <cuda_bf16.h>
 
@@ -19,11 +20,14 @@ namespace rg {
 
 constexpr int ST_THREADS = 544;
 constexpr int ST_TH = 16, ST_TW = 8;
-constexpr int ST_STAGES = 6;                 // A tiles in flight (16 KB each)
+constexpr int ST_STAGES = 8;                 // A tiles in flight (16 KB each); >= the 8 builder warps, so a warp can never
+                                             // run two uses ahead of the issuer on one stage (parity waits would alias)
 constexpr int ST_A_BYTES = 128 * 128;
 constexpr int ST_MAX_COUT = 256;
 constexpr int ST_STAGE_OUT = 32 * 64;          // epilogue staging: 32 voxels x 32 channels bf16, two buffers per warp
 constexpr int ST_OUT_BYTES = 8 * 2 * ST_STAGE_OUT;
+constexpr int ST_PATCH_PITCH = 50;             // elements per patch row (34 used); 25 words: 4 consecutive rows -> disjoint banks
+constexpr int ST_PATCH_BYTES = 2048;           // 18 rows x 50 x 2 B = 1800, one buffer per builder warp
 
 struct alignas(64) StemParams {
   CUtensorMap y_map;                         // 5-D {Cout, W, H, D, N} view of y; box {32, 8, 4, 1, 1}, 64B swizzle
@@ -33,6 +37,9 @@ struct alignas(64) StemParams {
   int in_d, in_h, in_w;
   int out_d, out_h, out_w, batch;
   int tiles_h, tiles_w;
+  int tile_h, tile_w;                        // 16 x 8 (generic builders) or 4 x 32 (3^3 single-channel row builders)
+  int quad_h;                                // h rows per TMEM lane quadrant = rows of one epilogue store box (4 or 1)
+  int afull_count;                           // arrivals that complete an A stage: 128 builder threads, or 1 warp leader
   long long total_tiles;
   const __nv_bfloat16* w;                    // [cout][64] bf16, K-major, zero padded
   int cout;
@@ -45,7 +52,7 @@ __device__ __forceinline__ void stem_tile_coords(const StemParams& p, long long 
   const unsigned iw = u % (unsigned)p.tiles_w; u /= (unsigned)p.tiles_w;
   const unsigned ih = u % (unsigned)p.tiles_h; u /= (unsigned)p.tiles_h;
   d = (int)(u % (unsigned)p.out_d); n = (int)(u / (unsigned)p.out_d);
-  h0 = (int)ih * ST_TH; w0 = (int)iw * ST_TW;
+  h0 = (int)ih * p.tile_h; w0 = (int)iw * p.tile_w;
 }
 
 // KSTEPS = ceil(K / 16): the builder writes 2*KSTEPS 16-byte chunks per row, the issuer KSTEPS MMAs per tile
@@ -60,7 +67,8 @@ __global__ void __launch_bounds__(ST_THREADS, 1) stem_conv_kernel(const __grid_c
   const uint32_t smem_w = base + ST_STAGES * ST_A_BYTES;
   uint8_t* w_ptr = base_ptr + ST_STAGES * ST_A_BYTES;
   uint8_t* out_stage = w_ptr + ST_MAX_COUT * 128;            // 1024-aligned
-  uint8_t* tail = out_stage + ST_OUT_BYTES;
+  uint8_t* patch_base = out_stage + ST_OUT_BYTES;
+  uint8_t* tail = patch_base + 8 * ST_PATCH_BYTES;
   uint64_t* bars = reinterpret_cast<uint64_t*>(tail);      // afull[S] aempty[S] tfull[2] tempty[2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tail + 8 * (2 * ST_STAGES + 4));
   float* bias_s = reinterpret_cast<float*>(tail + 8 * (2 * ST_STAGES + 4) + 64);      // [ST_MAX_COUT]
@@ -72,7 +80,7 @@ __global__ void __launch_bounds__(ST_THREADS, 1) stem_conv_kernel(const __grid_c
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (warp == 0 && lane == 0) {
-    for (int s = 0; s < ST_STAGES; ++s) { ptx::mbar_init(afull(s), 128); ptx::mbar_init(aempty(s), 1); }
+    for (int s = 0; s < ST_STAGES; ++s) { ptx::mbar_init(afull(s), (uint32_t)p.afull_count); ptx::mbar_init(aempty(s), 1); }
     for (int s = 0; s < 2; ++s) { ptx::mbar_init(tfull(s), 1); ptx::mbar_init(tempty(s), 256); }
     ptx::fence_mbar_init();
     ptx::prefetch_tmap(&p.y_map);
@@ -118,69 +126,109 @@ __global__ void __launch_bounds__(ST_THREADS, 1) stem_conv_kernel(const __grid_c
     }
     __syncwarp();
   } else if (warp <= 8) {
-    // ================= builders: thread = output voxel, two groups alternate tiles =================
-    const int grp = (warp - 1) >> 2;
-    const int v = (threadIdx.x - 32) & 127;
-    const int vh = v >> 3, vw = v & 7;
+    // ================= builders =================
     uint8_t* a_ptr = base_ptr;
-    const __nv_bfloat16 zero = __float2bfloat16(0.f);
-    const long long t_first = blockIdx.x + (long long)grp * gridDim.x, t_step = 2LL * gridDim.x;
     if constexpr (SPEC333) {
-      // The 27 taps of a voxel are gathered into registers (zero outside the input: the conv's zero padding) one tile
-      // AHEAD: the loads of tile i+2 are in flight while tile i waits for its stage and is written as 16-byte chunks.
-      auto gather = [&](long long t, __nv_bfloat16* vals) {
+      // Tile = 4 (h) x 32 (w) output voxels; ONE WARP builds a whole tile.  The warp stages the tile's input patch
+      // (3 d x 6 h x 34 w single-channel values, zero outside the input = the conv's zero padding) in shared memory
+      // with 20 coalesced 2-byte loads per lane, then every lane assembles the 27-tap rows of its four voxels
+      // (w = q + 8k) from the patch and writes them as swizzled 16-byte chunks.  Row r of the tile is voxel
+      // (h = r / 32, w = r % 32), so a quarter-warp's chunks land in eight different swizzle positions
+      // (conflict-free) and a TMEM lane quadrant is one 32-voxel row for the epilogue's store box.
+      // The patch of the warp's NEXT tile is loaded into registers before the current one is assembled.
+      static_assert(KSTEPS == 2, "row builder: K = 27 taps padded to 32");
+      const int bw = warp - 1;                                   // 0..7
+      const int q = lane & 7, vh = lane >> 3;
+      uint16_t* patch = reinterpret_cast<uint16_t*>(patch_base + bw * ST_PATCH_BYTES);
+      const int xsw = (int)p.xs_w;
+      auto load_patch = [&](long long t, uint16_t* v) {
         int n, d, h0, w0;
         stem_tile_coords(p, t, n, d, h0, w0);
-        const int hh = h0 + vh - p.ph, ww = w0 + vw - p.pw, dd = d - p.pd;
         const __nv_bfloat16* xn = p.x + (long long)n * p.xs_n;
-        const int xsw = (int)p.xs_w;
-#pragma unroll
-        for (int kk = 0; kk < 16 * KSTEPS; ++kk) vals[kk] = zero;
+        const int xw = w0 - p.pw + lane;
+        const bool win = xw >= 0 && xw < p.in_w;
+        // columns 32, 33 of patch rows 2i, 2i+1 .. : lane l covers row l >> 1 (rows 0..15), lanes 0..3 rows 16, 17
+        const int xe = w0 - p.pw + 32 + (lane & 1);
+        const bool ein = xe >= 0 && xe < p.in_w;
 #pragma unroll
         for (int a = 0; a < 3; ++a) {
-          const int z = dd + a;
+          const int z = d - p.pd + a;
           const bool zin = z >= 0 && z < p.in_d;
 #pragma unroll
-          for (int b = 0; b < 3; ++b) {
-            const int y = hh + b;
-            const bool rin = zin && y >= 0 && y < p.in_h;
-            const __nv_bfloat16* row = xn + (long long)z * p.xs_d + (long long)y * p.xs_h;
-#pragma unroll
-            for (int c = 0; c < 3; ++c) {
-              const int xw = ww + c;
-              if (rin && xw >= 0 && xw < p.in_w) vals[(a * 3 + b) * 3 + c] = __ldg(row + xw * xsw);
-            }
+          for (int hh = 0; hh < 6; ++hh) {
+            const int y = h0 - p.ph + hh;
+            const bool ok = zin && y >= 0 && y < p.in_h && win;
+            uint16_t val = 0;
+            if (ok) val = __ldg(reinterpret_cast<const uint16_t*>(xn + (long long)z * p.xs_d + (long long)y * p.xs_h) + xw * xsw);
+            v[a * 6 + hh] = val;
           }
         }
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          const int row = e * 16 + (lane >> 1);                  // patch row a * 6 + hh
+          const int a = row / 6, hh = row - a * 6;
+          const int z = d - p.pd + a, y = h0 - p.ph + hh;
+          const bool ok = row < 18 && z >= 0 && z < p.in_d && y >= 0 && y < p.in_h && ein;
+          uint16_t val = 0;
+          if (ok) val = __ldg(reinterpret_cast<const uint16_t*>(xn + (long long)z * p.xs_d + (long long)y * p.xs_h) + xe * xsw);
+          v[18 + e] = val;
+        }
       };
-      __nv_bfloat16 cur[16 * KSTEPS], nxt[16 * KSTEPS];
-      if (t_first < p.total_tiles) gather(t_first, cur);
-      long long i = grp;
-      for (long long t = t_first; t < p.total_tiles; t += t_step, i += 2) {
+      uint16_t cur[20], nxt[20];
+      const long long t_first = blockIdx.x + (long long)bw * gridDim.x, t_step = 8LL * gridDim.x;
+      if (t_first < p.total_tiles) load_patch(t_first, cur);
+      long long i = bw;
+      for (long long t = t_first; t < p.total_tiles; t += t_step, i += 8) {
+        // registers -> patch (pitch ST_PATCH_PITCH elements per row: the four h rows a warp reads sit in disjoint banks)
+#pragma unroll
+        for (int row = 0; row < 18; ++row) patch[row * ST_PATCH_PITCH + lane] = cur[row];
+        patch[(lane >> 1) * ST_PATCH_PITCH + 32 + (lane & 1)] = cur[18];
+        if (lane < 4) patch[(16 + (lane >> 1)) * ST_PATCH_PITCH + 32 + (lane & 1)] = cur[19];
         const bool more = t + t_step < p.total_tiles;
-        if (more) gather(t + t_step, nxt);
+        if (more) load_patch(t + t_step, nxt);
+        __syncwarp();
         const int st = (int)((unsigned)i % ST_STAGES);
         const uint32_t ph = (uint32_t)(((unsigned)i / ST_STAGES) & 1);
-        uint8_t* rowp = a_ptr + st * ST_A_BYTES + v * 128;
         ptx::mbar_wait_backoff(aempty(st), ph ^ 1u);
+        uint8_t* tile_ptr = a_ptr + st * ST_A_BYTES;
 #pragma unroll
-        for (int j = 0; j < 2 * KSTEPS; ++j) {
-          uint4 q;
-          q.x = (uint32_t)__bfloat16_as_ushort(cur[8 * j + 0]) | ((uint32_t)__bfloat16_as_ushort(cur[8 * j + 1]) << 16);
-          q.y = (uint32_t)__bfloat16_as_ushort(cur[8 * j + 2]) | ((uint32_t)__bfloat16_as_ushort(cur[8 * j + 3]) << 16);
-          q.z = (uint32_t)__bfloat16_as_ushort(cur[8 * j + 4]) | ((uint32_t)__bfloat16_as_ushort(cur[8 * j + 5]) << 16);
-          q.w = (uint32_t)__bfloat16_as_ushort(cur[8 * j + 6]) | ((uint32_t)__bfloat16_as_ushort(cur[8 * j + 7]) << 16);
-          *reinterpret_cast<uint4*>(rowp + ((j ^ (v & 7)) << 4)) = q;
+        for (int k = 0; k < 4; ++k) {
+          const int vw = q + 8 * k;
+          const uint16_t* src = patch + vh * ST_PATCH_PITCH + vw;
+          uint32_t wd[16];
+#pragma unroll
+          for (int m = 0; m < 16; ++m) {
+            uint32_t lo = 0, hi = 0;
+            if (2 * m < 27) {
+              const int kk = 2 * m, a = kk / 9, b = (kk / 3) % 3, c = kk % 3;
+              lo = src[(a * 6 + b) * ST_PATCH_PITCH + c];
+            }
+            if (2 * m + 1 < 27) {
+              const int kk = 2 * m + 1, a = kk / 9, b = (kk / 3) % 3, c = kk % 3;
+              hi = src[(a * 6 + b) * ST_PATCH_PITCH + c];
+            }
+            wd[m] = lo | (hi << 16);
+          }
+          const int r = vh * 32 + vw;
+          uint8_t* rowp = tile_ptr + r * 128;
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            *reinterpret_cast<uint4*>(rowp + ((j ^ (r & 7)) << 4)) = make_uint4(wd[4 * j], wd[4 * j + 1], wd[4 * j + 2], wd[4 * j + 3]);
         }
         ptx::fence_proxy_async_smem();             // generic-proxy writes -> visible to the tensor core (async proxy)
-        ptx::mbar_arrive(afull(st));
+        __syncwarp();                              // also: every lane is done reading the patch before it is rewritten
+        if (lane == 0) ptx::mbar_arrive(afull(st));
         if (more) {
 #pragma unroll
-          for (int kk = 0; kk < 16 * KSTEPS; ++kk) cur[kk] = nxt[kk];
+          for (int kk = 0; kk < 20; ++kk) cur[kk] = nxt[kk];
         }
       }
     } else {
       // generic shapes: clear the row, then one 2-byte store per tap into its swizzled position
+      const int grp = (warp - 1) >> 2;
+      const int v = (threadIdx.x - 32) & 127;
+      const int vh = v >> 3, vw = v & 7;
+      const long long t_first = blockIdx.x + (long long)grp * gridDim.x, t_step = 2LL * gridDim.x;
       long long i = grp;
       for (long long t = t_first; t < p.total_tiles; t += t_step, i += 2) {
         int n, d, h0, w0;
@@ -271,7 +319,7 @@ __global__ void __launch_bounds__(ST_THREADS, 1) stem_conv_kernel(const __grid_c
         ptx::fence_proxy_async_smem();
         __syncwarp();
         if (lane == 0) {
-          ptx::tma_store_5d(&p.y_map, my_stage_u32 + (gcount & 1u) * ST_STAGE_OUT, cb, w0, h0 + quad * 4, d, n);
+          ptx::tma_store_5d(&p.y_map, my_stage_u32 + (gcount & 1u) * ST_STAGE_OUT, cb, w0, h0 + quad * p.quad_h, d, n);
           ptx::tma_store_commit();
         }
       }
@@ -310,7 +358,7 @@ static int stem_check(const rg_igemm_desc* d) {
     K *= d->kernel[i];
   }
   RG_UNSUPPORTED(K < 1 || K > 64, "stem conv: Cin * taps must be <= 64");
-  RG_UNSUPPORTED((long long)d->n * d->out_dhw[0] * ((d->out_dhw[1] + ST_TH - 1) / ST_TH) * ((d->out_dhw[2] + ST_TW - 1) / ST_TW) >=
+  RG_UNSUPPORTED((long long)d->n * d->out_dhw[0] * ((d->out_dhw[1] + 3) / 4) * ((d->out_dhw[2] + ST_TW - 1) / ST_TW) >=
                      (1LL << 31) || llabs(d->x_strides[3]) >= (1LL << 20), "stem conv: problem too large for 32-bit tile indices");
   RG_UNSUPPORTED(d->cout % 32 != 0 || d->cout < 32 || d->cout > ST_MAX_COUT, "stem conv: Cout must be a multiple of 32, <= 256");
   for (int i = 0; i < 4; ++i) RG_UNSUPPORTED(d->y_strides[i] % 8 != 0, "stem conv: output strides must be multiples of 16 bytes");
@@ -359,8 +407,12 @@ int rg_stem_conv_run(const rg_igemm_desc* d, const void* x, long long x_channel_
   p.in_d = d->in_dhw[0]; p.in_h = d->in_dhw[1]; p.in_w = d->in_dhw[2];
   p.out_d = d->out_dhw[0]; p.out_h = d->out_dhw[1]; p.out_w = d->out_dhw[2];
   p.batch = d->n;
-  p.tiles_h = (p.out_h + ST_TH - 1) / ST_TH;
-  p.tiles_w = (p.out_w + ST_TW - 1) / ST_TW;
+  const bool spec = d->cin == 1 && d->kernel[0] == 3 && d->kernel[1] == 3 && d->kernel[2] == 3;
+  p.tile_h = spec ? 4 : ST_TH; p.tile_w = spec ? 32 : ST_TW;
+  p.quad_h = spec ? 1 : 4;
+  p.afull_count = spec ? 1 : 128;
+  p.tiles_h = (p.out_h + p.tile_h - 1) / p.tile_h;
+  p.tiles_w = (p.out_w + p.tile_w - 1) / p.tile_w;
   p.total_tiles = (long long)p.batch * p.out_d * p.tiles_h * p.tiles_w;
   p.w = (const __nv_bfloat16*)w64;
   p.cout = d->cout;
@@ -381,17 +433,17 @@ int rg_stem_conv_run(const rg_igemm_desc* d, const void* x, long long x_channel_
     cuuint64_t dims[5] = {(cuuint64_t)d->cout, (cuuint64_t)d->out_dhw[2], (cuuint64_t)d->out_dhw[1], (cuuint64_t)d->out_dhw[0], (cuuint64_t)d->n};
     cuuint64_t gs[4] = {(cuuint64_t)(d->y_strides[3] * 2), (cuuint64_t)(d->y_strides[2] * 2), (cuuint64_t)(d->y_strides[1] * 2),
                         (cuuint64_t)(d->y_strides[0] * 2)};
-    cuuint32_t bx[5] = {32, ST_TW, 4, 1, 1};
+    cuuint32_t bx[5] = {32, (cuuint32_t)p.tile_w, (cuuint32_t)p.quad_h, 1, 1};     // 32 voxels of one TMEM lane quadrant
     cuuint32_t es[5] = {1, 1, 1, 1, 1};
     CUresult r = enc(&p.y_map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, y, dims, gs, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
                      CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) { set_error("stem conv: cuTensorMapEncodeTiled (output) failed: %d", (int)r); return RG_E_CUDA; }
   }
-  const size_t smem = 1024 + (size_t)ST_STAGES * ST_A_BYTES + ST_MAX_COUT * 128 + ST_OUT_BYTES + 8 * (2 * ST_STAGES + 4) + 64 + ST_MAX_COUT * 4;
+  const size_t smem = 1024 + (size_t)ST_STAGES * ST_A_BYTES + ST_MAX_COUT * 128 + ST_OUT_BYTES + 8 * ST_PATCH_BYTES +
+                      8 * (2 * ST_STAGES + 4) + 64 + ST_MAX_COUT * 4;
   const int grid = (int)(p.total_tiles < stem_num_sms() ? p.total_tiles : stem_num_sms());
   cudaStream_t st = (cudaStream_t)stream;
   const int ksteps = (p.K + 15) / 16;
-  const bool spec = p.cin == 1 && p.kd == 3 && p.kh == 3 && p.kw == 3;
   if (spec) rc = stem_launch<2, true>(p, grid, smem, st);
   else if (ksteps == 1) rc = stem_launch<1, false>(p, grid, smem, st);
   else if (ksteps == 2) rc = stem_launch<2, false>(p, grid, smem, st);
