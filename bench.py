@@ -383,7 +383,10 @@ def run_ours(args):
     dom = max(by_kernel, key=lambda k: by_kernel[k][1])
     dfl, dms, dn = by_kernel[dom]
     achieved = dfl / (dms * 1e-3) / 1e12 if dms > 0 else 0.0
-    peak = peaks["tf_sustained"]
+    # each launch is timed between its own pair of events in an instrumented (eager) step: the kernel runs at the
+    # clocks of a kernel timed alone, so the denominator is the BURST peak (against the sustained figure the ring
+    # kernel reads 1.01); frac_of_sustained is kept beside it
+    peak = peaks["tf_burst"]
     traffic = None
     try:        # DRAM bytes per launch of that kernel from the committed `ncu --set full` capture (profiles/)
         with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
@@ -391,8 +394,8 @@ def run_ours(args):
     except OSError:
         pass
     roofline = dict(bound="tensor", kernel=f"{dom} (tcgen05; {dn} launches per step)", achieved=achieved, peak=peak,
-                    unit="TFLOP/s", frac=achieved / peak,
-                    peak_kind=f"{peaks['source']} sustained bf16 (burst {peaks['tf_burst']})", traffic=traffic,
+                    unit="TFLOP/s", frac=achieved / peak, frac_of_sustained=achieved / peaks["tf_sustained"],
+                    peak_kind=f"{peaks['source']} burst bf16 (sustained {peaks['tf_sustained']})", traffic=traffic,
                     algorithmic_tflop_per_launch=dfl / dn / 1e12, ms_per_launch=dms / dn, share_of_step=dms / ms,
                     all_convs=dict(tflops=tot_fl / (tot_ms * 1e-3) / 1e12 if tot_ms > 0 else 0.0,
                                    frac=(tot_fl / (tot_ms * 1e-3) / 1e12) / peak if tot_ms > 0 else 0.0,
