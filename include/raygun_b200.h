@@ -193,6 +193,10 @@ int rg_pad3d_fwd(const rg_tensor5* xd, const void* x, const rg_tensor5* yd, void
 /* dx = fold(dy): the adjoint of rg_pad3d_fwd (every dx element is written; no zero-initialisation needed) */
 int rg_pad3d_bwd(const rg_tensor5* dyd, const void* dy, const rg_tensor5* dxd, void* dx,
                  const int32_t lo[3], int mode, void* stream);
+/* In-place adjoint of the padding for a padded bf16 NDHWC gradient: folds the shell (lo/hi voxels per side) into the
+ * interior voxels it mirrors (reflect) or clamps to (replicate); afterwards the interior view of `g` is the gradient of
+ * the pad's input (autograd adjoint of F.pad / padding_mode="reflect", UNet.py:61-69) at O(surface) bytes.          */
+int rg_pad3d_fold(const rg_tensor5* gd, void* g, const int32_t lo[3], const int32_t hi[3], int mode, void* stream);
 /* In-place fill of the `margin`-voxel shell of a padded bf16 NDHWC buffer whose interior is already written (the
  * producing convolution's epilogue wrote it through strides): the reference's explicit padded copy
  * (F.pad / padding_mode="reflect", UNet.py:61-69, ResNet.py:262-270) reduced to O(surface) bytes.               */

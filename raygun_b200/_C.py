@@ -30,7 +30,7 @@ SYMBOLS = [
     "rg_stem_conv_supported", "rg_stem_conv_run", "rg_upconv2_supported", "rg_upconv2_run",
     "rg_halo_wgrad_supported", "rg_halo_wgrad_workspace_bytes", "rg_halo_wgrad",
     "rg_pw_conv_fprop", "rg_pw_conv_dgrad", "rg_pw_conv_wgrad", "rg_smallcin_dgrad",
-    "rg_copy5", "rg_im2col_hw", "rg_pad3d_fwd", "rg_pad3d_bwd", "rg_pad_border_fill",
+    "rg_copy5", "rg_im2col_hw", "rg_pad3d_fwd", "rg_pad3d_bwd", "rg_pad3d_fold", "rg_pad_border_fill",
     "rg_norm_stats", "rg_norm_finalize", "rg_norm_apply", "rg_norm_bwd",
     "rg_act_fwd", "rg_act_bwd", "rg_act_bwd_bias",
     "rg_maxpool3d_fwd", "rg_maxpool3d_bwd", "rg_upsample_nearest_fwd", "rg_upsample_nearest_bwd",

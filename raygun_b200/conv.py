@@ -486,7 +486,7 @@ def conv_wgrad(x, dy, w_shape, stride, pad, groups=1, want_bias=False, db=None):
     cout, cin_g = w_shape[0], w_shape[1]
     kernel = tuple(w_shape[2:])
     if _igemm_ok(cin_g, cout, kernel, stride, groups) and groups == 1:
-        xb, dyb = K.convert(x, torch.bfloat16), K.convert(dy, torch.bfloat16)
+        xb, dyb = K.conv_operand(x), K.conv_operand(dy)      # strided channel-inner views (arena interiors) in place
         n = x.shape[0]
         hd = _halo_wgrad_desc(n, cin_g, cout, tuple(x.shape[2:]), tuple(dy.shape[2:]), kernel, stride, pad,
                               _sp_strides(xb), _sp_strides(dyb))
@@ -513,7 +513,7 @@ def conv_wgrad(x, dy, w_shape, stride, pad, groups=1, want_bias=False, db=None):
             db = (db if db is not None else K.norm_stats(dyb, _C.NORM_BATCH)[0]) if want_bias else None
             return dw, db
     if _pw_ok(cin_g, cout, kernel, stride, pad, groups):
-        xb = K.convert(x, torch.bfloat16)
+        xb = K.conv_operand(x)
         dw = torch.zeros(tuple(w_shape), dtype=torch.float32, device=x.device)
         db = torch.zeros(cout, dtype=torch.float32, device=x.device) if want_bias else None
         check(lib().rg_pw_conv_wgrad(C.byref(t5(xb)), ptr(xb), C.byref(t5(dy)), ptr(dy), ptr(dw), ptr(db),

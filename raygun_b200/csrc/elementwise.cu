@@ -261,6 +261,53 @@ __global__ void __launch_bounds__(256) row_pad_bwd_kernel(T5 gd, const __nv_bflo
   }
 }
 
+// In-place adjoint of the padding: the shell of a padded NDHWC bf16 gradient is folded into the interior voxels whose
+// images it holds, and the INTERIOR VIEW of the same buffer then is the pad's input gradient -- O(surface) bytes instead
+// of the read + write of the whole volume an explicit adjoint copy costs (the backward twin of border_fill_kernel).
+// Only voxels with more than one pre-image are rewritten; every other pre-image of such a voxel lies in the shell,
+// which is never written, so the gather is race-free and deterministic.  One block per interior row (n, d, h).
+__global__ void __launch_bounds__(256) pad_fold_kernel(T5 gd, __nv_bfloat16* __restrict__ g, int lo_d, int lo_h, int lo_w,
+                                                       int hi_d, int hi_h, int hi_w, int mode) {
+  const int D = (int)gd.d - lo_d - hi_d, H = (int)gd.h - lo_h - hi_h, W = (int)gd.w - lo_w - hi_w, cg = (int)(gd.c >> 3);
+  const long long rows = gd.n * D * H;
+  const int ncand = (lo_w + 1) + (hi_w + 1);            // w candidates of a row with a single (d, h) pre-image
+  const bool edge_only_ok = ncand < W;
+  // one WARP per interior row: most rows only own their few edge voxels (ncand * cg 16-byte items)
+  const int lane = threadIdx.x & 31, warps = blockDim.x >> 5;
+  for (long long row = (long long)blockIdx.x * warps + (threadIdx.x >> 5); row < rows; row += (long long)gridDim.x * warps) {
+    const int h = (int)(row % H);
+    const long long t = row / H;
+    const int d = (int)(t % D);
+    const long long n = t / D;
+    const int nd = pad_npre(d, lo_d, hi_d, D, mode), nh = pad_npre(h, lo_h, hi_h, H, mode);
+    const bool full = (nd * nh > 1) || !edge_only_ok;
+    const int items = (full ? W : ncand) * cg;
+    __nv_bfloat16* base = g + n * gd.sn;
+    for (int j = lane; j < items; j += 32) {
+      const int wi = j / cg, c = (j - wi * cg) << 3;
+      const int w = full ? wi : (wi <= lo_w ? wi : W - 1 - hi_w + (wi - lo_w - 1));
+      const int nw = pad_npre(w, lo_w, hi_w, W, mode);
+      if (nd * nh * nw == 1) continue;
+      float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      for (int a = 0; a < nd; ++a) {
+        const long long od = pad_pre(d, a, lo_d, hi_d, D, mode);
+        for (int b = 0; b < nh; ++b) {
+          const long long oh = pad_pre(h, b, lo_h, hi_h, H, mode);
+          const __nv_bfloat16* srow = base + od * gd.sd + oh * gd.sh + c;
+          for (int e = 0; e < nw; ++e) {
+            const long long ow = pad_pre(w, e, lo_w, hi_w, W, mode);
+            float v[8];
+            ld8(srow + ow * gd.sw, v);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) acc[k] += v[k];
+          }
+        }
+      }
+      st8(base + (long long)(d + lo_d) * gd.sd + (long long)(h + lo_h) * gd.sh + (long long)(w + lo_w) * gd.sw + c, acc);
+    }
+  }
+}
+
 __global__ void vec_act_fwd_kernel(T5 xd, const __nv_bfloat16* __restrict__ x, T5 yd, __nv_bfloat16* __restrict__ y,
                                    int act, float slope) {
   const long long total = yd.numel() >> 3;
@@ -496,6 +543,23 @@ int rg_im2col_hw(const rg_tensor5* xd, const void* x, int kh, int kw, int ph, in
     im2col_hw_kernel<TS><<<grid_for(yd->n * yd->d * yd->h, 1, 148 * 32), 256, 0, st>>>(view(xd), (const TS*)x, kh, kw, ph, pw, view(yd), (__nv_bfloat16*)y);
   })
   RG_LAUNCH_CHECK("rg_im2col_hw");
+  return RG_OK;
+}
+
+int rg_pad3d_fold(const rg_tensor5* gd, void* g, const int32_t lo[3], const int32_t hi[3], int mode, void* stream) {
+  RG_CHECK_ARG(gd && g && lo && hi, "rg_pad3d_fold: null argument");
+  RG_CHECK_ARG(mode >= RG_PAD_ZEROS && mode <= RG_PAD_REPLICATE, "rg_pad3d_fold: bad mode %d", mode);
+  RG_UNSUPPORTED(!vec_ok(gd, g), "rg_pad3d_fold: buffer must be bf16 NDHWC with C %% 8 == 0");
+  for (int i = 0; i < 3; ++i) RG_CHECK_ARG(lo[i] >= 0 && lo[i] < 30 && hi[i] >= 0 && hi[i] < 30, "rg_pad3d_fold: bad pad");
+  const long long id = gd->d - lo[0] - hi[0], ih = gd->h - lo[1] - hi[1], iw = gd->w - lo[2] - hi[2];
+  RG_CHECK_ARG(id >= 1 && ih >= 1 && iw >= 1, "rg_pad3d_fold: pad larger than the buffer");
+  if (mode == RG_PAD_REFLECT)
+    RG_CHECK_ARG(lo[0] < id && hi[0] < id && lo[1] < ih && hi[1] < ih && lo[2] < iw && hi[2] < iw,
+                 "rg_pad3d_fold: reflect padding must be smaller than the interior");
+  if (mode == RG_PAD_ZEROS || gd->n * gd->c == 0) return RG_OK;       // zero padding: the interior view already is the adjoint
+  pad_fold_kernel<<<grid_for((gd->n * id * ih + 7) / 8, 1, 148 * 32), 256, 0, (cudaStream_t)stream>>>(
+      view(gd), (__nv_bfloat16*)g, lo[0], lo[1], lo[2], hi[0], hi[1], hi[2], mode);
+  RG_LAUNCH_CHECK("rg_pad3d_fold");
   return RG_OK;
 }
 

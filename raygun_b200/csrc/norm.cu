@@ -391,6 +391,52 @@ __global__ void __launch_bounds__(256) dense_act_bwd_sum_kernel(int act, float s
   }
 }
 
+// Row-strided twin of dense_act_bwd_sum_kernel: y and dy may be interiors of padded buffers (a pad-arena output, a
+// gradient folded in place by rg_pad3d_fold) -- channels contiguous, w stride = C, arbitrary h / d / n strides.
+// A block owns a contiguous range of (n, d, h) rows; one index decode per row, constant strides inside it.
+__global__ void __launch_bounds__(256) row_act_bwd_sum_kernel(int act, float slope, int cg, int lanes_v, T5 yd, T5 gd, T5 xd,
+                                                              long long rows, long long rows_per_block,
+                                                              const __nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ dy,
+                                                              __nv_bfloat16* __restrict__ dx, float* __restrict__ sums) {
+  const int cgi = threadIdx.x % cg, lv = threadIdx.x / cg;
+  const int c = cgi << 3, W = (int)yd.w, H = (int)yd.h, D = (int)yd.d;
+  float s[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) s[k] = 0.f;
+  const long long r0 = blockIdx.x * rows_per_block, r1 = min(r0 + rows_per_block, rows);
+  for (long long r = r0; r < r1; ++r) {
+    const int h = (int)(r % H);
+    const long long t = r / H;
+    const int d = (int)(t % D);
+    const long long n = t / D;
+    const __nv_bfloat16* yr = y + n * yd.sn + d * yd.sd + h * yd.sh + c;
+    const __nv_bfloat16* gr = dy + n * gd.sn + d * gd.sd + h * gd.sh + c;
+    __nv_bfloat16* xr = dx + n * xd.sn + d * xd.sd + h * xd.sh + c;
+#pragma unroll 2
+    for (int w = lv; w < W; w += lanes_v) {
+      float g[8], yy[8];
+      ld8(gr + (long long)w * gd.sw, g);
+      ld8(yr + (long long)w * yd.sw, yy);
+      act_grad8(g, yy, act, slope);
+      st8(xr + (long long)w * xd.sw, g);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) s[k] += g[k];
+    }
+  }
+  __shared__ float red[256];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    red[threadIdx.x] = s[k];
+    __syncthreads();
+    if (threadIdx.x < cg) {
+      float a = 0.f;
+      for (int l = 0; l < lanes_v; ++l) a += red[threadIdx.x + cg * l];
+      atomicAdd(sums + (threadIdx.x << 3) + k, a);
+    }
+    __syncthreads();
+  }
+}
+
 }  // namespace rg
 
 using namespace rg;
@@ -522,12 +568,25 @@ int rg_act_bwd_bias(const rg_tensor5* yd, const void* y, const rg_tensor5* dyd, 
   RG_CHECK_ARG(yd && dyd && dxd && y && dy && dx && bias_sum, "rg_act_bwd_bias: null argument");
   RG_CHECK_ARG(same_shape(yd, dyd) && same_shape(yd, dxd), "rg_act_bwd_bias: shape mismatch");
   const long long per = yd->d * yd->h * yd->w * yd->c;
-  RG_UNSUPPORTED(!dense_ok(yd, y) || !dense_ok(dyd, dy) || !dense_ok(dxd, dx) || !dense_cg_ok(yd) || yd->sn != per ||
-                     dyd->sn != per || dxd->sn != per,
-                 "rg_act_bwd_bias: needs dense NDHWC bf16 tensors");
   const long long vox = yd->n * yd->d * yd->h * yd->w;
   if (vox == 0) return RG_OK;
-  const int cg = (int)(yd->c >> 3), lanes_v = 256 / cg;
+  const int cg = (int)(yd->c >> 3), lanes_v = cg ? 256 / cg : 0;
+  if (!dense_ok(yd, y) || !dense_ok(dyd, dy) || !dense_ok(dxd, dx) || yd->sn != per || dyd->sn != per || dxd->sn != per) {
+    // row-strided operands (pad-arena interiors, gradients folded in place): channels contiguous, w stride = C
+    RG_UNSUPPORTED(!vec_ok(yd, y) || !vec_ok(dyd, dy) || !vec_ok(dxd, dx) || !dense_cg_ok(yd),
+                   "rg_act_bwd_bias: needs bf16 NDHWC tensors with C %% 8 == 0 and 256 %% (C/8) == 0");
+    const long long rows = yd->n * yd->d * yd->h;
+    long long rpb = (rows + 148LL * 8 - 1) / (148LL * 8);
+    const long long min_rpb = (48LL * lanes_v + yd->w - 1) / yd->w;
+    if (rpb < min_rpb) rpb = min_rpb;
+    const long long blocks = (rows + rpb - 1) / rpb;
+    row_act_bwd_sum_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(act, slope, cg, lanes_v, view(yd), view(dyd), view(dxd),
+                                                                              rows, rpb, (const __nv_bfloat16*)y, (const __nv_bfloat16*)dy,
+                                                                              (__nv_bfloat16*)dx, bias_sum);
+    RG_LAUNCH_CHECK("rg_act_bwd_bias(row)");
+    return RG_OK;
+  }
+  RG_UNSUPPORTED(!dense_cg_ok(yd), "rg_act_bwd_bias: needs C %% 8 == 0 and 256 %% (C/8) == 0");
   long long blocks = 148LL * 8;
   long long vpb = (vox + blocks - 1) / blocks;
   const long long min_vpb = 48LL * lanes_v;                 // fat blocks: a fixed smem + atomics tail per block

@@ -12,6 +12,10 @@ from . import kernels as K
 from ._C import (ACT_LEAKY, ACT_NONE, ACT_RELU, ACT_SIGMOID, ACT_TANH, LOSS_L1, LOSS_MEAN, LOSS_MSE_CONST, LOSS_SMOOTHL1,
                  NORM_BATCH, NORM_INSTANCE, PAD_REFLECT, PAD_REPLICATE, PAD_ZEROS)
 
+import os as _os
+TRAIN_ARENA = _os.environ.get("RAYGUN_B200_TRAIN_ARENA", "1") != "0"     # pad arenas for conv+activation outputs in training
+PAD_FOLD = _os.environ.get("RAYGUN_B200_PAD_FOLD", "1") != "0"           # in-place pad adjoint behind our convolutions
+
 PAD_MODES = {"zeros": PAD_ZEROS, "constant": PAD_ZEROS, "reflect": PAD_REFLECT, "replicate": PAD_REPLICATE}
 
 
@@ -182,7 +186,10 @@ def conv3d(x, w, bias=None, stride=1, padding=0, groups=1, act=ACT_NONE, slope=0
     skip-connection concat buffer; the result IS `out` when the kernel could honour it (callers check identity)."""
     if torch.is_grad_enabled():
         out = None
-    with K.arena_scope(not torch.is_grad_enabled()):
+    # training: a convolution + activation with no norm behind it (every G-UNet ConvPass conv) also writes into a pad
+    # arena -- the next reflect-padded conv mirrors the shell in place, the activation backward reads the interior view
+    train_arena = TRAIN_ARENA and act != ACT_NONE and not want_stats
+    with K.arena_scope(not torch.is_grad_enabled() or train_arena):
         if _stem_eligible(x, w, _t3(stride), int(groups)):
             y, s, q = _StemConv3d.apply(x, w, bias, _t3(padding), act, float(slope), bool(want_stats), out)
         else:
@@ -250,25 +257,54 @@ def conv_transpose3d(x, w, bias=None, stride=1, padding=0, output_padding=0, act
 # padding
 # ---------------------------------------------------------------------------------------------
 class _Pad3d(torch.autograd.Function):
-    """nn.ReflectionPad3d / ReplicationPad3d / F.pad (ResNet.py:270-279,392-401; Conv3d padding_mode)."""
+    """nn.ReflectionPad3d / ReplicationPad3d / F.pad (ResNet.py:270-279,392-401; Conv3d padding_mode).
+    fold=True: the adjoint folds the shell of the incoming gradient IN PLACE and hands its interior view upstream
+    (O(surface) bytes); only where the single consumer of the padded tensor is one of our convolutions, whose
+    data gradient is a fresh buffer."""
 
     @staticmethod
-    def forward(ctx, x, lo, hi, mode):
-        ctx.args = (tuple(x.shape), lo, mode)
+    def forward(ctx, x, lo, hi, mode, fold=False):
+        ctx.args = (tuple(x.shape), lo, hi, mode, fold)
         return K.pad3d(x, lo, hi, mode)
 
     @staticmethod
     def backward(ctx, dy):
-        shape, lo, mode = ctx.args
+        shape, lo, hi, mode, fold = ctx.args
+        if fold and K.is_ndhwc(dy) and dy.shape[1] % 8 == 0:
+            return K.pad3d_fold(dy, lo, hi, mode), None, None, None, None
+        return K.pad3d_bwd(dy, shape, lo, mode), None, None, None, None
+
+
+class _PadArena(torch.autograd.Function):
+    """Padding of a tensor that IS the interior of a pad arena (kernels.empty5_arena): the shell is mirrored in place
+    and the padded view of the same buffer is returned (no copy); the adjoint folds the gradient's shell in place.
+    Same call sites as _Pad3d (UNet.py:61-69 padding_mode="reflect")."""
+
+    @staticmethod
+    def forward(ctx, x, lo, hi, mode):
+        full, m = K.arena_of(x, lo, hi)
+        K.border_fill(full, m, mode)
+        d, h, w = x.shape[2:]
+        ctx.args = (tuple(x.shape), lo, hi, mode)
+        return full[:, :, m - lo[0]: m + d + hi[0], m - lo[1]: m + h + hi[1], m - lo[2]: m + w + hi[2]]
+
+    @staticmethod
+    def backward(ctx, dy):
+        shape, lo, hi, mode = ctx.args
+        if K.is_ndhwc(dy) and dy.shape[1] % 8 == 0:
+            return K.pad3d_fold(dy, lo, hi, mode), None, None, None
         return K.pad3d_bwd(dy, shape, lo, mode), None, None, None
 
 
-def pad3d(x, lo, hi=None, mode="reflect"):
+def pad3d(x, lo, hi=None, mode="reflect", fold=False):
     lo = _t3(lo)
     hi = lo if hi is None else _t3(hi)
     if not any(lo) and not any(hi):
         return x
-    return _Pad3d.apply(x, lo, hi, PAD_MODES[mode] if isinstance(mode, str) else mode)
+    mode = PAD_MODES[mode] if isinstance(mode, str) else mode
+    if x.dim() == 5 and x.is_cuda and K.arena_of(x, lo, hi) is not None:
+        return _PadArena.apply(x, lo, hi, mode)
+    return _Pad3d.apply(x, lo, hi, mode, bool(fold) and x.dtype == torch.bfloat16)
 
 
 # ---------------------------------------------------------------------------------------------
@@ -304,7 +340,9 @@ class _NormAct(torch.autograd.Function):
 
 
 def norm_act(x, kind, mean, rstd, gamma=None, beta=None, residual=None, act=ACT_NONE, slope=0.0, training=True):
-    return _NormAct.apply(x, kind, mean, rstd, gamma, beta, residual, act, float(slope), bool(training))
+    y = _NormAct.apply(x, kind, mean, rstd, gamma, beta, residual, act, float(slope), bool(training))
+    y._rg_dense_grad = True      # the norm backward kernels are fastest on dense gradients: no in-place pad fold upstream
+    return y
 
 
 def add_act(x, residual, act=ACT_NONE, slope=0.0):
@@ -353,19 +391,22 @@ class _MaxPool3d(torch.autograd.Function):
     """nn.MaxPool3d(f, stride=f) (UNet.py:209-218)."""
 
     @staticmethod
-    def forward(ctx, x, f):
+    def forward(ctx, x, f, arena=False):
         ctx.f = f
         ctx.save_for_backward(x)
-        return K.maxpool_fwd(x, f)
+        return K.maxpool_fwd(x, f, arena=arena)
 
     @staticmethod
     def backward(ctx, dy):
         (x,) = ctx.saved_tensors
-        return K.maxpool_bwd(x, dy, ctx.f), None
+        return K.maxpool_bwd(x, dy, ctx.f), None, None
 
 
 def max_pool3d(x, f):
-    return _MaxPool3d.apply(x, _t3(f))
+    # training: the pooled tensor feeds the next level's reflect-padded ConvPass -> allocate it as a pad arena
+    arena = (TRAIN_ARENA and torch.is_grad_enabled() and x.dtype == torch.bfloat16 and x.shape[1] % 8 == 0
+             and K.get_precision() == "bf16")
+    return _MaxPool3d.apply(x, _t3(f), arena)
 
 
 class _UpsampleNearest(torch.autograd.Function):
@@ -402,11 +443,15 @@ class _CropCat(torch.autograd.Function):
     buffer; backward hands out strided views / zero-padded slices of dy."""
 
     @staticmethod
-    def forward(ctx, a, b, spatial):
+    def forward(ctx, a, b, spatial, train_arena=False):
+        ctx.train_arena = train_arena
         av, bv = center_crop_view(a, spatial), center_crop_view(b, spatial)
         n = a.shape[0]
         dt = a.dtype if a.dtype == b.dtype else K.compute_dtype()
-        out = K.empty5((n, a.shape[1] + b.shape[1], *spatial), dt, a.device)
+        shape = (n, a.shape[1] + b.shape[1], *spatial)
+        # training: the concat buffer is a pad arena too (the decoder ConvPass behind it pads by mirroring its shell)
+        arena = ctx.train_arena and dt == torch.bfloat16 and shape[1] % 8 == 0 and K.get_precision() == "bf16"
+        out = K.empty5_arena(shape, dt, a.device) if arena else K.empty5(shape, dt, a.device)
         K.copy_into(out[:, : a.shape[1]], av)
         K.copy_into(out[:, a.shape[1]:], bv)
         ctx.shapes = (tuple(a.shape), tuple(b.shape), tuple(spatial), a.dtype, b.dtype)
@@ -419,6 +464,9 @@ class _CropCat(torch.autograd.Function):
         def part(sl, shape, dt):
             g = dy[:, sl]
             if tuple(shape[2:]) == spatial:
+                # densified: handing the channel-slice view upstream was measured slower (autograd's skip-gradient add
+                # and the up-conv bias reduction leave their vectorised paths on strided operands: +3.8 ms vs 2.6 ms of
+                # copies per cfg3 step)
                 return K.convert(g, dt)
             full = K.empty5(shape, dt, dy.device)
             full.zero_()
@@ -427,11 +475,11 @@ class _CropCat(torch.autograd.Function):
 
         ga = part(slice(0, sa[1]), sa, da) if ctx.needs_input_grad[0] else None
         gb = part(slice(sa[1], sa[1] + sb[1]), sb, db) if ctx.needs_input_grad[1] else None
-        return ga, gb, None
+        return ga, gb, None, None
 
 
 def crop_cat(a, b, spatial):
-    return _CropCat.apply(a, b, tuple(int(s) for s in spatial))
+    return _CropCat.apply(a, b, tuple(int(s) for s in spatial), TRAIN_ARENA and torch.is_grad_enabled())
 
 
 class _Crop(torch.autograd.Function):

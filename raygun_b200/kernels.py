@@ -181,6 +181,23 @@ def pad3d(x, lo, hi, mode):
     return y
 
 
+def is_row_ndhwc(t: torch.Tensor) -> bool:
+    """bf16, channels contiguous, 16-byte aligned rows: dense NDHWC tensors and interiors / channel-complete crops of them."""
+    st = t.stride()
+    return (t.dtype == torch.bfloat16 and t.dim() == 5 and st[1] == 1 and t.shape[1] % 8 == 0
+            and all(v % 8 == 0 for v in (st[0], st[2], st[3], st[4])) and t.data_ptr() % 16 == 0)
+
+
+def pad3d_fold(dy, lo, hi, mode):
+    """Adjoint of the padding IN PLACE: folds the shell of the padded gradient `dy` into its interior and returns the
+    interior VIEW (shape of the pad's input).  `dy` must be a bf16 NDHWC buffer this call may overwrite."""
+    require_device(dy)
+    check(lib().rg_pad3d_fold(C.byref(t5(dy)), ptr(dy), i3(lo), i3(hi), C.c_int(mode), stream_ptr(dy.device)), "rg_pad3d_fold")
+    count_launch()
+    d, h, w = dy.shape[2:]
+    return dy[:, :, lo[0]: d - hi[0], lo[1]: h - hi[1], lo[2]: w - hi[2]]
+
+
 def pad3d_bwd(dy, x_shape, lo, mode):
     dx = empty5(x_shape, dy.dtype, dy.device)          # fully written by the kernel
     check(lib().rg_pad3d_bwd(C.byref(t5(dy)), ptr(dy), C.byref(t5(dx)), ptr(dx), i3(lo), C.c_int(mode),
@@ -212,9 +229,10 @@ def act_bwd(y, dy, act, slope=0.0):
 
 
 def act_bwd_bias(y, dy, act, slope=0.0):
-    """(dy * act'(y), per-channel sum of it) in one pass when everything is dense NDHWC bf16, else (act_bwd, None)."""
-    if (y.dtype == torch.bfloat16 and dy.dtype == torch.bfloat16 and is_ndhwc(y) and is_ndhwc(dy) and y.shape[1] % 8 == 0
-            and y.shape[1] <= 2048 and 256 % (y.shape[1] // 8) == 0):
+    """(dy * act'(y), per-channel sum of it) in one pass for bf16 NDHWC operands (dense, or row-strided interiors of
+    padded buffers), else (act_bwd, None)."""
+    if (is_row_ndhwc(y) and is_row_ndhwc(dy) and y.shape[1] <= 2048 and 256 % (y.shape[1] // 8) == 0
+            and y.shape[2] * y.shape[3] * y.shape[4] * y.shape[1] < 2 ** 31):
         dx = empty5(y.shape, y.dtype, y.device)
         db = torch.zeros(y.shape[1], dtype=torch.float32, device=y.device)
         check(lib().rg_act_bwd_bias(C.byref(t5(y)), ptr(y), C.byref(t5(dy)), ptr(dy), C.c_int(act), C.c_float(slope),
@@ -224,10 +242,11 @@ def act_bwd_bias(y, dy, act, slope=0.0):
     return act_bwd(y, dy, act, slope), None
 
 
-def maxpool_fwd(x, f):
+def maxpool_fwd(x, f, arena=False):
     require_device(x)
     n, c, d, h, w = x.shape
-    y = empty5((n, c, d // f[0], h // f[1], w // f[2]), x.dtype, x.device)
+    shape = (n, c, d // f[0], h // f[1], w // f[2])
+    y = empty5_arena(shape, x.dtype, x.device) if arena else empty5(shape, x.dtype, x.device)
     check(lib().rg_maxpool3d_fwd(C.byref(t5(x)), ptr(x), i3(f), C.byref(t5(y)), ptr(y), stream_ptr(x.device)),
           "rg_maxpool3d_fwd")
     count_launch()

@@ -103,15 +103,19 @@ class Conv3d(tnn.Conv3d):
             if self.padding_mode == "zeros" and lo == hi:
                 pad = lo
             elif self.padding_mode in ("zeros", "reflect", "replicate"):
-                arena = K.arena_of(x, lo, hi) if (x.dim() == 5 and x.is_cuda and not torch.is_grad_enabled()) else None
-                if arena is not None:
+                arena = K.arena_of(x, lo, hi) if (x.dim() == 5 and x.is_cuda) else None
+                if arena is not None and not torch.is_grad_enabled():
                     # x is the interior of a pad arena: mirror the shell in place, read the padded view (no copy)
                     full, m = arena
                     K.border_fill(full, m, F.PAD_MODES[self.padding_mode])
                     d, h, w = x.shape[2:]
                     x = full[:, :, m - lo[0]: m + d + hi[0], m - lo[1]: m + h + hi[1], m - lo[2]: m + w + hi[2]]
                 else:
-                    x = F.pad3d(x, lo, hi, self.padding_mode)
+                    # training: arena interiors take the same in-place route through autograd (F._PadArena); other
+                    # inputs are copied, and the adjoint folds the conv's fresh data gradient in place unless the
+                    # producer is a norm layer (dense-gradient kernels)
+                    x = F.pad3d(x, lo, hi, self.padding_mode,
+                                fold=F.PAD_FOLD and not getattr(x, "_rg_dense_grad", False))
             else:
                 raise NotImplementedError(f"padding_mode {self.padding_mode!r} is not implemented")
         return F.conv3d(x, self.weight, self.bias, self.stride, pad, self.groups, act, slope, want_stats, out=out)

@@ -247,7 +247,8 @@ def _ndhwc(t):
 @pytest.mark.parametrize("mode", ["reflect", "replicate", "zeros"])
 @pytest.mark.parametrize("lo,hi", [((1, 1, 1), (1, 1, 1)), ((3, 3, 3), (3, 3, 3)), ((0, 2, 1), (2, 0, 1))])
 @pytest.mark.parametrize("c", [16, 64])          # 64 channels x 9 voxels per row: the row-based adjoint kernel
-def test_vec_pad_and_adjoint_bf16_ndhwc(mode, lo, hi, c):
+@pytest.mark.parametrize("fold", [False, True])   # True: rg_pad3d_fold, the in-place O(surface) adjoint
+def test_vec_pad_and_adjoint_bf16_ndhwc(mode, lo, hi, c, fold):
     from raygun_b200 import functional as F
     torch.manual_seed(21)
     x = _bf(torch.randn(2, c, 5, 6, 9 if c == 64 else 7)).requires_grad_(True)
@@ -256,11 +257,17 @@ def test_vec_pad_and_adjoint_bf16_ndhwc(mode, lo, hi, c):
     r = _bf(torch.randn_like(y_ref))
     (gx,) = torch.autograd.grad((y_ref * r).sum(), [x])
     xg = _ndhwc(x.detach()).requires_grad_(True)
-    y = F.pad3d(xg, lo, hi, mode)
-    y.backward(_ndhwc(r))
+    y = F.pad3d(xg, lo, hi, mode, fold=fold)
+    y.backward(_ndhwc(r).clone())
     assert y.dtype == torch.bfloat16
     _close(y, y_ref, 0.0, "vec pad")
     _close(xg.grad, gx, 1e-2, "vec pad adjoint")
+    if fold:        # the folded interior view equals the copying adjoint bit for bit (same fp32 gather order)
+        from raygun_b200 import kernels as K
+        m = F.PAD_MODES[mode]
+        a = K.pad3d_bwd(_ndhwc(r), tuple(x.shape), lo, m)
+        b = K.pad3d_fold(_ndhwc(r).clone(), lo, hi, m)
+        assert tuple(b.shape) == tuple(x.shape) and torch.equal(a, b)
 
 
 @pytest.mark.parametrize("kind", ["instance", "batch"])
@@ -457,9 +464,20 @@ def test_fused_activation_backward_and_bias_gradient(act):
     assert db is not None and torch.equal(dx, ref)
     want = ref.float().sum(dim=(0, 2, 3, 4))
     assert float((db - want).abs().max()) <= 2e-3 * float(want.abs().max())
-    # a strided (non-dense) operand falls back to the two-kernel path
-    dx2, db2 = K.act_bwd_bias(y[:, :32], dy[:, :32], act, 0.2)
-    assert db2 is None and torch.equal(dx2, ref[:, :32])
+    # row-strided operands (interiors of padded buffers: pad-arena outputs, gradients folded in place) take the row kernel
+    yp = torch.nn.functional.pad(y, (1, 1, 1, 1, 1, 1)).contiguous(memory_format=torch.channels_last_3d)
+    dp = torch.nn.functional.pad(dy, (2, 0, 1, 2, 0, 1)).contiguous(memory_format=torch.channels_last_3d)
+    yi, di = yp[:, :, 1:-1, 1:-1, 1:-1], dp[:, :, 0:-1, 1:-2, 2:]
+    assert not yi.is_contiguous(memory_format=torch.channels_last_3d) and torch.equal(yi, y) and torch.equal(di, dy)
+    dx2, db2 = K.act_bwd_bias(yi, di, act, 0.2)
+    assert db2 is not None and torch.equal(dx2, ref)
+    assert float((db2 - want).abs().max()) <= 2e-3 * float(want.abs().max())
+    # a channel slice is row-strided too
+    dx3, db3 = K.act_bwd_bias(y[:, :32], dy[:, :32], act, 0.2)
+    assert db3 is not None and torch.equal(dx3, ref[:, :32])
+    # fp32 operands fall back to the two-kernel path
+    dx4, db4 = K.act_bwd_bias(y.float(), dy.float(), act, 0.2)
+    assert db4 is None
 
 
 def test_conv_relu_bias_gradient_through_the_fused_pass():
@@ -482,3 +500,50 @@ def test_conv_relu_bias_gradient_through_the_fused_pass():
         yg.backward(g.to(DEV).to(yg.dtype))
     rel = lambda a, b: float((a.float().cpu() - b).abs().max()) / max(1e-6, float(b.abs().max()))
     assert rel(bg.grad, rb_) <= 1e-2 and rel(wg.grad, rw) <= 1e-2
+
+
+def test_training_pad_arenas_and_in_place_fold_match_the_copying_path():
+    """Two reflect-'same' Conv3d + ReLU layers (a G-UNet ConvPass, UNet.py:61-69) in training: with pad arenas and the
+    in-place pad adjoint the output is bit-identical to the copying path and every gradient agrees; both match torch."""
+    import raygun_b200 as rb
+    from raygun_b200 import functional as F, nn as L
+    torch.manual_seed(31)
+    q = lambda t: t.bfloat16().float()
+    c1 = L.Conv3d(64, 64, 3, padding="same", padding_mode="reflect").to(DEV)
+    c2 = L.Conv3d(64, 128, 3, padding="same", padding_mode="reflect").to(DEV)
+    with torch.no_grad():
+        for c in (c1, c2):
+            c.weight.copy_(q(c.weight))
+    layers = [c1, L.ReLU(), c2, L.ReLU()]
+    x0 = q(torch.randn(2, 64, 10, 12, 16, device=DEV))
+    g0 = q(torch.randn(2, 128, 10, 12, 16, device=DEV))
+    params = [c1.weight, c1.bias, c2.weight, c2.bias]
+
+    def run(arena, fold):
+        F.TRAIN_ARENA, F.PAD_FOLD = arena, fold
+        try:
+            with rb.precision("bf16"):
+                x = x0.bfloat16().contiguous(memory_format=torch.channels_last_3d).requires_grad_(True)
+                # a max-pool in front: its output is neither an arena interior nor a norm output -> copying pad + fold
+                y = L.run_layers(layers, F.max_pool3d(F.upsample_nearest(x, (2, 2, 2)), (2, 2, 2)))
+                grads = torch.autograd.grad(y, [x] + params, g0.to(y.dtype))
+            return y.detach().float(), [g.float() for g in grads], y
+        finally:
+            F.TRAIN_ARENA, F.PAD_FOLD = True, True
+
+    y_a, g_a, yt = run(True, True)
+    assert getattr(yt._base, "_rg_arena", None) == 1          # conv + ReLU outputs are arena interiors in training
+    y_b, g_b, yt_b = run(False, False)
+    assert yt_b.is_contiguous(memory_format=torch.channels_last_3d)
+    assert torch.equal(y_a, y_b)
+    for a, b in zip(g_a, g_b):
+        assert float((a - b).abs().max()) <= 2e-3 * max(1e-6, float(b.abs().max()))
+    # torch reference (fp32 math on the bf16-rounded parameters)
+    xr = x0.clone().requires_grad_(True)
+    h = TF.relu(TF.conv3d(TF.pad(xr, (1,) * 6, mode="reflect"), c1.weight, c1.bias))
+    yr = TF.relu(TF.conv3d(TF.pad(h, (1,) * 6, mode="reflect"), c2.weight, c2.bias))
+    gr = torch.autograd.grad(yr, [xr] + params, g0)
+    rel = lambda a, b: float((a - b.float()).abs().max()) / max(1e-6, float(b.abs().max()))
+    assert rel(y_a, yr.detach()) <= 2e-2
+    for a, b in zip(g_a, gr):
+        assert rel(a, b) <= 1e-1          # bf16 activations through two layers (the copying path shows the same)
