@@ -40,6 +40,7 @@ struct alignas(64) IgemmParams {
   int kc;             // reduction channels per tap (multiple of 64)
   int tiles_w, tiles_h, tiles_d, batch;
   int tw, th, td;
+  int a_box_bytes;    // bytes one activation TMA box delivers: tw*th*td rows of 128 B (<= A_BYTES: free-form boxes)
   int n_tiles_n;      // output-channel tiles of BN
   int out_w, out_h, out_d;
   int cout_total;
@@ -123,7 +124,7 @@ __global__ void __launch_bounds__(IGEMM_THREADS, 1) igemm_conv_kernel(const __gr
               const int koff = ((p.tap_kidx[0][a] * p.kdims[1] + p.tap_kidx[1][b]) * p.kdims[2] + p.tap_kidx[2][c]) * p.kc;
               for (int q = 0; q < chunks; ++q) {
                 ptx::mbar_wait(empty_bar(stage), phase ^ 1u);
-                ptx::mbar_arrive_expect_tx(full_bar(stage), Cfg::STAGE_BYTES);
+                ptx::mbar_arrive_expect_tx(full_bar(stage), (uint32_t)(p.a_box_bytes + Cfg::B_BYTES));
                 ptx::tma_load_5d(smem_a + stage * A_BYTES, am, full_bar(stage), q * BLOCK_K, cw, ch, cd, n);
                 ptx::tma_load_2d(smem_b + stage * Cfg::B_BYTES, &p.b_map, full_bar(stage), koff + q * BLOCK_K, nt * BN);
                 if (++stage == STAGES) { stage = 0; phase ^= 1u; }
@@ -189,7 +190,8 @@ __global__ void __launch_bounds__(IGEMM_THREADS, 1) igemm_conv_kernel(const __gr
       int nt, n, d0, h0, w0;
       decode_tile(tile, nt, n, d0, h0, w0);
       if (n != st_n || nt != st_nt) { flush_stats(); st_n = n; st_nt = nt; }
-      const bool valid = (w0 + rw < p.out_w) && (h0 + rh < p.out_h) && (d0 + rd < p.out_d);
+      // rd >= td: a row past the end of a free-form box (tw*th*td < 128): the MMA read stale shared memory for it
+      const bool valid = (rd < p.td) && (w0 + rw < p.out_w) && (h0 + rh < p.out_h) && (d0 + rd < p.out_d);
       // bias for this channel tile -> smem (visible after the first named barrier below)
       for (int i = et; i < BN; i += 128) bias_s[i] = p.bias ? p.bias[nt * BN + i] : 0.f;
       ptx::mbar_wait(tfull_bar(acc), acc_phase);
@@ -519,8 +521,36 @@ static int encode_weight_map(CUtensorMap* m, const void* ptr, long long ktot, in
   return RG_OK;
 }
 
-// Pick the {d,h,w} box with 128 voxels that wastes the fewest padded voxels; ties -> most cubic.
-static void choose_box(const int ext[3], int box[3]) {
+// Pick the {d,h,w} output box of one 128-row MMA tile.
+// exact (wgrad: the box is the GEMM-K dimension, every row must be data): power-of-two dims with product 128 that waste
+// the fewest padded voxels; ties -> most cubic.
+// free-form (fprop / dgrad: rows are independent outputs): ANY dims with product <= 128 -- the TMA box lands as
+// consecutive 128-byte rows whatever its shape, rows past its end are masked in the epilogue -- chosen to minimise the
+// waves of the persistent grid, then the tile count (odd extents: the 34^3 padded data gradient of a ResnetBlock
+// takes 5 waves of (1,7,17) boxes instead of 6 waves of (4,4,8); the discriminator's 33^3 / 17^3 / 9^3 maps likewise).
+static bool free_form_boxes() {
+  static const bool on = [] { const char* e = getenv("RAYGUN_B200_FREE_BOX"); return !(e && e[0] == '0'); }();
+  return on;
+}
+
+static void choose_box(const int ext[3], int box[3], bool exact, long long mult, int sms) {
+  if (!exact) {
+    long long best_w = -1, best_t = -1; int bscore = 0;
+    for (int bd = 1; bd <= 128 && bd <= ext[0]; ++bd)
+      for (int bh = 1; bd * bh <= 128 && bh <= ext[1]; ++bh) {
+        int bw = 128 / (bd * bh);
+        if (bw > ext[2]) bw = ext[2];
+        if (bw > 256) bw = 256;
+        const long long tiles = (long long)((ext[0] + bd - 1) / bd) * ((ext[1] + bh - 1) / bh) * ((ext[2] + bw - 1) / bw) * mult;
+        const long long waves = (tiles + sms - 1) / sms;
+        int mx = bd > bh ? bd : bh; mx = mx > bw ? mx : bw;
+        const int score = -mx + (bw >= 8 ? 1000 : 0);
+        if (best_w < 0 || waves < best_w || (waves == best_w && (tiles < best_t || (tiles == best_t && score > bscore)))) {
+          best_w = waves; best_t = tiles; bscore = score; box[0] = bd; box[1] = bh; box[2] = bw;
+        }
+      }
+    return;
+  }
   long long best = -1; int bscore = 0;
   for (int bd = 1; bd <= 128; bd *= 2)
     for (int bh = 1; bd * bh <= 128; bh *= 2) {
@@ -643,9 +673,10 @@ int rg_plan_create(const rg_igemm_desc* d, rg_plan** out) {
     for (int a = 0; a < L.p.ntap[0]; ++a)
       for (int b = 0; b < L.p.ntap[1]; ++b)
         for (int c = 0; c < L.p.ntap[2]; ++c) L.a_used[L.p.tap_par[0][a] * 4 + L.p.tap_par[1][b] * 2 + L.p.tap_par[2][c]] = 1;
-    choose_box(L.out_ext, L.box);
+    choose_box(L.out_ext, L.box, d->mode == 2 || !free_form_boxes(), (long long)d->n * (rows / pl->bn), num_sms());
     L.p.kc = kc;
     L.p.td = L.box[0]; L.p.th = L.box[1]; L.p.tw = L.box[2];
+    L.p.a_box_bytes = L.box[0] * L.box[1] * L.box[2] * BLOCK_K * 2;
     L.p.tiles_d = (L.out_ext[0] + L.box[0] - 1) / L.box[0];
     L.p.tiles_h = (L.out_ext[1] + L.box[1] - 1) / L.box[1];
     L.p.tiles_w = (L.out_ext[2] + L.box[2] - 1) / L.box[2];
