@@ -639,7 +639,9 @@ def run_cyclegan(args):
             N.init_weights(d, "kaiming")
     sync = GradSync({"G": list(g1.parameters()) + list(g2.parameters()),
                      "D": list(d1.parameters()) + list(d2.parameters())}) if world > 1 else None
-    step = CycleGANStep(g1, g2, d1, d2, lr=1e-5, grad_sync=sync)
+    # the whole step (forwards, backwards, gradient all-reduces, both Adam updates) replays as ONE CUDA graph after
+    # three eager steps; --no-graph keeps ~1500 eager launches per step (host-bound at one sample per GPU)
+    step = CycleGANStep(g1, g2, d1, d2, lr=1e-5, grad_sync=sync, graph=not args.no_graph)
     host_a = synth_batch(per, SIDE, 42 + 100 * rank).pin_memory()
     host_b = synth_batch(per, SIDE, 43 + 100 * rank).pin_memory()
     dev_a = K.u8_normalise(host_a.to(dev), dtype=torch.bfloat16)
@@ -674,14 +676,16 @@ def run_cyclegan(args):
             ms = float(t)
         return ms, r
 
-    for _ in range(max(3, args.warmup)):
+    for _ in range(max(3, args.warmup) + (2 if not args.no_graph else 0)):   # 3 eager steps, the capture, replays
         resident()
+    if step.graph_error is not None:
+        print(f"bench.py: CUDA graph capture failed ({step.graph_error}); running eager", file=sys.stderr)
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
     l0 = _C.launch_count
     ms, losses = timed(resident, args.steps)
-    launches = (_C.launch_count - l0) // args.steps
+    launches = step.graph_launches if step.graph is not None else (_C.launch_count - l0) // args.steps
     clocks = sampler.stop() if rank == 0 else None
     ms_e2e, _ = timed(e2e, args.steps)
     if rank == 0:
@@ -701,7 +705,8 @@ def run_cyclegan(args):
                     config=dict(workload="cfg3: CycleGAN step, 2 x G-UNet + 2 x NLayerDiscriminator(n_layers 3, kw 3), LSGAN + "
                                          "SmoothL1 cycle loss (lambda 10/0/1), Adam lr 1e-5, global batch 8 of 1x64^3 per domain",
                                 per_gpu_batch=per, l2="activations of one step (GBs) >> 126 MB L2; no explicit flush",
-                                parallelism=f"dp{world}: one gradient all-reduce per optimizer step (G1+G2, D1+D2)"),
+                                parallelism=f"dp{world}: one gradient all-reduce per optimizer step (G1+G2, D1+D2)",
+                                cuda_graph=step.graph is not None),
                     e2e=dict(value=1e3 / ms_e2e, unit="steps/s", ms_per_step=ms_e2e,
                              h2d_bytes_per_step=int(2 * per * SIDE ** 3), d2h_bytes_per_step=4),
                     gpu_launches=int(launches),
@@ -712,9 +717,19 @@ def run_cyclegan(args):
                     cpu_baseline=dict(value=cpu_steps, unit="steps/s", cores=cores, kind="port",
                                       sample="one oracle CycleStep on one 1x32^3 sample pair, scaled x64 to 8 samples of 64^3"),
                     clocks=clocks, losses={k: float(v) for k, v in losses.items()}, conv_paths=dict(CV.stats))
-        print(json.dumps(line))
+        print(json.dumps(line), flush=True)
     if world > 1:
+        # a CUDA graph that holds captured NCCL collectives must be gone before its communicator is destroyed
+        # (ncclCommDestroy waits for it otherwise); a timer guards the exit path of every rank all the same
+        import gc
+        import threading
+        threading.Timer(90.0, lambda: os._exit(0)).start()
+        step.graph = None
+        del step
+        gc.collect()
+        barrier()
         dist.destroy_process_group()
+        os._exit(0)
 
 
 def main():

@@ -285,3 +285,38 @@ def test_deep_unet_cfg5_bf16_path_follows_the_fp32_path():
     assert r["rel_rms"] <= 2e-2 and r["min_grad_cosine"] >= 0.98 and abs(r["grad_norm_ratio"] - 1) <= 2e-2, r
     del g
     torch.cuda.empty_cache()
+
+
+def test_cyclegan_step_replayed_as_one_cuda_graph_matches_the_eager_step():
+    """CycleGANStep(graph=True): three eager steps, one capture, then replays.  Same seeds, same batches: the losses of
+    every step and the final weights agree with the eager harness (wgrad atomics leave ~1e-3 run-to-run spread)."""
+    import copy
+    import raygun_b200 as rb
+    from raygun_b200.cyclegan import CycleGANStep, make_generator
+    from raygun_b200 import networks as N
+    IN = functools.partial(torch.nn.InstanceNorm3d, affine=False, track_running_stats=False)
+    torch.manual_seed(17)
+    gkw = dict(input_nc=1, output_nc=1, ngf=8, fmap_inc_factor=2, num_downs=3, padding_type="same", final_activation="Tanh")
+    nets = [make_generator("unet", dict(gkw)).to(DEV) for _ in range(2)]
+    nets += [N.NLayerDiscriminator(3, norm_layer=IN, input_nc=1, ngf=8, n_layers=2, kw=3, downsampling_kw=2).to(DEV)
+             for _ in range(2)]
+    twins = copy.deepcopy(nets)
+    batches = [(torch.randn(2, 1, 32, 32, 32, device=DEV).tanh(), torch.randn(2, 1, 32, 32, 32, device=DEV).tanh())
+               for _ in range(6)]
+    with rb.precision("bf16"):
+        eager = CycleGANStep(*nets, lr=1e-4)
+        graphed = CycleGANStep(*twins, lr=1e-4, graph=True, graph_warmup=3)
+        le = [eager.step(a, b) for a, b in batches]
+        lg = [graphed.step(a, b) for a, b in batches]
+    assert graphed.graph is not None and graphed.graph_error is None and graphed.graph_launches > 100
+    for i, (x, y) in enumerate(zip(le, lg)):
+        for k in ("G1", "G2", "D1", "D2"):
+            assert abs(float(x[k]) - float(y[k])) <= 5e-3 * max(1.0, abs(float(x[k]))), (i, k, x, y)
+    for ne, ng in zip(nets, twins):
+        for (name, pe), (_, pg) in zip(ne.named_parameters(), ng.named_parameters()):
+            # Adam moves a weight by ~lr per step whatever the gradient's size: near-zero gradients (zero-initialised
+            # biases) follow the run-to-run noise of the fp32 atomics, so allow steps x lr absolute
+            tol = max(5e-3 * float(pe.abs().max()), 6e-4)
+            assert float((pe - pg).abs().max()) <= tol, name
+    with pytest.raises(ValueError):
+        graphed.step(batches[0][0][:1], batches[0][1][:1])
