@@ -15,6 +15,10 @@
  *  - the library never allocates user-visible memory; the caller owns all tensors.
  *  - tensors are described by rg_tensor5 (logical N,C,D,H,W + element strides), so the
  *    same entry points serve NCDHW fp32 and NDHWC (channels-last-3d) bf16 storage.
+ *  - DETERMINISM: no entry point finishes a floating-point reduction with atomics.  Reducing kernels write one
+ *    partial row per block into a caller-provided fp32 workspace (`ws` / `workspace`, uninitialised device memory of
+ *    the size the matching *_workspace_bytes / rg_reduce_ws_floats query returns) and a second kernel adds the rows in
+ *    a fixed order: same inputs -> bit-identical outputs, run after run (the reference's CPU path has that property).
  */
 #ifndef RAYGUN_B200_H
 #define RAYGUN_B200_H
@@ -26,7 +30,7 @@
 extern "C" {
 #endif
 
-#define RG_VERSION 100
+#define RG_VERSION 200
 
 enum { RG_OK = 0, RG_E_BADARG = -1, RG_E_UNSUPPORTED = -2, RG_E_CUDA = -3, RG_E_ARCH = -4 };
 enum { RG_F32 = 0, RG_BF16 = 1, RG_U8 = 2 };
@@ -71,10 +75,11 @@ int rg_conv3d_direct_fprop(const rg_tensor5* xd, const void* x, const float* w, 
                            const rg_tensor5* yd, void* y, const rg_conv_geom* g, void* stream);
 int rg_conv3d_direct_dgrad(const rg_tensor5* dyd, const void* dy, const float* w, const float* bias,
                            const rg_tensor5* dxd, void* dx, const rg_conv_geom* g, void* stream);
-/* dw (fp32, [Cout,Cin/g,kD,kH,kW]) must be zeroed by the caller unless accumulate!=0;
- * dbias may be NULL. */
+/* dw (fp32, [Cout,Cin/g,kD,kH,kW]) is overwritten, or added to when accumulate != 0; dbias (may be NULL) is overwritten;
+ * ws = rg_conv3d_direct_wgrad_workspace_bytes(...) bytes (split-K partial rows). */
+size_t rg_conv3d_direct_wgrad_workspace_bytes(const rg_tensor5* xd, const rg_tensor5* dyd, const rg_conv_geom* g);
 int rg_conv3d_direct_wgrad(const rg_tensor5* xd, const void* x, const rg_tensor5* dyd, const void* dy,
-                           float* dw, float* dbias, const rg_conv_geom* g, int accumulate, void* stream);
+                           float* dw, float* dbias, const rg_conv_geom* g, int accumulate, float* ws, void* stream);
 
 /* ---- tcgen05 / TMEM / TMA implicit-GEMM convolutions (bf16 NDHWC, fp32 accumulate) --
  * The performance path for the same call sites when Cin%64==0 and Cout%16==0.
@@ -96,18 +101,20 @@ typedef struct rg_igemm_desc {
 
 int rg_plan_create(const rg_igemm_desc* desc, rg_plan** out);
 int rg_plan_destroy(rg_plan* plan);
+/* bytes of `workspace` rg_igemm_run (only when statistics are requested) / rg_igemm_wgrad need for this plan */
 size_t rg_plan_workspace_bytes(const rg_plan* plan);
 /* Re-pack fp32 checkpoint weights [Cout,Cin,kD,kH,kW] into the bf16 K-major layouts the
  * plans read: fprop pack [Cout][tap][Cin]; dgrad pack [Cin][tap][Cout].             */
 int rg_pack_weights(const float* w, int cout, int cin, int taps, void* w_fprop_bf16, void* w_dgrad_bf16,
                     void* stream);
 /* in -> out of the plan's mode.  fprop: in = x, out = y.  dgrad: in = dy, out = dx.
- * stats_sum/sumsq: fp32 [n*cout] accumulators (zeroed by caller) or NULL.           */
+ * stats_sum/sumsq: fp32 [n*cout] outputs (overwritten) or NULL; they need `workspace`. */
 int rg_igemm_run(const rg_plan* plan, const void* in, const void* w_packed, const float* bias, void* out,
                  float* stats_sum, float* stats_sqsum, void* workspace, void* stream);
-/* wgrad: dw fp32 [Cout,Cin,kD,kH,kW] (+= ; caller zeroes), dbias optional.          */
+/* wgrad: dw fp32 [Cout,Cin,kD,kH,kW] overwritten, or added to when accumulate != 0 (gradient buckets);
+ * dbias must be NULL (rg_norm_stats(kind = batch) on dy produces it).                 */
 int rg_igemm_wgrad(const rg_plan* plan, const void* x, const void* dy, float* dw, float* dbias,
-                   void* workspace, void* stream);
+                   void* workspace, int accumulate, void* stream);
 
 /* ---- slice-ring convolution (stride 1; 64-channel produced blocks; ring_conv_sm100.cu) -------------------
  * Same role as rg_igemm_run for fprop (ConvPass / ResnetGenerator3D head, UNet.py:52-87, ResNet.py:324-327) and
@@ -119,8 +126,9 @@ int rg_igemm_wgrad(const rg_plan* plan, const void* x, const void* dy, float* dw
 int rg_ring_supported(const rg_igemm_desc* desc);
 int rg_ring_config(const rg_igemm_desc* desc, int* out8);
 int rg_ring_pack_weights(const float* w, int cout, int cin, const int* kernel3, int mode, void* out_bf16, void* stream);
+size_t rg_ring_workspace_bytes(const rg_igemm_desc* desc);     /* needed only when statistics are requested */
 int rg_ring_run(const rg_igemm_desc* desc, const void* in, const void* w_ring, const float* bias, void* out,
-                float* stats_sum, float* stats_sqsum, void* stream);
+                float* stats_sum, float* stats_sqsum, void* workspace, void* stream);
 
 /* ---- small-K stem convolution (stem_conv_sm100.cu) ---------------------------------------------------------
  * Forward of a stride-1 Conv3d whose whole reduction Cin*kD*kH*kW is <= 64 (the 1 -> ngf 3^3 convolution that
@@ -152,15 +160,18 @@ int rg_upconv2_run(const rg_upconv2_desc* desc, const void* x, const void* w_pac
 /* ---- halo-resident weight gradient (stride 1; halo_wgrad_sm100.cu) ------------------------------------------
  * Same role as rg_igemm_wgrad (autograd of Conv3d, reference: torch.nn.Conv3d call sites UNet.py:69-87,
  * ResNet.py:262-327) for stride-1 layers: one X plane with its (kh,kw) halo per 128-voxel chunk serves every tap
- * of a pass through row-shifted UMMA descriptors.  desc->mode must be 2.  dw fp32 [Cout,Cin,kD,kH,kW] is
- * ACCUMULATED into (caller zeroes); workspace = rg_halo_wgrad_workspace_bytes(desc) bytes of device scratch.   */
+ * of a pass through row-shifted UMMA descriptors.  desc->mode must be 2.  dw fp32 [Cout,Cin,kD,kH,kW] is overwritten,
+ * or added to when accumulate != 0; workspace = rg_halo_wgrad_workspace_bytes(desc) bytes of device scratch (one
+ * [tap][ci][co] slab per voxel split, summed in split order).                                                   */
 int rg_halo_wgrad_supported(const rg_igemm_desc* desc);
 size_t rg_halo_wgrad_workspace_bytes(const rg_igemm_desc* desc);
-int rg_halo_wgrad(const rg_igemm_desc* desc, const void* x, const void* dy, float* dw, void* workspace, void* stream);
+int rg_halo_wgrad(const rg_igemm_desc* desc, const void* x, const void* dy, float* dw, void* workspace, int accumulate,
+                  void* stream);
 
 /* ---- 1x1x1 convolutions onto <= 4 channels (BaseSystem.py:209-224: Conv3d(ngf, output_nc, 1) + Tanh) -------
  * HBM-bound streaming kernels over a bf16 NDHWC x (Cin/8 a power of two <= 32); w fp32 [Cout][Cin].
- * fprop fuses bias + activation; wgrad accumulates into dw / dbias (caller zeroes).                     */
+ * fprop fuses bias + activation; wgrad overwrites dw (adds when accumulate != 0) and dbias, ws =
+ * rg_pw_conv_wgrad_workspace_bytes(cin, cout) bytes.                                                       */
 int rg_pw_conv_fprop(const rg_tensor5* xd, const void* x, const float* w, const float* bias, int act, float slope,
                      const rg_tensor5* yd, void* y, void* stream);
 int rg_pw_conv_dgrad(const rg_tensor5* dyd, const void* dy, const float* w, const rg_tensor5* dxd, void* dx, void* stream);
@@ -169,8 +180,9 @@ int rg_pw_conv_dgrad(const rg_tensor5* dyd, const void* dy, const float* w, cons
  * innermost (Cout % 8 == 0), w fp32 [Cout][Cin][kD][kH][kW], dx any layout / dtype.                               */
 int rg_smallcin_dgrad(const rg_tensor5* dyd, const void* dy, const float* w, const rg_tensor5* dxd, void* dx,
                       const rg_conv_geom* g, void* stream);
+size_t rg_pw_conv_wgrad_workspace_bytes(int cin, int cout);
 int rg_pw_conv_wgrad(const rg_tensor5* xd, const void* x, const rg_tensor5* dyd, const void* dy, float* dw, float* dbias,
-                     void* stream);
+                     float* ws, int accumulate, void* stream);
 
 /* ---- data movement: strided copy / cast / crop / concat-slice ------------------------
  * Replaces the reference's center `crop` + torch.cat (UNet.py:327-351), ResNet crop
@@ -204,8 +216,12 @@ int rg_pad_border_fill(const rg_tensor5* bufd, void* buf, const int32_t margin[3
 
 /* ---- normalisation (nn.InstanceNorm3d / nn.BatchNorm3d; ResNet.py:236,284,299,334,408,417;
  *      NLayerDiscriminator.py:112,146-168; UNet.py:84-88) --------------------------------
- * stats: sum[g], sqsum[g] (fp32, zeroed by caller) with g = n*C+c (instance) or c (batch). */
-int rg_norm_stats(const rg_tensor5* xd, const void* x, int kind, float* sum, float* sqsum, void* stream);
+ * stats: sum[g], sqsum[g] (fp32, overwritten) with g = n*C+c (instance) or c (batch);
+ * ws = rg_reduce_ws_floats(N, C) fp32 elements of scratch (shared by rg_norm_bwd / rg_act_bwd_bias). */
+long long rg_reduce_ws_floats(long long n, long long c);
+/* out[g] (+)= sum over r < rows of part[r * groups + g], r ascending (the second stage, for partial rows the caller owns) */
+int rg_rows_sum(const float* part, int rows, long long groups, float* out, int accumulate, void* stream);
+int rg_norm_stats(const rg_tensor5* xd, const void* x, int kind, float* sum, float* sqsum, float* ws, void* stream);
 /* mean/rstd from sum/sqsum: count elements per group, biased variance, eps inside sqrt. */
 int rg_norm_finalize(const float* sum, const float* sqsum, int groups, double count, float eps,
                      float* mean, float* rstd, float* var_out, void* stream);
@@ -216,11 +232,11 @@ int rg_norm_apply(const rg_tensor5* xd, const void* x, int kind, const float* me
                   int act, float slope, const rg_tensor5* yd, void* y, void* stream);
 /* Backward of y = act(norm(x)): needs x, dy and (for act!=NONE) y.  Two launches inside:
  * reductions (sum g, sum g*xhat per group; dgamma/dbeta) then the dx pass.
- * red: fp32 scratch [2*groups], zeroed by caller.  training=0 -> statistics are constants. */
+ * red: fp32 [2*groups] (overwritten); ws as for rg_norm_stats.  training=0 -> statistics are constants. */
 int rg_norm_bwd(const rg_tensor5* xd, const void* x, const rg_tensor5* dyd, const void* dy,
                 const rg_tensor5* yd, const void* y, int kind, int training, const float* mean,
                 const float* rstd, const float* gamma, int act, float slope, float* red,
-                float* dgamma, float* dbeta, const rg_tensor5* dxd, void* dx, void* stream);
+                float* dgamma, float* dbeta, const rg_tensor5* dxd, void* dx, float* ws, void* stream);
 
 /* ---- activations (nn.ReLU / LeakyReLU(0.2) / Tanh / Sigmoid; UNet.py:41-47,
  *      NLayerDiscriminator.py:138, BaseSystem.py:175-176) -------------------------------*/
@@ -230,11 +246,11 @@ int rg_act_fwd(const rg_tensor5* xd, const void* x, int act, float slope, const 
 int rg_act_bwd(const rg_tensor5* yd, const void* y, const rg_tensor5* dyd, const void* dy, int act,
                float slope, const rg_tensor5* dxd, void* dx, void* stream);
 
-/* dx = dy * act'(y) and bias_sum[c] += sum_{n,voxels} dx in one pass (the activation derivative and the bias gradient of
- * a Conv3d + activation layer read the same dy): dense NDHWC bf16 only (RG_E_UNSUPPORTED otherwise); bias_sum fp32 [C],
- * zeroed by the caller.                                                                                            */
+/* dx = dy * act'(y) and bias_sum[c] = sum_{n,voxels} dx in one pass (the activation derivative and the bias gradient of
+ * a Conv3d + activation layer read the same dy): dense NDHWC bf16 only (RG_E_UNSUPPORTED otherwise); bias_sum fp32 [C]
+ * (overwritten); ws = rg_reduce_ws_floats(1, C) fp32 elements.                                                     */
 int rg_act_bwd_bias(const rg_tensor5* yd, const void* y, const rg_tensor5* dyd, const void* dy, int act, float slope,
-                    const rg_tensor5* dxd, void* dx, float* bias_sum, void* stream);
+                    const rg_tensor5* dxd, void* dx, float* bias_sum, float* ws, void* stream);
 
 /* ---- pooling / nearest up-sampling (UNet.py:209-218 MaxPool3d; UNet.py:273 nn.Upsample) --*/
 int rg_maxpool3d_fwd(const rg_tensor5* xd, const void* x, const int32_t f[3], const rg_tensor5* yd, void* y,
@@ -250,11 +266,13 @@ int rg_upsample_nearest_bwd(const rg_tensor5* dyd, const void* dy, const int32_t
 
 /* ---- losses (losses/GANLoss.py:24-25,48-64 MSELoss vs constant label;
  *      losses/LinkCycleLoss.py:22,99-105 SmoothL1Loss / L1Loss), warp-shuffle reductions ----
- * loss[0] += scale_loss * mean(f(a, b|target)); grad_a = scale_grad * d mean/da (may be NULL).
- * b is ignored for MSE_CONST / MEAN (target used instead).  a,b share a logical shape.  */
+ * loss[0] = scale_loss * mean(f(a, b|target)); grad_a = scale_grad * d mean/da (may be NULL).
+ * b is ignored for MSE_CONST / MEAN (target used instead).  a,b share a logical shape.
+ * ws: RG_LOSS_WS_FLOATS fp32 elements (one partial per block).                              */
+#define RG_LOSS_WS_FLOATS 1184
 int rg_loss_fwd_grad(int kind, const rg_tensor5* ad, const void* a, const rg_tensor5* bd, const void* b,
                      float target, float beta, float scale_loss, float* loss, float scale_grad,
-                     const rg_tensor5* gd, void* grad_a, void* stream);
+                     const rg_tensor5* gd, void* grad_a, float* ws, void* stream);
 
 /* ---- blockwise prediction arithmetic (predict/worker.py:100-114 and :133-147) ---------- */
 /* y = (float(u8) - 0) / 255 * scale + shift */

@@ -24,14 +24,15 @@ E_UNSUPPORTED = -2
 # every exported symbol of include/raygun_b200.h (checked by tests/test_abi.py)
 SYMBOLS = [
     "rg_version", "rg_last_error", "rg_device_check",
-    "rg_conv3d_direct_fprop", "rg_conv3d_direct_dgrad", "rg_conv3d_direct_wgrad",
+    "rg_conv3d_direct_fprop", "rg_conv3d_direct_dgrad", "rg_conv3d_direct_wgrad", "rg_conv3d_direct_wgrad_workspace_bytes",
     "rg_plan_create", "rg_plan_destroy", "rg_plan_workspace_bytes", "rg_pack_weights",
-    "rg_igemm_run", "rg_igemm_wgrad", "rg_ring_supported", "rg_ring_config", "rg_ring_pack_weights", "rg_ring_run",
+    "rg_igemm_run", "rg_igemm_wgrad", "rg_ring_supported", "rg_ring_config", "rg_ring_pack_weights", "rg_ring_workspace_bytes",
+    "rg_ring_run",
     "rg_stem_conv_supported", "rg_stem_conv_run", "rg_upconv2_supported", "rg_upconv2_run",
     "rg_halo_wgrad_supported", "rg_halo_wgrad_workspace_bytes", "rg_halo_wgrad",
-    "rg_pw_conv_fprop", "rg_pw_conv_dgrad", "rg_pw_conv_wgrad", "rg_smallcin_dgrad",
+    "rg_pw_conv_fprop", "rg_pw_conv_dgrad", "rg_pw_conv_wgrad_workspace_bytes", "rg_pw_conv_wgrad", "rg_smallcin_dgrad",
     "rg_copy5", "rg_im2col_hw", "rg_pad3d_fwd", "rg_pad3d_bwd", "rg_pad3d_fold", "rg_pad_border_fill",
-    "rg_norm_stats", "rg_norm_finalize", "rg_norm_apply", "rg_norm_bwd",
+    "rg_reduce_ws_floats", "rg_rows_sum", "rg_norm_stats", "rg_norm_finalize", "rg_norm_apply", "rg_norm_bwd",
     "rg_act_fwd", "rg_act_bwd", "rg_act_bwd_bias",
     "rg_maxpool3d_fwd", "rg_maxpool3d_bwd", "rg_upsample_nearest_fwd", "rg_upsample_nearest_bwd",
     "rg_loss_fwd_grad", "rg_u8_normalise", "rg_denorm_clamp_u8", "rg_adam_step",
@@ -87,6 +88,10 @@ def lib():
                 l.rg_last_error.restype = C.c_char_p
                 l.rg_plan_workspace_bytes.restype = C.c_size_t
                 l.rg_halo_wgrad_workspace_bytes.restype = C.c_size_t
+                l.rg_ring_workspace_bytes.restype = C.c_size_t
+                l.rg_pw_conv_wgrad_workspace_bytes.restype = C.c_size_t
+                l.rg_conv3d_direct_wgrad_workspace_bytes.restype = C.c_size_t
+                l.rg_reduce_ws_floats.restype = C.c_longlong
                 _lib = l
     return _lib
 

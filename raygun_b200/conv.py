@@ -309,6 +309,14 @@ def ring_packed_weights(w: torch.Tensor, mode: int):
     return out
 
 
+def _stats_buffers(n_groups, nbytes, device):
+    """(stats [2][n*c] outputs, partial-row workspace) of a tensor-core convolution that also produces norm statistics."""
+    return torch.empty(2, n_groups, dtype=torch.float32, device=device), K.ws_bytes(nbytes, device)
+
+
+_ws_bytes_cache: "dict[tuple, int]" = {}
+
+
 def _sp_strides(t):
     s = t.stride()
     return (s[0], s[2], s[3], s[4])
@@ -358,12 +366,12 @@ def conv_fprop(x, w, bias, stride, pad, groups=1, act=ACT_NONE, slope=0.0, want_
                         act, float(slope))
         if rd is not None:
             wr = ring_packed_weights(w, 0)
-            st = torch.zeros(2, n * cout, dtype=torch.float32, device=x.device) if want_stats else None
+            st, sws = _stats_buffers(n * cout, lib().rg_ring_workspace_bytes(C.byref(rd)), x.device) if want_stats else (None, None)
             with _Timed("fprop", 2.0 * y.numel() * cin_t * kernel[0] * kernel[1] * kernel[2], x.device, "ring_conv_kernel"):
                 check(lib().rg_ring_run(C.byref(rd), ptr(xb), ptr(wr), ptr(bias_f), ptr(y),
-                                        ptr(st[0]) if want_stats else None, ptr(st[1]) if want_stats else None,
+                                        ptr(st[0]) if want_stats else None, ptr(st[1]) if want_stats else None, ptr(sws),
                                         stream_ptr(x.device)), "rg_ring_run(fprop)")
-            count_launch()
+            count_launch(3 if want_stats else 1)
             stats["igemm"] += 1
             stats["ring"] = stats.get("ring", 0) + 1
             return (y, st[0], st[1]) if want_stats else (y, None, None)
@@ -371,12 +379,12 @@ def conv_fprop(x, w, bias, stride, pad, groups=1, act=ACT_NONE, slope=0.0, want_
                          act, float(slope))
         if plan is not None:
             wf, _ = packed_weights(w)
-            st = torch.zeros(2, n * cout, dtype=torch.float32, device=x.device) if want_stats else None
+            st, sws = _stats_buffers(n * cout, lib().rg_plan_workspace_bytes(plan.handle), x.device) if want_stats else (None, None)
             with _Timed("fprop", 2.0 * y.numel() * cin_t * kernel[0] * kernel[1] * kernel[2], x.device):
                 check(lib().rg_igemm_run(plan.handle, ptr(xb), ptr(wf), ptr(bias_f), ptr(y),
-                                         ptr(st[0]) if want_stats else None, ptr(st[1]) if want_stats else None, None,
+                                         ptr(st[0]) if want_stats else None, ptr(st[1]) if want_stats else None, ptr(sws),
                                          stream_ptr(x.device)), "rg_igemm_run(fprop)")
-            count_launch()
+            count_launch(3 if want_stats else 1)
             stats["igemm"] += 1
             return (y, st[0], st[1]) if want_stats else (y, None, None)
     if _pw_ok(cin_t, cout, kernel, stride, pad, groups):
@@ -419,12 +427,12 @@ def conv_dgrad(dy, w, x_shape, stride, pad, groups=1, bias=None, act=ACT_NONE, s
                         _sp_strides(dyb), act, float(slope))
         if rd is not None:
             wr = ring_packed_weights(w, 1)
-            st = torch.zeros(2, n * cin_t, dtype=torch.float32, device=dy.device) if want_stats else None
+            st, sws = _stats_buffers(n * cin_t, lib().rg_ring_workspace_bytes(C.byref(rd)), dy.device) if want_stats else (None, None)
             with _Timed("dgrad", 2.0 * dyb.numel() * cin_t * kernel[0] * kernel[1] * kernel[2], dy.device, "ring_conv_kernel"):
                 check(lib().rg_ring_run(C.byref(rd), ptr(dyb), ptr(wr), ptr(bias_f), ptr(dx),
-                                        ptr(st[0]) if want_stats else None, ptr(st[1]) if want_stats else None,
+                                        ptr(st[0]) if want_stats else None, ptr(st[1]) if want_stats else None, ptr(sws),
                                         stream_ptr(dy.device)), "rg_ring_run(dgrad)")
-            count_launch()
+            count_launch(3 if want_stats else 1)
             stats["igemm"] += 1
             stats["ring"] = stats.get("ring", 0) + 1
             return (dx, st[0], st[1]) if want_stats else (dx, None, None)
@@ -432,12 +440,12 @@ def conv_dgrad(dy, w, x_shape, stride, pad, groups=1, bias=None, act=ACT_NONE, s
                          _sp_strides(dyb), act, float(slope))
         if plan is not None:
             _, wdp = packed_weights(w)
-            st = torch.zeros(2, n * cin_t, dtype=torch.float32, device=dy.device) if want_stats else None
+            st, sws = _stats_buffers(n * cin_t, lib().rg_plan_workspace_bytes(plan.handle), dy.device) if want_stats else (None, None)
             with _Timed("dgrad", 2.0 * dyb.numel() * cin_t * kernel[0] * kernel[1] * kernel[2], dy.device):
                 check(lib().rg_igemm_run(plan.handle, ptr(dyb), ptr(wdp), ptr(bias_f), ptr(dx),
-                                         ptr(st[0]) if want_stats else None, ptr(st[1]) if want_stats else None, None,
+                                         ptr(st[0]) if want_stats else None, ptr(st[1]) if want_stats else None, ptr(sws),
                                          stream_ptr(dy.device)), "rg_igemm_run(dgrad)")
-            count_launch(stride[0] * stride[1] * stride[2])
+            count_launch(stride[0] * stride[1] * stride[2] + (2 if want_stats else 0))
             stats["igemm"] += 1
             return (dx, st[0], st[1]) if want_stats else (dx, None, None)
     if (_pw_ok(cin_t, cout_t, kernel, stride, pad, groups) and bias is None and act == ACT_NONE
@@ -480,21 +488,37 @@ def conv_dgrad(dy, w, x_shape, stride, pad, groups=1, bias=None, act=ACT_NONE, s
     return dx, None, None
 
 
-def conv_wgrad(x, dy, w_shape, stride, pad, groups=1, want_bias=False, db=None):
-    """dw (fp32, conv layout) and optionally dbias = sum(dy) (`db`: already computed by the caller's activation pass)."""
+def conv_wgrad(x, dy, w_shape, stride, pad, groups=1, want_bias=False, db=None, dw_out=None, accumulate=False):
+    """dw (fp32, conv layout) and optionally dbias = sum(dy) (`db`: already computed by the caller's activation pass).
+    `dw_out`: write (or, with `accumulate`, add) the weight gradient into this fp32 tensor of shape `w_shape` -- a view of
+    a flat gradient bucket (optim.FlatAdam) -- instead of a fresh one.  Every reduction is two-stage and ordered: the result
+    is bit-reproducible."""
     require_device(x)
     cout, cin_g = w_shape[0], w_shape[1]
     kernel = tuple(w_shape[2:])
+    acc = C.c_int(int(bool(accumulate and dw_out is not None)))
+
+    def _dw():
+        if dw_out is not None:
+            if tuple(dw_out.shape) != tuple(w_shape) or dw_out.dtype != torch.float32 or not dw_out.is_contiguous():
+                raise RuntimeError("conv_wgrad: dw_out must be a contiguous fp32 tensor of the weight's shape")
+            return dw_out
+        return torch.empty(tuple(w_shape), dtype=torch.float32, device=x.device)
+
     if _igemm_ok(cin_g, cout, kernel, stride, groups) and groups == 1:
         xb, dyb = K.conv_operand(x), K.conv_operand(dy)      # strided channel-inner views (arena interiors) in place
         n = x.shape[0]
         hd = _halo_wgrad_desc(n, cin_g, cout, tuple(x.shape[2:]), tuple(dy.shape[2:]), kernel, stride, pad,
                               _sp_strides(xb), _sp_strides(dyb))
         if hd is not None:
-            dw = torch.zeros(tuple(w_shape), dtype=torch.float32, device=x.device)
-            ws = torch.empty(dw.numel(), dtype=torch.float32, device=x.device)
+            dw = _dw()
+            key = ("halo", n, cin_g, cout, tuple(x.shape[2:]), kernel, tuple(pad))
+            nb = _ws_bytes_cache.get(key)
+            if nb is None:
+                nb = _ws_bytes_cache[key] = int(lib().rg_halo_wgrad_workspace_bytes(C.byref(hd)))
+            ws = K.ws_bytes(nb, x.device)
             with _Timed("wgrad", 2.0 * dyb.numel() * cin_g * kernel[0] * kernel[1] * kernel[2], x.device, "halo_wgrad_kernel"):
-                check(lib().rg_halo_wgrad(C.byref(hd), ptr(xb), ptr(dyb), ptr(dw), ptr(ws), stream_ptr(x.device)),
+                check(lib().rg_halo_wgrad(C.byref(hd), ptr(xb), ptr(dyb), ptr(dw), ptr(ws), acc, stream_ptr(x.device)),
                       "rg_halo_wgrad")
             count_launch(2)
             stats["igemm"] += 1
@@ -504,28 +528,32 @@ def conv_wgrad(x, dy, w_shape, stride, pad, groups=1, want_bias=False, db=None):
         plan = _get_plan(2, n, cin_g, cout, tuple(x.shape[2:]), tuple(dy.shape[2:]), kernel, stride, pad,
                          _sp_strides(xb), _sp_strides(dyb), ACT_NONE, 0.0)
         if plan is not None:
-            dw = torch.zeros(tuple(w_shape), dtype=torch.float32, device=x.device)
+            dw = _dw()
+            ws = K.ws_bytes(lib().rg_plan_workspace_bytes(plan.handle), x.device)
             with _Timed("wgrad", 2.0 * dyb.numel() * cin_g * kernel[0] * kernel[1] * kernel[2], x.device, "igemm_wgrad_kernel"):
-                check(lib().rg_igemm_wgrad(plan.handle, ptr(xb), ptr(dyb), ptr(dw), None, None,
+                check(lib().rg_igemm_wgrad(plan.handle, ptr(xb), ptr(dyb), ptr(dw), None, ptr(ws), acc,
                                            stream_ptr(x.device)), "rg_igemm_wgrad")
-            count_launch()
+            count_launch(2)
             stats["igemm"] += 1
             db = (db if db is not None else K.norm_stats(dyb, _C.NORM_BATCH)[0]) if want_bias else None
             return dw, db
     if _pw_ok(cin_g, cout, kernel, stride, pad, groups):
         xb = K.conv_operand(x)
-        dw = torch.zeros(tuple(w_shape), dtype=torch.float32, device=x.device)
-        db = torch.zeros(cout, dtype=torch.float32, device=x.device) if want_bias else None
-        check(lib().rg_pw_conv_wgrad(C.byref(t5(xb)), ptr(xb), C.byref(t5(dy)), ptr(dy), ptr(dw), ptr(db),
+        dw = _dw()
+        db = torch.empty(cout, dtype=torch.float32, device=x.device) if want_bias else None
+        ws = K.ws_bytes(lib().rg_pw_conv_wgrad_workspace_bytes(C.c_int(cin_g), C.c_int(cout)), x.device)
+        check(lib().rg_pw_conv_wgrad(C.byref(t5(xb)), ptr(xb), C.byref(t5(dy)), ptr(dy), ptr(dw), ptr(db), ptr(ws), acc,
                                      stream_ptr(x.device)), "rg_pw_conv_wgrad")
-        count_launch()
+        count_launch(3 if want_bias else 2)
         stats["pointwise"] = stats.get("pointwise", 0) + 1
         return dw, db
-    dw = torch.empty(tuple(w_shape), dtype=torch.float32, device=x.device)
-    db = torch.empty(w_shape[0], dtype=torch.float32, device=x.device) if want_bias else None
     g = _geom(tuple(w_shape[2:]), stride, pad, groups)
-    check(lib().rg_conv3d_direct_wgrad(C.byref(t5(x)), ptr(x), C.byref(t5(dy)), ptr(dy), ptr(dw), ptr(db),
-                                       C.byref(g), C.c_int(0), stream_ptr(x.device)), "rg_conv3d_direct_wgrad")
-    count_launch(groups)
+    xd, dyd = t5(x), t5(dy)
+    ws = K.ws_bytes(lib().rg_conv3d_direct_wgrad_workspace_bytes(C.byref(xd), C.byref(dyd), C.byref(g)), x.device)
+    dw = _dw()
+    db = torch.empty(w_shape[0], dtype=torch.float32, device=x.device) if want_bias else None
+    check(lib().rg_conv3d_direct_wgrad(C.byref(xd), ptr(x), C.byref(dyd), ptr(dy), ptr(dw), ptr(db), C.byref(g), acc,
+                                       ptr(ws), stream_ptr(x.device)), "rg_conv3d_direct_wgrad")
+    count_launch((3 if want_bias else 2) * groups)
     stats["direct"] += 1
     return dw, db

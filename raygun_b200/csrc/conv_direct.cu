@@ -11,6 +11,7 @@
 //   wgrad: M = Cout,          N = Cin*taps, K = voxels (split-K over gridDim.z, fp32 atomics)
 // Tensors are stride-generic (NCDHW fp32 or NDHWC bf16 ...). Zero padding only (see rg_pad3d_*).
 #include "common.cuh"
+#include "reduce_rows.cuh"
 
 namespace rg {
 
@@ -160,10 +161,11 @@ __global__ void __launch_bounds__(256) direct_dgrad_kernel(ConvP p, const TG* __
   }
 }
 
-// dw[co,ci,k] += sum_{n,o} dy[n,co,o] * x[n,ci,o*s-p+k]; split-K over blockIdx.z
+// part[split][co,ci,k] = sum over the split's (n,o) of dy[n,co,o] * x[n,ci,o*s-p+k]; split-K over blockIdx.z, one
+// partial row per split (+ the bias partial behind it), added in split order by rows_sum_kernel
 template <typename TX, typename TG>
 __global__ void __launch_bounds__(256) direct_wgrad_kernel(ConvP p, const TX* __restrict__ x, const TG* __restrict__ dy,
-                                                           float* __restrict__ dw, float* __restrict__ dbias,
+                                                           float* __restrict__ part, long long ld, int want_bias,
                                                            long long k_per_split) {
   __shared__ float As[BK][BM + PADT], Bs[BK][BN + PADT];
   const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
@@ -182,7 +184,9 @@ __global__ void __launch_bounds__(256) direct_wgrad_kernel(ConvP p, const TX* __
   if (nvalid) { bci = (int)(nn_g / taps); int t = (int)(nn_g % taps); bkw = t % p.kw; t /= p.kw; bkh = t % p.kh; bkd = t / p.kh; }
   float acc[4][4] = {};
   float rowsum[4] = {0.f, 0.f, 0.f, 0.f};
-  const bool do_bias = dbias != nullptr && blockIdx.y == 0;
+  const bool do_bias = want_bias && blockIdx.y == 0;
+  float* dw = part + (long long)blockIdx.z * ld;
+  float* dbias = dw + (long long)p.cout * NN;
   for (long long k0 = kbeg; k0 < kend; k0 += BK) {
 #pragma unroll
     for (int j = 0; j < 4; ++j) {   // A: dy[vox][co]; threads fastest over vox (kk) for W-inner coalescing
@@ -230,9 +234,9 @@ __global__ void __launch_bounds__(256) direct_wgrad_kernel(ConvP p, const TX* __
     for (int j = 0; j < 4; ++j) {
       long long nn = n0 + tx * 4 + j;
       if (nn >= NN) continue;
-      atomicAdd(dw + (long long)co * NN + nn, acc[i][j]);
+      dw[(long long)co * NN + nn] = acc[i][j];
     }
-    if (do_bias && tx == 0) atomicAdd(dbias + co, rowsum[i]);
+    if (do_bias && tx == 0) dbias[co] = rowsum[i];
   }
 }
 
@@ -308,44 +312,75 @@ int rg_conv3d_direct_dgrad(const rg_tensor5* dyd, const void* dy, const float* w
   return RG_OK;
 }
 
-int rg_conv3d_direct_wgrad(const rg_tensor5* xd, const void* x, const rg_tensor5* dyd, const void* dy, float* dw,
-                           float* dbias, const rg_conv_geom* g, int accumulate, void* stream) {
-  RG_CHECK_ARG(xd && x && dyd && dy && dw && g, "rg_conv3d_direct_wgrad: null argument");
-  ConvP p;
-  int rc = fill_params(p, xd, dyd, g, "rg_conv3d_direct_wgrad");
-  if (rc) return rc;
-  cudaStream_t st = (cudaStream_t)stream;
+static long long direct_wgrad_splits(const ConvP& p, long long* kps_out) {
   const long long taps = (long long)p.kd * p.kh * p.kw;
-  const long long wcount = (long long)dyd->c * p.cin * taps;
-  if (!accumulate) {
-    cudaError_t e = cudaMemsetAsync(dw, 0, wcount * sizeof(float), st);
-    if (e != cudaSuccess) return cuda_fail(e, "rg_conv3d_direct_wgrad memset");
-    if (dbias) {
-      e = cudaMemsetAsync(dbias, 0, dyd->c * sizeof(float), st);
-      if (e != cudaSuccess) return cuda_fail(e, "rg_conv3d_direct_wgrad memset bias");
-    }
-  }
   long long Ktot = p.y.n * p.y.d * p.y.h * p.y.w;
-  if (Ktot == 0) return RG_OK;
   long long NN = (long long)p.cin * taps;
   unsigned gx = (unsigned)((p.cout + BM - 1) / BM), gy = (unsigned)((NN + BN - 1) / BN);
   long long want = (148LL * 4 + (long long)gx * gy - 1) / ((long long)gx * gy);   // ~4 blocks per SM
   long long maxsplit = (Ktot + 255) / 256;
   long long splits = want < 1 ? 1 : (want > maxsplit ? maxsplit : want);
   if (splits > 65535) splits = 65535;
+  if (splits < 1) splits = 1;
   long long kps = (Ktot + splits - 1) / splits;
   kps = (kps + BK - 1) / BK * BK;
-  splits = (Ktot + kps - 1) / kps;
+  if (kps < BK) kps = BK;
+  splits = Ktot > 0 ? (Ktot + kps - 1) / kps : 1;
+  if (kps_out) *kps_out = kps;
+  return splits;
+}
+
+size_t rg_conv3d_direct_wgrad_workspace_bytes(const rg_tensor5* xd, const rg_tensor5* dyd, const rg_conv_geom* g) {
+  if (!xd || !dyd || !g) return 0;
+  ConvP p;
+  if (fill_params(p, xd, dyd, g, "rg_conv3d_direct_wgrad_workspace_bytes")) return 0;
+  const long long taps = (long long)p.kd * p.kh * p.kw;
+  const long long ld = (long long)p.cout * p.cin * taps + p.cout;
+  return (size_t)(direct_wgrad_splits(p, nullptr) * ld * g->groups) * sizeof(float);
+}
+
+int rg_conv3d_direct_wgrad(const rg_tensor5* xd, const void* x, const rg_tensor5* dyd, const void* dy, float* dw,
+                           float* dbias, const rg_conv_geom* g, int accumulate, float* ws, void* stream) {
+  RG_CHECK_ARG(xd && x && dyd && dy && dw && g && ws, "rg_conv3d_direct_wgrad: null argument");
+  ConvP p;
+  int rc = fill_params(p, xd, dyd, g, "rg_conv3d_direct_wgrad");
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  const long long taps = (long long)p.kd * p.kh * p.kw;
+  const long long wcount_g = (long long)p.cout * p.cin * taps;
+  long long Ktot = p.y.n * p.y.d * p.y.h * p.y.w;
+  if (Ktot == 0) {
+    if (!accumulate) {
+      cudaError_t e = cudaMemsetAsync(dw, 0, wcount_g * g->groups * sizeof(float), st);
+      if (e != cudaSuccess) return cuda_fail(e, "rg_conv3d_direct_wgrad memset");
+      if (dbias) {
+        e = cudaMemsetAsync(dbias, 0, dyd->c * sizeof(float), st);
+        if (e != cudaSuccess) return cuda_fail(e, "rg_conv3d_direct_wgrad memset bias");
+      }
+    }
+    return RG_OK;
+  }
+  long long NN = (long long)p.cin * taps;
+  unsigned gx = (unsigned)((p.cout + BM - 1) / BM), gy = (unsigned)((NN + BN - 1) / BN);
+  long long kps;
+  const long long splits = direct_wgrad_splits(p, &kps);
+  const long long ld = wcount_g + p.cout;
   dim3 grid(gx, gy, (unsigned)splits);
   for (int gi = 0; gi < g->groups; ++gi) {
+    float* part = ws + (long long)gi * splits * ld;
     RG_DISPATCH_FLOAT(xd->dtype, TX, RG_DISPATCH_FLOAT(dyd->dtype, TG, {
       const TX* xg = (const TX*)x + (long long)gi * p.cin * p.x.sc;
       const TG* dyg = (const TG*)dy + (long long)gi * p.cout * p.y.sc;
-      direct_wgrad_kernel<TX, TG><<<grid, 256, 0, st>>>(p, xg, dyg, dw + (long long)gi * p.cout * p.cin * taps,
-                                                        dbias ? dbias + gi * p.cout : nullptr, kps);
+      direct_wgrad_kernel<TX, TG><<<grid, 256, 0, st>>>(p, xg, dyg, part, ld, dbias ? 1 : 0, kps);
     }))
+    RG_LAUNCH_CHECK("rg_conv3d_direct_wgrad");
+    rc = launch_rows_sum(part, (int)splits, wcount_g, ld, dw + (long long)gi * wcount_g, nullptr, wcount_g, accumulate, 1.0, st);
+    if (rc) return rc;
+    if (dbias) {      // the bias gradient is always overwritten (accumulate concerns the weight-gradient bucket only)
+      rc = launch_rows_sum(part + wcount_g, (int)splits, p.cout, ld, dbias + gi * p.cout, nullptr, p.cout, 0, 1.0, st);
+      if (rc) return rc;
+    }
   }
-  RG_LAUNCH_CHECK("rg_conv3d_direct_wgrad");
   return RG_OK;
 }
 

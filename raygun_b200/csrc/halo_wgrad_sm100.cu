@@ -8,8 +8,10 @@
 // rows, 8-voxel-group stride WB*128 B; the second tap of a pair sits LBO = (shift_b - shift_a)*128 B further), so a
 // chunk costs one ~39 KB slice + the dY tile for up to 16 taps.
 // A CTA = (pass, output-channel tile, voxel split); a pass = one kd, one 64-channel ci chunk and up to 512/BN tap
-// pairs whose accumulators fill TMEM.  Partial sums go to an fp32 workspace laid out [tap][ci][co] with 16-byte vector
-// reductions; a final kernel transposes it into the checkpoint layout [co][ci][kd][kh][kw].
+// pairs whose accumulators fill TMEM.  Every CTA STORES its partial sums (16-byte vectors, no atomics) into the slab of
+// its voxel split in an fp32 workspace laid out [split][tap][ci][co]; a final kernel adds the slabs in split order
+// (deterministic: the result is a function of the shapes only) and transposes into the checkpoint layout
+// [co][ci][kd][kh][kw].
 // Warp roles: warp 0 = TMA producer, warp 1 = MMA issuer (one elected thread), warps 2-5 = epilogue.
 #include <cuda.h>
 #include <cuda_bf16.h>
@@ -18,6 +20,7 @@
 
 #include "common.cuh"
 #include "sm100_ptx.cuh"
+#include "wgrad_finish.cuh"
 
 namespace rg {
 
@@ -39,7 +42,7 @@ struct alignas(64) HaloWgradParams {
   int kd_first, kd_step, n_kd;   // depth taps this launch covers: kd = kd_first + i*kd_step
   int dpair;                     // 1: N = {dY[d], dY[d+1]} x 64 co -> taps kd and kd-1 in one MMA (BN = 128)
   int planes;                    // out_d + dpair (the chunk walk starts one plane early when dpair)
-  float* ws;                     // [taps][cin][cout] fp32 partial sums
+  float* ws;                     // [n_splits][taps][cin][cout] fp32 partial sums
 };
 
 template <int BN>
@@ -162,7 +165,7 @@ __global__ void __launch_bounds__(HW_THREADS, 1) halo_wgrad_kernel(const __grid_
     }
     __syncwarp();
   } else {
-    // ================= epilogue: TMEM -> vector reductions into ws[tap][ci][co] =================
+    // ================= epilogue: TMEM -> vector stores into ws[split][tap][ci][co] =================
     const int quad = warp & 3;
     ptx::mbar_wait_backoff(done_bar, 0);
     ptx::tc_fence_after();
@@ -176,26 +179,30 @@ __global__ void __launch_bounds__(HW_THREADS, 1) halo_wgrad_kernel(const __grid_
         any = any || (z >= 0 && z < p.in_d);
       }
     }
-    if (any && c_end > c_begin) {
+    const bool live = any && c_end > c_begin;       // otherwise this CTA's slab entries are zero
+    {
+      float* ws_split = p.ws + (size_t)split * ((size_t)p.kd * ntaps_hw * p.cin * p.cout);
       for (int j = j_begin; j < j_end; ++j) {
         const int t = 2 * j + (quad >> 1);
         if (t >= ntaps_hw) continue;                          // unpaired second half (warp-uniform)
         const int ci = q * 64 + (quad & 1) * 32 + lane;
-        float* dst0 = p.ws + ((size_t)(kd * ntaps_hw + t) * p.cin + ci) * p.cout;
+        float* dst0 = ws_split + ((size_t)(kd * ntaps_hw + t) * p.cin + ci) * p.cout;
 #pragma unroll 1
         for (int cb = 0; cb < BN; cb += 32) {
           // dpair: columns 64..127 are the same 64 output channels against dY[d+1], i.e. depth tap kd-1
           float* dst = p.dpair ? dst0 - (size_t)(cb >> 6) * ntaps_hw * p.cin * p.cout + co_tile * 64 + (cb & 63) - cb
                                : dst0 + co_tile * BN;
           uint32_t v[32];
-          ptx::tmem_ld_32x32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)((j - j_begin) * BN + cb), v);
-          ptx::tmem_ld_wait();
+          if (live) {
+            ptx::tmem_ld_32x32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)((j - j_begin) * BN + cb), v);
+            ptx::tmem_ld_wait();
+          } else {
 #pragma unroll
-          for (int e = 0; e < 32; e += 4) {
-            asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + cb + e), "f"(__uint_as_float(v[e])),
-                         "f"(__uint_as_float(v[e + 1])), "f"(__uint_as_float(v[e + 2])), "f"(__uint_as_float(v[e + 3]))
-                         : "memory");
+            for (int e = 0; e < 32; ++e) v[e] = 0u;
           }
+#pragma unroll
+          for (int e = 0; e < 32; e += 4)
+            *reinterpret_cast<uint4*>(dst + cb + e) = make_uint4(v[e], v[e + 1], v[e + 2], v[e + 3]);
         }
       }
     }
@@ -205,22 +212,6 @@ __global__ void __launch_bounds__(HW_THREADS, 1) halo_wgrad_kernel(const __grid_
   if (warp == 1) {
     ptx::tc_fence_after();
     ptx::tmem_dealloc<512>(tmem_base);
-  }
-}
-
-// ws[tap][ci][co] -> dw[co][ci][tap]  (+=)
-__global__ void halo_wgrad_finish_kernel(const float* __restrict__ ws, int taps, int cin, int cout, float* __restrict__ dw) {
-  __shared__ float tile[32][33];
-  // grid: (ceil(cout/32), cin, ceil(taps/32)); block (32, 8)
-  const int co0 = blockIdx.x * 32, ci = blockIdx.y, t0 = blockIdx.z * 32;
-  for (int r = threadIdx.y; r < 32; r += 8) {
-    const int t = t0 + r, co = co0 + threadIdx.x;
-    tile[r][threadIdx.x] = (t < taps && co < cout) ? ws[((size_t)t * cin + ci) * cout + co] : 0.f;
-  }
-  __syncthreads();
-  for (int r = threadIdx.y; r < 32; r += 8) {
-    const int co = co0 + r, t = t0 + threadIdx.x;
-    if (co < cout && t < taps) dw[((size_t)co * cin + ci) * taps + t] += tile[threadIdx.x][r];
   }
 }
 
@@ -341,12 +332,27 @@ int rg_halo_wgrad_supported(const rg_igemm_desc* d) {
   return hw_geometry(d, &g) == RG_OK ? 1 : 0;
 }
 
-size_t rg_halo_wgrad_workspace_bytes(const rg_igemm_desc* d) {
-  if (!d) return 0;
-  return (size_t)d->cout * d->cin * d->kernel[0] * d->kernel[1] * d->kernel[2] * sizeof(float);
+static bool hw_use_dpair(const rg_igemm_desc* d) {
+  static const char* nopair = getenv("RAYGUN_B200_WGRAD_NO_DPAIR");
+  return d->cout == 64 && d->kernel[0] >= 4 &&       // (3-tap kernels: two short launches cost more than they gain)
+         !(nopair && nopair[0] == '1');
 }
 
-int rg_halo_wgrad(const rg_igemm_desc* d, const void* x, const void* dy, float* dw, void* workspace, void* stream) {
+size_t rg_halo_wgrad_workspace_bytes(const rg_igemm_desc* d) {
+  if (!d) return 0;
+  const bool dpair = hw_use_dpair(d);
+  int max_splits = 1;
+  for (int variant = dpair ? 1 : 0; variant <= (dpair ? 2 : 0); ++variant) {
+    if (variant == 2 && d->kernel[0] % 2 == 0) break;
+    HwGeom gv;
+    if (hw_geometry(d, &gv, variant)) return 0;
+    if (gv.p.n_splits > max_splits) max_splits = gv.p.n_splits;
+  }
+  return (size_t)max_splits * d->cout * d->cin * d->kernel[0] * d->kernel[1] * d->kernel[2] * sizeof(float);
+}
+
+int rg_halo_wgrad(const rg_igemm_desc* d, const void* x, const void* dy, float* dw, void* workspace, int accumulate,
+                  void* stream) {
   RG_CHECK_ARG(d && x && dy && dw && workspace, "rg_halo_wgrad: null argument");
   HwGeom g;
   int rc = hw_geometry(d, &g);
@@ -372,11 +378,9 @@ int rg_halo_wgrad(const rg_igemm_desc* d, const void* x, const void* dy, float* 
     if (r != CUDA_SUCCESS) { set_error("halo wgrad: cuTensorMapEncodeTiled failed: %d", (int)r); return RG_E_CUDA; }
   }
   const int taps = p.kd * p.kh * p.kw;
-  cudaError_t e = cudaMemsetAsync(workspace, 0, rg_halo_wgrad_workspace_bytes(d), st);
-  if (e != cudaSuccess) return cuda_fail(e, "cudaMemsetAsync(halo wgrad workspace)");
-  static const char* nopair = getenv("RAYGUN_B200_WGRAD_NO_DPAIR");
-  const bool dpair = d->cout == 64 && p.kd >= 4 &&     // (3-tap kernels: two short launches cost more than they gain)
-                     !(nopair && nopair[0] == '1');
+  const bool dpair = hw_use_dpair(d);
+  HwSplits splits;
+  for (int i = 0; i < 8; ++i) splits.of_kd[i] = 0;
   for (int variant = dpair ? 1 : 0; variant <= (dpair ? 2 : 0); ++variant) {
     if (variant == 2 && p.kd % 2 == 0) break;
     HwGeom gv;
@@ -384,6 +388,11 @@ int rg_halo_wgrad(const rg_igemm_desc* d, const void* x, const void* dy, float* 
     if (rc) return rc;
     gv.p.x_map = p.x_map; gv.p.dy_map = p.dy_map;
     gv.p.ws = (float*)workspace;
+    for (int i = 0; i < gv.p.n_kd; ++i) {       // every depth tap this launch covers is written in all of its split slabs
+      const int kd = gv.p.kd_first + i * gv.p.kd_step;
+      splits.of_kd[kd] = gv.p.n_splits;
+      if (gv.p.dpair) splits.of_kd[kd - 1] = gv.p.n_splits;
+    }
     if (gv.bn == 256) rc = hw_launch<256>(gv, st);
     else if (gv.bn == 192) rc = hw_launch<192>(gv, st);
     else if (gv.bn == 128) rc = hw_launch<128>(gv, st);
@@ -392,7 +401,8 @@ int rg_halo_wgrad(const rg_igemm_desc* d, const void* x, const void* dy, float* 
     RG_LAUNCH_CHECK("rg_halo_wgrad");
   }
   dim3 fg((d->cout + 31) / 32, d->cin, (taps + 31) / 32);
-  halo_wgrad_finish_kernel<<<fg, dim3(32, 8), 0, st>>>((const float*)workspace, taps, d->cin, d->cout, dw);
+  halo_wgrad_finish_kernel<<<fg, dim3(32, 8), 0, st>>>((const float*)workspace, splits, p.kh * p.kw, taps, d->cin, d->cout, dw,
+                                                      accumulate);
   RG_LAUNCH_CHECK("rg_halo_wgrad(finish)");
   return RG_OK;
 }

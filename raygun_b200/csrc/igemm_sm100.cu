@@ -17,6 +17,8 @@
 
 #include "common.cuh"
 #include "sm100_ptx.cuh"
+#include "reduce_rows.cuh"
+#include "wgrad_finish.cuh"
 
 namespace rg {
 
@@ -46,7 +48,8 @@ struct alignas(64) IgemmParams {
   int cout_total;
   int act; float slope;
   const float* bias;
-  float* stats_sum; float* stats_sq;
+  float* stats_part;      // partial rows [4 * gridDim.x][2 * stats_G]: row = 4 * CTA + epilogue warp, columns [0,G) sum, [G,2G) sumsq
+  long long stats_G;      // batch * cout_total
 };
 
 template <int BN> struct IgemmCfg {
@@ -171,16 +174,18 @@ __global__ void __launch_bounds__(IGEMM_THREADS, 1) igemm_conv_kernel(const __gr
 #pragma unroll
     for (int s = 0; s < NSLAB; ++s) st_acc[s][0] = st_acc[s][1] = st_acc[s][2] = st_acc[s][3] = 0.f;
     int st_n = -1, st_nt = -1;
-    const bool want_stats = p.stats_sum != nullptr;
+    const bool want_stats = p.stats_part != nullptr;
+    // no atomics: this thread is the only writer of its columns in row 4 * CTA + (et >> 5) (reduce_rows.cuh)
+    float* st_row = want_stats ? p.stats_part + ((size_t)blockIdx.x * 4 + (et >> 5)) * (size_t)(2 * p.stats_G) : nullptr;
     auto flush_stats = [&]() {
       if (!want_stats || st_n < 0) return;
 #pragma unroll
       for (int s = 0; s < NSLAB; ++s) {
         const int c = st_nt * BN + s * 64 + 2 * (et & 31);
-        float* ps = p.stats_sum + (size_t)st_n * p.cout_total + c;
-        float* pq = p.stats_sq + (size_t)st_n * p.cout_total + c;
-        atomicAdd(ps, st_acc[s][0]); atomicAdd(ps + 1, st_acc[s][1]);
-        atomicAdd(pq, st_acc[s][2]); atomicAdd(pq + 1, st_acc[s][3]);
+        float* ps = st_row + (size_t)st_n * p.cout_total + c;
+        float* pq = ps + p.stats_G;
+        ps[0] += st_acc[s][0]; ps[1] += st_acc[s][1];
+        pq[0] += st_acc[s][2]; pq[1] += st_acc[s][3];
         st_acc[s][0] = st_acc[s][1] = st_acc[s][2] = st_acc[s][3] = 0.f;
       }
     };
@@ -273,7 +278,8 @@ __global__ void __launch_bounds__(IGEMM_THREADS, 1) igemm_conv_kernel(const __gr
 //   A slab = TMA box {64 ci, tw, th, td, 1} of X shifted by one tap   (one slab per (tap, ci-chunk))
 //   B      = TMA boxes {64 co, tw, th, td, 1} of dY (loaded once per voxel chunk, shared by all slabs)
 // A CTA owns one (slab group, voxel split): all 512 TMEM columns hold 512/N accumulators of 128 x N,
-// it streams its voxel range once and finally reduces into dW with fp32 atomics.
+// it streams its voxel range once and finally stores its partial sums into the slab of its voxel split
+// (workspace [split][tap][ci][co]); halo_wgrad_finish_kernel adds the slabs in split order (wgrad_finish.cuh).
 // -------------------------------------------------------------------------------------------------
 struct alignas(64) WgradParams {
   CUtensorMap x_maps[8];
@@ -288,7 +294,7 @@ struct alignas(64) WgradParams {
   int tw, th, td;
   int n_co_tiles, n_groups, n_splits, chunks_per_split, total_chunks;
   int n_slabs;        // ntaps * cin/64
-  float* dw;          // [cout][cin][taps] fp32
+  float* ws;          // [n_splits][taps][cin][cout] fp32 partial sums
 };
 
 template <int BN> struct WgradCfg {
@@ -409,7 +415,7 @@ __global__ void __launch_bounds__(IGEMM_THREADS, 1) igemm_wgrad_kernel(const __g
     }
     __syncwarp();
   } else if (c_end > c_begin) {
-    // ================= epilogue: TMEM -> fp32 atomics into dW =================
+    // ================= epilogue: TMEM -> vector stores into ws[split][tap][ci][co] =================
     const int quad = warp & 3;
     const int taps_total = p.kdims[0] * p.kdims[1] * p.kdims[2];
     ptx::mbar_wait(done_bar, 0);
@@ -432,11 +438,10 @@ __global__ void __launch_bounds__(IGEMM_THREADS, 1) igemm_wgrad_kernel(const __g
         ptx::tmem_ld_32x32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(j * BN + cb), v);
         ptx::tmem_ld_wait();
         if (valid) {
+          float* dst = p.ws + (((size_t)split * taps_total + widx) * p.cin + ci) * p.cout + co_tile * BN + cb;
 #pragma unroll
-          for (int e = 0; e < 32; ++e) {
-            const int co = co_tile * BN + cb + e;
-            atomicAdd(p.dw + ((size_t)co * p.cin + ci) * taps_total + widx, __uint_as_float(v[e]));
-          }
+          for (int e = 0; e < 32; e += 4)
+            *reinterpret_cast<uint4*>(dst + e) = make_uint4(v[e], v[e + 1], v[e + 2], v[e + 3]);
         }
       }
     }
@@ -609,6 +614,22 @@ template <int BN> static int launch_bn(const IgemmParams& p, int grid, cudaStrea
   return RG_OK;
 }
 
+static void wgrad_split_plan(const rg_plan* pl, int* n_groups, int* n_splits, int* cps, int* total_chunks) {
+  const rg_igemm_desc& d = pl->d;
+  const Launch& L = pl->launches[0];
+  const int nacc = 512 / pl->bn;
+  const int n_slabs = pl->taps * (d.cin / 64);
+  *n_groups = (n_slabs + 2 * nacc - 1) / (2 * nacc);
+  *total_chunks = L.p.tiles_w * L.p.tiles_h * L.p.tiles_d * d.n;
+  const long long base_units = (long long)*n_groups * (d.cout / pl->bn);
+  long long splits = (2LL * num_sms() + base_units - 1) / base_units;     // ~2 waves of CTAs
+  const long long max_splits = (*total_chunks + 3) / 4;                    // >= 4 chunks per CTA
+  if (splits > max_splits) splits = max_splits;
+  if (splits < 1) splits = 1;
+  *cps = (int)((*total_chunks + splits - 1) / splits);
+  *n_splits = (*total_chunks + *cps - 1) / *cps;
+}
+
 extern "C" {
 
 int rg_plan_create(const rg_igemm_desc* d, rg_plan** out) {
@@ -696,16 +717,30 @@ int rg_plan_destroy(rg_plan* plan) {
   return RG_OK;
 }
 
-size_t rg_plan_workspace_bytes(const rg_plan* plan) { (void)plan; return 0; }
+size_t rg_plan_workspace_bytes(const rg_plan* plan) {
+  if (!plan) return 0;
+  if (plan->d.mode == 2) {
+    int ng, ns, cps, tc;
+    wgrad_split_plan(plan, &ng, &ns, &cps, &tc);
+    return (size_t)ns * plan->d.cout * plan->d.cin * plan->taps * sizeof(float);
+  }
+  // statistics partial rows: 4 epilogue warps x one CTA per SM, 2 statistics x (n * produced channels)
+  return (size_t)4 * num_sms() * 2 * plan->d.n * plan->rows * sizeof(float);
+}
 
 int rg_igemm_run(const rg_plan* pl, const void* in, const void* w_packed, const float* bias, void* outp,
                  float* stats_sum, float* stats_sqsum, void* workspace, void* stream) {
-  (void)workspace;
   RG_CHECK_ARG(pl && in && w_packed && outp, "rg_igemm_run: null argument");
   RG_CHECK_ARG(pl->d.mode != 2, "rg_igemm_run: plan was created for wgrad");
   RG_CHECK_ARG((stats_sum == nullptr) == (stats_sqsum == nullptr), "rg_igemm_run: stats pointers must come together");
+  RG_CHECK_ARG(!stats_sum || workspace, "rg_igemm_run: statistics need the plan's workspace");
   const rg_igemm_desc& d = pl->d;
   cudaStream_t st = (cudaStream_t)stream;
+  const long long stats_G = (long long)d.n * pl->rows;
+  if (stats_sum) {
+    cudaError_t e = cudaMemsetAsync(workspace, 0, rg_plan_workspace_bytes(pl), st);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaMemsetAsync(igemm statistics rows)");
+  }
   // in-side / out-side tensors of this mode
   const int64_t* in_str = d.mode == 0 ? d.x_strides : d.y_strides;
   const int64_t* out_str = d.mode == 0 ? d.y_strides : d.x_strides;
@@ -726,7 +761,7 @@ int rg_igemm_run(const rg_plan* pl, const void* in, const void* w_packed, const 
     if (rc) return rc;
     rc = encode_weight_map(&p.b_map, w_packed, (long long)pl->taps * pl->kc, pl->rows, pl->bn);
     if (rc) return rc;
-    p.bias = bias; p.stats_sum = stats_sum; p.stats_sq = stats_sqsum;
+    p.bias = bias; p.stats_part = stats_sum ? (float*)workspace : nullptr; p.stats_G = stats_G;
     const long long total = (long long)p.tiles_w * p.tiles_h * p.tiles_d * p.batch * p.n_tiles_n;
     const int grid = (int)(total < num_sms() ? total : num_sms());
     if (pl->bn == 256) rc = launch_bn<256>(p, grid, st);
@@ -736,13 +771,15 @@ int rg_igemm_run(const rg_plan* pl, const void* in, const void* w_packed, const 
     if (rc) return rc;
     RG_LAUNCH_CHECK("rg_igemm_run");
   }
+  if (stats_sum)
+    return launch_rows_sum((const float*)workspace, 4 * num_sms(), 2 * stats_G, 2 * stats_G, stats_sum, stats_sqsum, stats_G, 0,
+                           1.0, st);
   return RG_OK;
 }
 
 int rg_igemm_wgrad(const rg_plan* pl, const void* x, const void* dy, float* dw, float* dbias, void* workspace,
-                   void* stream) {
-  (void)workspace;
-  RG_CHECK_ARG(pl && x && dy && dw, "rg_igemm_wgrad: null argument");
+                   int accumulate, void* stream) {
+  RG_CHECK_ARG(pl && x && dy && dw && workspace, "rg_igemm_wgrad: null argument");
   RG_CHECK_ARG(pl->d.mode == 2, "rg_igemm_wgrad: plan was not created for wgrad");
   RG_CHECK_ARG(dbias == nullptr, "rg_igemm_wgrad: dbias is produced by rg_norm_stats(kind=batch) on dy");
   const rg_igemm_desc& d = pl->d;
@@ -769,19 +806,11 @@ int rg_igemm_wgrad(const rg_plan* pl, const void* x, const void* dy, float* dw, 
   rc = encode_act_map(&p.dy_map, dy, d.cout, d.out_dhw, d.n, d.y_strides, zero, one, L.box);
   if (rc) return rc;
   const int bn = pl->bn;
-  const int nacc = 512 / bn;
   p.n_co_tiles = d.cout / bn;
   p.n_slabs = pl->taps * (d.cin / 64);
-  p.n_groups = (p.n_slabs + 2 * nacc - 1) / (2 * nacc);
-  p.total_chunks = p.tiles_w * p.tiles_h * p.tiles_d * p.batch;
+  wgrad_split_plan(pl, &p.n_groups, &p.n_splits, &p.chunks_per_split, &p.total_chunks);
   const long long base_units = (long long)p.n_groups * p.n_co_tiles;
-  long long splits = (2LL * num_sms() + base_units - 1) / base_units;     // ~2 waves of CTAs
-  const long long max_splits = (p.total_chunks + 3) / 4;                   // >= 4 chunks per CTA
-  if (splits > max_splits) splits = max_splits;
-  if (splits < 1) splits = 1;
-  p.chunks_per_split = (int)((p.total_chunks + splits - 1) / splits);
-  p.n_splits = (p.total_chunks + p.chunks_per_split - 1) / p.chunks_per_split;
-  p.dw = dw;
+  p.ws = (float*)workspace;
   const int grid = (int)(base_units * p.n_splits);
   if (bn == 256) rc = launch_wgrad<256>(p, grid, st);
   else if (bn == 192) rc = launch_wgrad<192>(p, grid, st);
@@ -789,6 +818,12 @@ int rg_igemm_wgrad(const rg_plan* pl, const void* x, const void* dy, float* dw, 
   else rc = launch_wgrad<64>(p, grid, st);
   if (rc) return rc;
   RG_LAUNCH_CHECK("rg_igemm_wgrad");
+  HwSplits splits;
+  for (int i = 0; i < 8; ++i) splits.of_kd[i] = p.n_splits;
+  dim3 fg((d.cout + 31) / 32, d.cin, (pl->taps + 31) / 32);
+  halo_wgrad_finish_kernel<<<fg, dim3(32, 8), 0, st>>>((const float*)workspace, splits, d.kernel[1] * d.kernel[2], pl->taps, d.cin,
+                                                      d.cout, dw, accumulate);
+  RG_LAUNCH_CHECK("rg_igemm_wgrad(finish)");
   return RG_OK;
 }
 

@@ -1,6 +1,7 @@
 // InstanceNorm3d / BatchNorm3d: statistics, apply (fused activation + residual), backward.
 // HBM-bound: stats 1 read; apply 1 read + 1 write; backward = 1 reduction pass (x, dy, y) + 1 pass.
 #include "common.cuh"
+#include "reduce_rows.cuh"
 #include "vec_ndhwc.cuh"
 
 namespace rg {
@@ -13,6 +14,14 @@ struct NormCtx {
 
 __device__ __forceinline__ int group_of(int kind, long long n, long long c, long long C) {
   return kind == RG_NORM_INSTANCE ? (int)(n * C + c) : (int)c;
+}
+
+// Partial-row output of the reducing kernels (reduce_rows.cuh): block (bx, n) writes row bx (instance statistics: the
+// samples' groups are disjoint columns of one row) or row n * gridDim.x + bx (batch statistics: every sample adds to the
+// same C columns).  A row holds both statistics: columns [0, G) and [G, 2G).
+struct RedRows { float* part; long long G; int per_n; };
+__device__ __forceinline__ float* red_row(const RedRows& ro, long long n) {
+  return ro.part + ((ro.per_n ? n * (long long)gridDim.x : 0) + blockIdx.x) * (2 * ro.G);
 }
 
 }  // namespace rg
@@ -38,7 +47,7 @@ __device__ __forceinline__ void red_terms(const NormCtx& cx, int grp, const T5& 
 // W-innermost storage: blockIdx.y = (n*C+c), blockIdx.x = chunk of the D*H*W extent.
 template <int MODE, typename TX, typename TG>
 __global__ void reduce2_w_inner(NormCtx cx, T5 xd, const TX* __restrict__ x, T5 gd, const TG* __restrict__ dy, T5 yd,
-                                const TG* __restrict__ y, float* __restrict__ out0, float* __restrict__ out1) {
+                                const TG* __restrict__ y, RedRows ro) {
   long long n = blockIdx.y / xd.c, c = blockIdx.y % xd.c;
   int grp = group_of(cx.kind, n, c, xd.c);
   long long vox = xd.d * xd.h * xd.w;
@@ -60,7 +69,7 @@ __global__ void reduce2_w_inner(NormCtx cx, T5 xd, const TX* __restrict__ x, T5 
     int nw = blockDim.x >> 5;
     s0 = lane < nw ? sh0[lane] : 0.f; s1 = lane < nw ? sh1[lane] : 0.f;
     s0 = warp_sum(s0); s1 = warp_sum(s1);
-    if (lane == 0) { atomicAdd(out0 + grp, s0); atomicAdd(out1 + grp, s1); }
+    if (lane == 0) { float* row = red_row(ro, n); row[grp] = s0; row[ro.G + grp] = s1; }
   }
 }
 
@@ -69,8 +78,7 @@ __global__ void reduce2_w_inner(NormCtx cx, T5 xd, const TX* __restrict__ x, T5 
 // (block, channel).
 template <int MODE, typename TX, typename TG>
 __global__ void reduce2_c_inner(NormCtx cx, T5 xd, const TX* __restrict__ x, T5 gd, const TG* __restrict__ dy, T5 yd,
-                                const TG* __restrict__ y, float* __restrict__ out0, float* __restrict__ out1,
-                                long long vox_per_block) {
+                                const TG* __restrict__ y, RedRows ro, long long vox_per_block) {
   long long n = blockIdx.y;
   long long vox = xd.d * xd.h * xd.w;
   long long v0 = blockIdx.x * vox_per_block;
@@ -95,7 +103,8 @@ __global__ void reduce2_c_inner(NormCtx cx, T5 xd, const TX* __restrict__ x, T5 
     if (wid == 0 && c < xd.c) {
       for (int k = 1; k < nw; ++k) { s0 += sh0[k][lane]; s1 += sh1[k][lane]; }
       int grp = group_of(cx.kind, n, c, xd.c);
-      atomicAdd(out0 + grp, s0); atomicAdd(out1 + grp, s1);
+      float* row = red_row(ro, n);
+      row[grp] = s0; row[ro.G + grp] = s1;
     }
     __syncthreads();
   }
@@ -176,8 +185,8 @@ __global__ void vec_norm_bwd_dx_kernel(NormCtx cx, int training, const float* __
 template <int MODE>
 __global__ void __launch_bounds__(256) vec_reduce2_kernel(NormCtx cx, T5 xd, const __nv_bfloat16* __restrict__ x, T5 gd,
                                                           const __nv_bfloat16* __restrict__ dy, T5 yd,
-                                                          const __nv_bfloat16* __restrict__ y, float* __restrict__ out0,
-                                                          float* __restrict__ out1, long long vox_per_block) {
+                                                          const __nv_bfloat16* __restrict__ y, RedRows ro,
+                                                          long long vox_per_block) {
   const long long n = blockIdx.y;
   const long long vox = xd.d * xd.h * xd.w;
   const long long v0 = blockIdx.x * vox_per_block;
@@ -232,8 +241,9 @@ __global__ void __launch_bounds__(256) vec_reduce2_kernel(NormCtx cx, T5 xd, con
         for (int l = 0; l < lanes_v; ++l) { a += red0[threadIdx.x + ncg * l]; b += red1[threadIdx.x + ncg * l]; }
         const int c = ((cg0 + threadIdx.x) << 3) + k;
         const int grp = group_of(cx.kind, n, c, xd.c);
-        atomicAdd(out0 + grp, a);
-        atomicAdd(out1 + grp, b);
+        float* row = red_row(ro, n);
+        row[grp] = a;
+        row[ro.G + grp] = b;
       }
       __syncthreads();
     }
@@ -312,35 +322,37 @@ __global__ void affine_grad_kernel(const float* __restrict__ red, int kind, int 
 
 template <int MODE, typename TX, typename TG>
 static int launch_reduce2(const NormCtx& cx, const rg_tensor5* xd, const TX* x, const rg_tensor5* gd, const TG* dy,
-                          const rg_tensor5* yd, const TG* y, float* out0, float* out1, cudaStream_t st) {
+                          const rg_tensor5* yd, const TG* y, float* out0, float* out1, float* ws, cudaStream_t st) {
   T5 xv = view(xd), gv = gd ? view(gd) : xv, yv = yd ? view(yd) : xv;
   long long vox = xv.d * xv.h * xv.w;
+  const long long G = cx.kind == RG_NORM_INSTANCE ? xv.n * xv.c : xv.c;
+  RedRows ro{ws, G, cx.kind == RG_NORM_INSTANCE ? 0 : 1};
+  long long rows_x;
   if (dense_ok(xd, x) && dense_cg_ok(xd) && xv.n <= 65535 &&
       (MODE == 0 || (dense_ok(gd, dy) && (cx.act == RG_ACT_NONE || dense_ok(yd, y))))) {
     dim3 grid;
     DenseGeom gm = dense_geom(xd, &grid, 48);
     if (MODE) { gm.gn = gd->sn; if (yd) gm.yn = yd->sn; }
     dense_reduce2_kernel<MODE><<<grid, 256, 0, st>>>(cx, gm, (const __nv_bfloat16*)x, (const __nv_bfloat16*)dy,
-                                                     (const __nv_bfloat16*)y, out0, out1);
-    return RG_OK;
-  }
-  if (vec_ok(xd, x) && (MODE == 0 || (vec_ok(gd, dy) && (cx.act == RG_ACT_NONE || vec_ok(yd, y))))) {
+                                                     (const __nv_bfloat16*)y, ro);
+    rows_x = grid.x;
+  } else if (vec_ok(xd, x) && (MODE == 0 || (vec_ok(gd, dy) && (cx.act == RG_ACT_NONE || vec_ok(yd, y))))) {
     long long blocks_x = (148LL * 4 + xv.n - 1) / xv.n;
     long long vpb = (vox + blocks_x - 1) / blocks_x;
     if (vpb < 256) vpb = 256;
     blocks_x = (vox + vpb - 1) / vpb;
     dim3 grid((unsigned)blocks_x, (unsigned)xv.n);
     vec_reduce2_kernel<MODE><<<grid, 256, 0, st>>>(cx, xv, (const __nv_bfloat16*)x, gv, (const __nv_bfloat16*)dy, yv,
-                                                   (const __nv_bfloat16*)y, out0, out1, vpb);
-    return RG_OK;
-  }
-  if (channels_inner(xd)) {
+                                                   (const __nv_bfloat16*)y, ro, vpb);
+    rows_x = blocks_x;
+  } else if (channels_inner(xd)) {
     long long blocks_x = (148LL * 8 + xv.n - 1) / xv.n;
     long long vpb = (vox + blocks_x - 1) / blocks_x;
     if (vpb < 64) vpb = 64;
     blocks_x = (vox + vpb - 1) / vpb;
     dim3 grid((unsigned)blocks_x, (unsigned)xv.n);
-    reduce2_c_inner<MODE, TX, TG><<<grid, 256, 0, st>>>(cx, xv, x, gv, dy, yv, y, out0, out1, vpb);
+    reduce2_c_inner<MODE, TX, TG><<<grid, 256, 0, st>>>(cx, xv, x, gv, dy, yv, y, ro, vpb);
+    rows_x = blocks_x;
   } else {
     long long groups = xv.n * xv.c;
     long long bx = (148LL * 8 + groups - 1) / groups;
@@ -349,9 +361,13 @@ static int launch_reduce2(const NormCtx& cx, const rg_tensor5* xd, const TX* x, 
     if (bx < 1) bx = 1;
     RG_CHECK_ARG(groups <= 65535, "norm reduce: N*C=%lld exceeds grid.y limit", groups);
     dim3 grid((unsigned)bx, (unsigned)groups);
-    reduce2_w_inner<MODE, TX, TG><<<grid, 256, 0, st>>>(cx, xv, x, gv, dy, yv, y, out0, out1);
+    reduce2_w_inner<MODE, TX, TG><<<grid, 256, 0, st>>>(cx, xv, x, gv, dy, yv, y, ro);
+    rows_x = bx;
   }
-  return RG_OK;
+  RG_LAUNCH_CHECK("norm reduce");
+  const long long rows = ro.per_n ? rows_x * xv.n : rows_x;
+  RG_CHECK_ARG(rows * 2 * G <= red_ws_floats(xv.n, xv.c), "norm reduce: workspace bound violated (rows %lld)", rows);
+  return launch_rows_sum(ws, (int)rows, 2 * G, 2 * G, out0, out1, G, 0, 1.0, st);
 }
 
 // dx = dy * act'(y) AND sum over (n, voxels) of dx per channel in the same pass: the activation derivative and the
@@ -385,7 +401,7 @@ __global__ void __launch_bounds__(256) dense_act_bwd_sum_kernel(int act, float s
     if (threadIdx.x < cg) {
       float a = 0.f;
       for (int l = 0; l < lanes_v; ++l) a += red[threadIdx.x + cg * l];
-      atomicAdd(sums + (threadIdx.x << 3) + k, a);
+      sums[(size_t)blockIdx.x * C + (threadIdx.x << 3) + k] = a;
     }
     __syncthreads();
   }
@@ -431,7 +447,7 @@ __global__ void __launch_bounds__(256) row_act_bwd_sum_kernel(int act, float slo
     if (threadIdx.x < cg) {
       float a = 0.f;
       for (int l = 0; l < lanes_v; ++l) a += red[threadIdx.x + cg * l];
-      atomicAdd(sums + (threadIdx.x << 3) + k, a);
+      sums[(size_t)blockIdx.x * (cg << 3) + (threadIdx.x << 3) + k] = a;
     }
     __syncthreads();
   }
@@ -443,15 +459,22 @@ using namespace rg;
 
 extern "C" {
 
-int rg_norm_stats(const rg_tensor5* xd, const void* x, int kind, float* sum, float* sqsum, void* stream) {
-  RG_CHECK_ARG(xd && x && sum && sqsum, "rg_norm_stats: null argument");
+long long rg_reduce_ws_floats(long long n, long long c) { return red_ws_floats(n, c); }
+
+int rg_rows_sum(const float* part, int rows, long long groups, float* out, int accumulate, void* stream) {
+  RG_CHECK_ARG(part && out && rows >= 1 && groups >= 0, "rg_rows_sum: bad argument");
+  return launch_rows_sum(part, rows, groups, groups, out, nullptr, groups, accumulate, 1.0, (cudaStream_t)stream);
+}
+
+int rg_norm_stats(const rg_tensor5* xd, const void* x, int kind, float* sum, float* sqsum, float* ws, void* stream) {
+  RG_CHECK_ARG(xd && x && sum && sqsum && ws, "rg_norm_stats: null argument");
   RG_CHECK_ARG(kind == RG_NORM_INSTANCE || kind == RG_NORM_BATCH, "rg_norm_stats: bad kind");
   if (view(xd).numel() == 0) return RG_OK;
   NormCtx cx{kind, RG_ACT_NONE, 0.f, nullptr, nullptr, nullptr};
   cudaStream_t st = (cudaStream_t)stream;
   int rc = RG_OK;
   RG_DISPATCH_FLOAT(xd->dtype, TX, {
-    rc = launch_reduce2<0, TX, TX>(cx, xd, (const TX*)x, nullptr, nullptr, nullptr, nullptr, sum, sqsum, st);
+    rc = launch_reduce2<0, TX, TX>(cx, xd, (const TX*)x, nullptr, nullptr, nullptr, nullptr, sum, sqsum, ws, st);
   })
   if (rc) return rc;
   RG_LAUNCH_CHECK("rg_norm_stats");
@@ -507,8 +530,8 @@ int rg_norm_apply(const rg_tensor5* xd, const void* x, int kind, const float* me
 int rg_norm_bwd(const rg_tensor5* xd, const void* x, const rg_tensor5* dyd, const void* dy, const rg_tensor5* yd,
                 const void* y, int kind, int training, const float* mean, const float* rstd, const float* gamma,
                 int act, float slope, float* red, float* dgamma, float* dbeta, const rg_tensor5* dxd, void* dx,
-                void* stream) {
-  RG_CHECK_ARG(xd && x && dyd && dy && mean && rstd && red, "rg_norm_bwd: null argument");
+                float* ws, void* stream) {
+  RG_CHECK_ARG(xd && x && dyd && dy && mean && rstd && red && ws, "rg_norm_bwd: null argument");
   RG_CHECK_ARG(same_shape(xd, dyd), "rg_norm_bwd: shape mismatch");
   if (act != RG_ACT_NONE) RG_CHECK_ARG(yd && y && same_shape(xd, yd) && yd->dtype == dyd->dtype, "rg_norm_bwd: y required for fused activation");
   if (dx) RG_CHECK_ARG(dxd && same_shape(xd, dxd), "rg_norm_bwd: dx shape mismatch");
@@ -522,7 +545,7 @@ int rg_norm_bwd(const rg_tensor5* xd, const void* x, const rg_tensor5* dyd, cons
   bool need_red = training || dgamma || dbeta;
   if (need_red) {
     RG_DISPATCH_FLOAT(xd->dtype, TX, RG_DISPATCH_FLOAT(dyd->dtype, TG, {
-      rc = launch_reduce2<1, TX, TG>(cx, xd, (const TX*)x, dyd, (const TG*)dy, yd, (const TG*)y, red, red + groups, st);
+      rc = launch_reduce2<1, TX, TG>(cx, xd, (const TX*)x, dyd, (const TG*)dy, yd, (const TG*)y, red, red + groups, ws, st);
     }))
     if (rc) return rc;
     RG_LAUNCH_CHECK("rg_norm_bwd reduce");
@@ -564,8 +587,8 @@ int rg_norm_bwd(const rg_tensor5* xd, const void* x, const rg_tensor5* dyd, cons
 }
 
 int rg_act_bwd_bias(const rg_tensor5* yd, const void* y, const rg_tensor5* dyd, const void* dy, int act, float slope,
-                    const rg_tensor5* dxd, void* dx, float* bias_sum, void* stream) {
-  RG_CHECK_ARG(yd && dyd && dxd && y && dy && dx && bias_sum, "rg_act_bwd_bias: null argument");
+                    const rg_tensor5* dxd, void* dx, float* bias_sum, float* ws, void* stream) {
+  RG_CHECK_ARG(yd && dyd && dxd && y && dy && dx && bias_sum && ws, "rg_act_bwd_bias: null argument");
   RG_CHECK_ARG(same_shape(yd, dyd) && same_shape(yd, dxd), "rg_act_bwd_bias: shape mismatch");
   const long long per = yd->d * yd->h * yd->w * yd->c;
   const long long vox = yd->n * yd->d * yd->h * yd->w;
@@ -582,22 +605,22 @@ int rg_act_bwd_bias(const rg_tensor5* yd, const void* y, const rg_tensor5* dyd, 
     const long long blocks = (rows + rpb - 1) / rpb;
     row_act_bwd_sum_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(act, slope, cg, lanes_v, view(yd), view(dyd), view(dxd),
                                                                               rows, rpb, (const __nv_bfloat16*)y, (const __nv_bfloat16*)dy,
-                                                                              (__nv_bfloat16*)dx, bias_sum);
+                                                                              (__nv_bfloat16*)dx, ws);
     RG_LAUNCH_CHECK("rg_act_bwd_bias(row)");
-    return RG_OK;
+    return launch_rows_sum(ws, (int)blocks, yd->c, yd->c, bias_sum, nullptr, yd->c, 0, 1.0, (cudaStream_t)stream);
   }
   RG_UNSUPPORTED(!dense_cg_ok(yd), "rg_act_bwd_bias: needs C %% 8 == 0 and 256 %% (C/8) == 0");
   long long blocks = 148LL * 8;
   long long vpb = (vox + blocks - 1) / blocks;
-  const long long min_vpb = 48LL * lanes_v;                 // fat blocks: a fixed smem + atomics tail per block
+  const long long min_vpb = 48LL * lanes_v;                 // fat blocks: a fixed smem reduction tail per block
   if (vpb < min_vpb) vpb = min_vpb;
   vpb = (vpb + lanes_v - 1) / lanes_v * lanes_v;
   blocks = (vox + vpb - 1) / vpb;
   dense_act_bwd_sum_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(act, slope, (int)yd->c, cg, lanes_v, vox, vpb,
                                                                               (const __nv_bfloat16*)y, (const __nv_bfloat16*)dy,
-                                                                              (__nv_bfloat16*)dx, bias_sum);
+                                                                              (__nv_bfloat16*)dx, ws);
   RG_LAUNCH_CHECK("rg_act_bwd_bias");
-  return RG_OK;
+  return launch_rows_sum(ws, (int)blocks, yd->c, yd->c, bias_sum, nullptr, yd->c, 0, 1.0, (cudaStream_t)stream);
 }
 
 }  // extern "C"

@@ -138,12 +138,11 @@ __global__ void __launch_bounds__(256) dense_norm_bwd_dx_kernel(NormCtx cx, int 
   }
 }
 
-// MODE 0: (sum x, sum x^2).  MODE 1: (sum g, sum g*xhat), g = dy * act'(y).  One atomic per (block, channel).
+// MODE 0: (sum x, sum x^2).  MODE 1: (sum g, sum g*xhat), g = dy * act'(y).  One partial-row entry per (block, channel).
 template <int MODE>
 __global__ void __launch_bounds__(256) dense_reduce2_kernel(NormCtx cx, DenseGeom gm, const __nv_bfloat16* __restrict__ x,
                                                             const __nv_bfloat16* __restrict__ dy,
-                                                            const __nv_bfloat16* __restrict__ y, float* __restrict__ out0,
-                                                            float* __restrict__ out1) {
+                                                            const __nv_bfloat16* __restrict__ y, RedRows ro) {
   const int cgi = threadIdx.x % gm.cg, lv = threadIdx.x / gm.cg;
   const int c = cgi << 3, n = blockIdx.y;
   const int g0 = group_of(cx.kind, n, c, gm.C);
@@ -192,8 +191,9 @@ __global__ void __launch_bounds__(256) dense_reduce2_kernel(NormCtx cx, DenseGeo
       float a = 0.f, b = 0.f;
       for (int l = 0; l < gm.lanes_v; ++l) { a += red0[threadIdx.x + gm.cg * l]; b += red1[threadIdx.x + gm.cg * l]; }
       const int grp = group_of(cx.kind, n, (threadIdx.x << 3) + k, gm.C);
-      atomicAdd(out0 + grp, a);
-      atomicAdd(out1 + grp, b);
+      float* row = red_row(ro, n);
+      row[grp] = a;
+      row[ro.G + grp] = b;
     }
     __syncthreads();
   }

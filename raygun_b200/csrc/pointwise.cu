@@ -3,6 +3,7 @@
 // tensor, 8 channels (16 bytes) per thread.  fprop = per-voxel dot products reduced with warp shuffles;
 // dgrad = rank-Cout outer product; wgrad = reduction over all voxels (block partials + fp32 atomics).
 #include "common.cuh"
+#include "reduce_rows.cuh"
 #include "vec_ndhwc.cuh"
 
 namespace rg {
@@ -99,11 +100,12 @@ __global__ void pw_dgrad_kernel(PwW pw, T5 gd, const TG* __restrict__ dy, T5 dxd
   }
 }
 
-// dw[co][c] += sum_vox dy[vox][co] * x[vox][c];  dbias[co] += sum_vox dy[vox][co]
+// part[block][co][c] = sum over the block's voxels of dy[vox][co] * x[vox][c];  part[block][cout*cin + co] = sum dy[vox][co]
+// (one partial row per block, added in block order by rows_sum_kernel: deterministic)
 template <typename TG>
 __global__ void __launch_bounds__(256) pw_wgrad_kernel(int cin, int cout, T5 xd, const __nv_bfloat16* __restrict__ x, T5 gd,
-                                                       const TG* __restrict__ dy, float* __restrict__ dw,
-                                                       float* __restrict__ dbias, long long vox_per_block) {
+                                                       const TG* __restrict__ dy, float* __restrict__ part,
+                                                       long long vox_per_block) {
   const int cg = cin >> 3;                       // <= 32
   const int lanes_v = 256 / cg;
   const int cgi = threadIdx.x % cg, lv = threadIdx.x / cg;
@@ -146,8 +148,9 @@ __global__ void __launch_bounds__(256) pw_wgrad_kernel(int cin, int cout, T5 xd,
       if (threadIdx.x < cg) {
         float a = 0.f;
         for (int l = 0; l < lanes_v; ++l) a += red[threadIdx.x + cg * l];
-        if (k < 8) atomicAdd(dw + co * cin + (threadIdx.x << 3) + k, a);
-        else if (threadIdx.x == 0 && dbias) atomicAdd(dbias + co, a);
+        float* row = part + (size_t)blockIdx.x * (cout * (cin + 1));
+        if (k < 8) row[co * cin + (threadIdx.x << 3) + k] = a;
+        else if (threadIdx.x == 0) row[cout * cin + co] = a;
       }
       __syncthreads();
     }
@@ -267,9 +270,11 @@ int rg_pw_conv_dgrad(const rg_tensor5* dyd, const void* dy, const float* w, cons
   return RG_OK;
 }
 
+size_t rg_pw_conv_wgrad_workspace_bytes(int cin, int cout) { return (size_t)148 * 4 * cout * (cin + 1) * sizeof(float); }
+
 int rg_pw_conv_wgrad(const rg_tensor5* xd, const void* x, const rg_tensor5* dyd, const void* dy, float* dw, float* dbias,
-                     void* stream) {
-  RG_CHECK_ARG(xd && x && dyd && dy && dw, "rg_pw_conv_wgrad: null argument");
+                     float* ws, int accumulate, void* stream) {
+  RG_CHECK_ARG(xd && x && dyd && dy && dw && ws, "rg_pw_conv_wgrad: null argument");
   RG_UNSUPPORTED(!vec_ok(xd, x) || !pw_shape_ok((int)xd->c, (int)dyd->c), "rg_pw_conv_wgrad: unsupported layout / channel counts");
   RG_CHECK_ARG(xd->n == dyd->n && xd->d == dyd->d && xd->h == dyd->h && xd->w == dyd->w, "rg_pw_conv_wgrad: shape mismatch");
   long long vox = xd->n * xd->d * xd->h * xd->w;
@@ -281,10 +286,13 @@ int rg_pw_conv_wgrad(const rg_tensor5* xd, const void* x, const rg_tensor5* dyd,
   cudaStream_t st = (cudaStream_t)stream;
   RG_DISPATCH_FLOAT(dyd->dtype, TG, {
     pw_wgrad_kernel<TG><<<(unsigned)blocks, 256, 0, st>>>((int)xd->c, (int)dyd->c, view(xd), (const __nv_bfloat16*)x, view(dyd),
-                                                          (const TG*)dy, dw, dbias, vpb);
+                                                          (const TG*)dy, ws, vpb);
   })
   RG_LAUNCH_CHECK("rg_pw_conv_wgrad");
-  return RG_OK;
+  const long long nw = (long long)xd->c * dyd->c;
+  int rc = launch_rows_sum(ws, (int)blocks, nw, nw + dyd->c, dw, nullptr, nw, accumulate, 1.0, st);
+  if (rc || !dbias) return rc;
+  return launch_rows_sum(ws + nw, (int)blocks, dyd->c, nw + dyd->c, dbias, nullptr, dyd->c, 0, 1.0, st);   // bias: always overwritten
 }
 
 int rg_smallcin_dgrad(const rg_tensor5* dyd, const void* dy, const float* w, const rg_tensor5* dxd, void* dx,

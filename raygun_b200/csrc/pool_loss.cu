@@ -1,5 +1,6 @@
 // Max-pool, nearest up-sampling, loss reductions (warp-shuffle), u8 normalise / denormalise, Adam.
 #include "common.cuh"
+#include "reduce_rows.cuh"
 #include "vec_ndhwc.cuh"
 
 namespace rg {
@@ -154,7 +155,7 @@ __global__ void upsample_bwd_kernel(T5 gd, const TS* __restrict__ dy, T5 dxd, TD
 
 // ---- losses: mean reduction + gradient in one pass ------------------------------------------
 // Each thread accumulates a private fp32 partial, warp-shuffle reduce, one smem slot per warp,
-// one atomicAdd per block (grid is <= 148*8 blocks).
+// one partial per block (grid is <= 148*8 blocks) summed in block order by rows_sum_kernel (reduce_rows.cuh).
 template <typename TA, typename TB, typename TG>
 __global__ void loss_kernel(int kind, T5 ad, const TA* __restrict__ a, T5 bd, const TB* __restrict__ b, float target,
                             float beta, float scale_loss, float* __restrict__ loss, float scale_grad, T5 gd,
@@ -192,7 +193,7 @@ __global__ void loss_kernel(int kind, T5 ad, const TA* __restrict__ a, T5 bd, co
   if (wid == 0) {
     float v = lane < (blockDim.x >> 5) ? ws[lane] : 0.f;
     v = warp_sum(v);
-    if (lane == 0) atomicAdd(loss, v * inv * scale_loss);
+    if (lane == 0) loss[blockIdx.x] = v;        // `loss` = this launch's partial rows
   }
 }
 
@@ -338,8 +339,8 @@ int rg_upsample_nearest_bwd(const rg_tensor5* dyd, const void* dy, const int32_t
 
 int rg_loss_fwd_grad(int kind, const rg_tensor5* ad, const void* a, const rg_tensor5* bd, const void* b, float target,
                      float beta, float scale_loss, float* loss, float scale_grad, const rg_tensor5* gd, void* grad_a,
-                     void* stream) {
-  RG_CHECK_ARG(ad && a && loss, "rg_loss_fwd_grad: null argument");
+                     float* ws, void* stream) {
+  RG_CHECK_ARG(ad && a && loss && ws, "rg_loss_fwd_grad: null argument");
   RG_CHECK_ARG(kind >= RG_LOSS_MSE_CONST && kind <= RG_LOSS_MEAN, "rg_loss_fwd_grad: bad kind %d", kind);
   bool two = (kind == RG_LOSS_SMOOTHL1 || kind == RG_LOSS_L1);
   if (two) {
@@ -357,10 +358,10 @@ int rg_loss_fwd_grad(int kind, const rg_tensor5* ad, const void* a, const rg_ten
   int bdt = two ? bd->dtype : ad->dtype;
   int gdt = grad_a ? gd->dtype : ad->dtype;
   RG_DISPATCH_FLOAT(ad->dtype, TA, RG_DISPATCH_FLOAT(bdt, TB, RG_DISPATCH_FLOAT(gdt, TG, {
-    loss_kernel<TA, TB, TG><<<grid, 256, 0, st>>>(kind, view(ad), (const TA*)a, bv, (const TB*)b, target, beta, scale_loss, loss, scale_grad, gv, (TG*)grad_a, ci);
+    loss_kernel<TA, TB, TG><<<grid, 256, 0, st>>>(kind, view(ad), (const TA*)a, bv, (const TB*)b, target, beta, scale_loss, ws, scale_grad, gv, (TG*)grad_a, ci);
   })))
   RG_LAUNCH_CHECK("rg_loss_fwd_grad");
-  return RG_OK;
+  return launch_rows_sum(ws, grid, 1, 1, loss, nullptr, 1, 0, (double)scale_loss / (double)total, st);
 }
 
 int rg_u8_normalise(const uint8_t* x, int64_t count, float scale, float shift, int out_dtype, void* y, void* stream) {

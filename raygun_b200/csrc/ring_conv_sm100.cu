@@ -25,6 +25,7 @@
 
 #include "common.cuh"
 #include "sm100_ptx.cuh"
+#include "reduce_rows.cuh"
 
 namespace rg {
 
@@ -57,10 +58,11 @@ struct alignas(64) RingParams {
   int cout_total;
   int act; float slope;
   const float* bias;
-  float* stats_sum; float* stats_sq;
+  float* stats_part;      // partial rows [4 * gridDim.x][2 * stats_G]: row = 4 * CTA + TMEM lane quadrant (reduce_rows.cuh)
+  long long stats_G;      // batch * cout_total
 };
 
-struct RingUnit { int nt, n, h0, w0, d0, len, z_begin, z_end; };
+struct RingUnit { int nt, n, h0, w0, d0, len, z_begin, z_end, zg0; };
 
 // Work partition: the (column, output plane) space is flattened column-major and cut into gridDim.x equal ranges, so
 // every CTA does the same number of plane-taps (no wave quantisation); a range is walked as at most a few units
@@ -101,6 +103,11 @@ struct RingWalk {
     }
     r.z_begin = r.d0 - p.pd;
     r.z_end = r.d0 + r.len - 1 - p.pd + p.kd - 1;
+    // Slice groups are anchored on the ABSOLUTE plane index (group boundaries where z + pd is a multiple of S), not on the
+    // unit's first plane: the order in which an output voxel receives its (slice, chunk, tap) contributions -- hence its
+    // fp32 rounding -- is then independent of how the depth axis was cut into units, and of the read-block geometry of a
+    // blockwise prediction whenever block origins are multiples of S at this resolution level (S <= 2 by default).
+    r.zg0 = r.z_begin - (r.d0 % p.S);
     return true;
   }
 };
@@ -172,11 +179,11 @@ __global__ void __launch_bounds__(RING_THREADS, 1) ring_conv_kernel(const __grid
       int b_i = 0; uint32_t b_ph = 0;
       RingUnit r;
       for (RingWalk walk(p); walk.next(p, r);) {
-        for (int zg = r.z_begin; zg <= r.z_end; zg += p.S) {
+        for (int zg = r.zg0; zg <= r.z_end; zg += p.S) {
           for (int q = 0; q < p.q_chunks; ++q) {
             auto load_slice = [&](int s) {
               const int z = zg + s;
-              if (z > r.z_end || z < 0 || z >= p.in_d) return;
+              if (z < r.z_begin || z > r.z_end || z < 0 || z >= p.in_d) return;
               ptx::mbar_wait_backoff(aempty(a_i), a_ph ^ 1u);
               ptx::mbar_arrive_expect_tx(afull(a_i), (uint32_t)p.slice_tx);
               ptx::tma_load_5d(smem_a + (uint32_t)(a_i * p.slice_bytes), &p.a_map, afull(a_i), q * 64, r.w0 - p.pw,
@@ -234,7 +241,7 @@ __global__ void __launch_bounds__(RING_THREADS, 1) ring_conv_kernel(const __grid
       const int d0 = r.d0, d1 = d0 + r.len;
       const int z_begin = d0 - p.pd, z_end = d1 - 1 - p.pd + p.kd - 1;
       const int z_last = min(z_end, p.in_d - 1);
-      for (int zg = z_begin; zg <= z_end; zg += p.S) {
+      for (int zg = r.zg0; zg <= z_end; zg += p.S) {
         // slice zg+s: weight block i (kd = KD-1-i) feeds output plane d = dbase + i, dbase = z + pd - KD + 1, which
         // lives in accumulator block (d - d0) & 7; only planes inside [d0, d1) exist: i in [ilo, ihi)
         // Per (weight part, slice) that is at most two MMA pieces: blocks up to the end of the ring, then the rest
@@ -246,7 +253,7 @@ __global__ void __launch_bounds__(RING_THREADS, 1) ring_conv_kernel(const __grid
 #pragma unroll
         for (int s = 0; s < MAX_GS; ++s) {
           const int z = zg + s;
-          const bool valid = s < p.S && z >= 0 && z <= z_last;
+          const bool valid = s < p.S && z >= z_begin && z >= 0 && z <= z_last;
           const int dbase = z + p.pd - p.kd + 1;
           const int ilo = max(0, d0 - dbase), ihi = valid ? min(p.kd, d1 - dbase) : 0;
 #pragma unroll
@@ -335,14 +342,16 @@ __global__ void __launch_bounds__(RING_THREADS, 1) ring_conv_kernel(const __grid
     const int row = quad * 32 + lane;
     const int rh = row >> 3, rw = row & 7;
     const uint32_t t_lane = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(half * 32);
-    const bool want_stats = p.stats_sum != nullptr;
+    const bool want_stats = p.stats_part != nullptr;
+    // no atomics: this warp is the only writer of its 32 columns in row 4 * CTA + quad
+    float* st_row = want_stats ? p.stats_part + ((size_t)blockIdx.x * 4 + quad) * (size_t)(2 * p.stats_G) : nullptr;
     float st_sum = 0.f, st_sq = 0.f;          // lane l: channel half*32 + l of the current (n, channel tile)
     int st_n = -1, st_nt = -1;
     auto flush_stats = [&]() {
       if (!want_stats || st_n < 0) return;
       const size_t c = (size_t)st_n * p.cout_total + st_nt * 64 + half * 32 + lane;
-      atomicAdd(p.stats_sum + c, st_sum);
-      atomicAdd(p.stats_sq + c, st_sq);
+      st_row[c] += st_sum;
+      st_row[p.stats_G + c] += st_sq;
       st_sum = st_sq = 0.f;
     };
     int g = 0;
@@ -362,7 +371,7 @@ __global__ void __launch_bounds__(RING_THREADS, 1) ring_conv_kernel(const __grid
         }
       }
       __nv_bfloat16* ybase = p.y + (size_t)r.n * p.ys_n + (size_t)oh * p.ys_h + (size_t)ow * p.ys_w + r.nt * 64 + half * 32;
-      for (int zg = r.z_begin; zg <= r.z_end; zg += p.S) {
+      for (int zg = r.zg0; zg <= r.z_end; zg += p.S) {
         ptx::mbar_wait_backoff(tfull(g & 1), (uint32_t)((g >> 1) & 1));
         ptx::tc_fence_after();
         // planes whose last contributing slice is in this group: d = z + pd - KD + 1
@@ -521,10 +530,13 @@ static int ring_geometry(const rg_igemm_desc* d, RingGeom* g) {
   p.slice_tx = hb * p.wb * 128;
   p.slice_bytes = (p.slice_tx + 1023) & ~1023;
   p.stage_bytes = (p.kd < STAGE_KD ? p.kd : STAGE_KD) * WBLK_BYTES;
-  // slices per weight stage: prefer a configuration with one group of drain slack (2S + KD - 1 <= 8)
-  int s2 = (RING_BLOCKS - (p.kd - 1)) / 2;
-  if (s2 >= 2) { p.S = s2; p.lag = 2; } else { p.S = RING_BLOCKS - (p.kd - 1); p.lag = 1; }
-  if (p.S > 4) p.S = 4;
+  // slices per weight stage: prefer a configuration with one group of drain slack (2S + KD - 1 <= 8).  S is a power of
+  // two, 2 by default (groups are anchored on absolute plane indices: see RingWalk), RAYGUN_B200_RING_S=4 allows 4.
+  static const int s_cap = [] { const char* e = getenv("RAYGUN_B200_RING_S"); const int v = e ? atoi(e) : 2; return v >= 4 ? 4 : (v >= 2 ? 2 : 1); }();
+  p.S = RING_BLOCKS - (p.kd - 1);
+  if (p.S > s_cap) p.S = s_cap;
+  if (p.S >= 4) p.S = 4; else if (p.S >= 2) p.S = 2; else p.S = 1;
+  p.lag = (2 * p.S + p.kd - 1 <= RING_BLOCKS) ? 2 : 1;
   for (;;) {
     p.nb = 3;
     const int avail = RING_SMEM_LIMIT - 1024 - RING_TAIL_BYTES - p.nb * p.stage_bytes;
@@ -533,8 +545,8 @@ static int ring_geometry(const rg_igemm_desc* d, RingGeom* g) {
     if (na > MAX_NA) na = MAX_NA;
     if (na >= p.S + 1 || (na >= p.S && p.S == 1)) { p.na = na; break; }
     RG_UNSUPPORTED(p.S == 1, "ring conv: slice does not fit shared memory");
-    --p.S;
-    if (2 * p.S + p.kd - 1 > RING_BLOCKS) p.lag = 1;
+    p.S /= 2;
+    p.lag = (2 * p.S + p.kd - 1 <= RING_BLOCKS) ? 2 : 1;
   }
   g->smem_bytes = 1024 + p.na * p.slice_bytes + p.nb * p.stage_bytes + RING_TAIL_BYTES;
   p.tiles_h = (g->out_ext[1] + RING_TH - 1) / RING_TH;
@@ -612,10 +624,17 @@ int rg_ring_pack_weights(const float* w, int cout, int cin, const int* kernel, i
   return RG_OK;
 }
 
+size_t rg_ring_workspace_bytes(const rg_igemm_desc* d) {
+  if (!d) return 0;
+  const int rows = d->mode == 0 ? d->cout : d->cin;
+  return (size_t)4 * ring_num_sms() * 2 * d->n * rows * sizeof(float);
+}
+
 int rg_ring_run(const rg_igemm_desc* d, const void* in, const void* w_ring, const float* bias, void* out, float* stats_sum,
-                float* stats_sqsum, void* stream) {
+                float* stats_sqsum, void* workspace, void* stream) {
   RG_CHECK_ARG(d && in && w_ring && out, "rg_ring_run: null argument");
   RG_CHECK_ARG((stats_sum == nullptr) == (stats_sqsum == nullptr), "rg_ring_run: stats pointers must come together");
+  RG_CHECK_ARG(!stats_sum || workspace, "rg_ring_run: statistics need rg_ring_workspace_bytes() of workspace");
   RingGeom g;
   int rc = ring_geometry(d, &g);
   if (rc) return rc;
@@ -645,7 +664,13 @@ int rg_ring_run(const rg_igemm_desc* d, const void* in, const void* w_ring, cons
     if (r != CUDA_SUCCESS) { set_error("ring conv: cuTensorMapEncodeTiled (weights) failed: %d", (int)r); return RG_E_CUDA; }
   }
   p.y = (__nv_bfloat16*)out;
-  p.bias = bias; p.stats_sum = stats_sum; p.stats_sq = stats_sqsum;
+  p.bias = bias;
+  p.stats_part = stats_sum ? (float*)workspace : nullptr;
+  p.stats_G = (long long)d->n * g.rows;
+  if (stats_sum) {
+    cudaError_t e = cudaMemsetAsync(workspace, 0, rg_ring_workspace_bytes(d), (cudaStream_t)stream);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaMemsetAsync(ring statistics rows)");
+  }
   static int smem_set = 0;
   if (smem_set < g.smem_bytes) {
     cudaError_t e = cudaFuncSetAttribute(ring_conv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, RING_SMEM_LIMIT);
@@ -658,6 +683,9 @@ int rg_ring_run(const rg_igemm_desc* d, const void* in, const void* w_ring, cons
   const int grid = (int)(want < ring_num_sms() ? (want < 1 ? 1 : want) : ring_num_sms());
   ring_conv_kernel<<<grid, RING_THREADS, g.smem_bytes, (cudaStream_t)stream>>>(p);
   RG_LAUNCH_CHECK("rg_ring_run");
+  if (stats_sum)
+    return launch_rows_sum((const float*)workspace, 4 * ring_num_sms(), 2 * p.stats_G, 2 * p.stats_G, stats_sum, stats_sqsum,
+                           p.stats_G, 0, 1.0, (cudaStream_t)stream);
   return RG_OK;
 }
 

@@ -234,10 +234,11 @@ def act_bwd_bias(y, dy, act, slope=0.0):
     if (is_row_ndhwc(y) and is_row_ndhwc(dy) and y.shape[1] <= 2048 and 256 % (y.shape[1] // 8) == 0
             and y.shape[2] * y.shape[3] * y.shape[4] * y.shape[1] < 2 ** 31):
         dx = empty5(y.shape, y.dtype, y.device)
-        db = torch.zeros(y.shape[1], dtype=torch.float32, device=y.device)
+        db = torch.empty(y.shape[1], dtype=torch.float32, device=y.device)
+        ws = reduce_ws(1, y.shape[1], y.device)
         check(lib().rg_act_bwd_bias(C.byref(t5(y)), ptr(y), C.byref(t5(dy)), ptr(dy), C.c_int(act), C.c_float(slope),
-                                    C.byref(t5(dx)), ptr(dx), ptr(db), stream_ptr(y.device)), "rg_act_bwd_bias")
-        count_launch()
+                                    C.byref(t5(dx)), ptr(dx), ptr(db), ptr(ws), stream_ptr(y.device)), "rg_act_bwd_bias")
+        count_launch(2)
         return dx, db
     return act_bwd(y, dy, act, slope), None
 
@@ -287,14 +288,37 @@ def upsample_bwd(dy, f):
 # --------------------------------------------------------------------------------------------
 # normalisation
 # --------------------------------------------------------------------------------------------
+RED_MAX_BLOCKS = 148 * 8
+
+
+def reduce_ws(n, c, device):
+    """Uninitialised fp32 scratch for the two-stage (partial rows + ordered sum) reductions: rg_reduce_ws_floats(n, c)."""
+    return torch.empty(2 * c * (RED_MAX_BLOCKS + 2 * n + 2) + 4 * n * c + 64, dtype=torch.float32, device=device)
+
+
+def ws_bytes(nbytes, device):
+    return torch.empty(max(int(nbytes) // 4, 1), dtype=torch.float32, device=device)
+
+
+def rows_sum(part, rows, groups, out=None, accumulate=False):
+    """out[g] (+)= sum_r part[r, g] in ascending r (deterministic second stage of a caller-owned partial-row buffer)."""
+    if out is None:
+        out = torch.empty(groups, dtype=torch.float32, device=part.device)
+    check(lib().rg_rows_sum(ptr(part), C.c_int(rows), C.c_longlong(groups), ptr(out), C.c_int(int(accumulate)),
+                            stream_ptr(part.device)), "rg_rows_sum")
+    count_launch()
+    return out
+
+
 def norm_stats(x, kind):
     """sum / sum-of-squares per (n,c) [instance] or per c [batch]; fp32."""
     require_device(x)
     groups = x.shape[0] * x.shape[1] if kind == NORM_INSTANCE else x.shape[1]
-    s = torch.zeros(2, groups, dtype=torch.float32, device=x.device)
-    check(lib().rg_norm_stats(C.byref(t5(x)), ptr(x), C.c_int(kind), ptr(s[0]), ptr(s[1]), stream_ptr(x.device)),
+    s = torch.empty(2, groups, dtype=torch.float32, device=x.device)
+    ws = reduce_ws(x.shape[0], x.shape[1], x.device)
+    check(lib().rg_norm_stats(C.byref(t5(x)), ptr(x), C.c_int(kind), ptr(s[0]), ptr(s[1]), ptr(ws), stream_ptr(x.device)),
           "rg_norm_stats")
-    count_launch()
+    count_launch(2)
     return s[0], s[1]
 
 
@@ -324,15 +348,16 @@ def norm_bwd(x, dy, y, kind, training, mean, rstd, gamma, act, slope, want_affin
         dy = convert(dy, y.dtype)
     groups = mean.numel()
     c = x.shape[1]
-    red = torch.zeros(2 * groups, dtype=torch.float32, device=x.device)
+    red = torch.empty(2 * groups, dtype=torch.float32, device=x.device)
+    ws = reduce_ws(x.shape[0], c, x.device)
     dg = torch.empty(2, c, dtype=torch.float32, device=x.device) if want_affine else None
     dx = empty5(x.shape, x.dtype, x.device) if need_dx else None
     yd = C.byref(t5(y)) if y is not None else None
     check(lib().rg_norm_bwd(C.byref(t5(x)), ptr(x), C.byref(t5(dy)), ptr(dy), yd, ptr(y), C.c_int(kind),
                             C.c_int(int(training)), ptr(mean), ptr(rstd), ptr(gamma), C.c_int(act), C.c_float(slope),
                             ptr(red), ptr(dg[0]) if want_affine else None, ptr(dg[1]) if want_affine else None,
-                            C.byref(t5(dx)) if need_dx else None, ptr(dx), stream_ptr(x.device)), "rg_norm_bwd")
-    count_launch(2 if training or want_affine else 1)
+                            C.byref(t5(dx)) if need_dx else None, ptr(dx), ptr(ws), stream_ptr(x.device)), "rg_norm_bwd")
+    count_launch(3 if training or want_affine else 1)
     return dx, (dg[0] if want_affine else None), (dg[1] if want_affine else None)
 
 
@@ -342,13 +367,14 @@ def norm_bwd(x, dy, y, kind, training, mean, rstd, gamma, act, slope, want_affin
 def loss_fwd_grad(kind, a, b=None, target=0.0, beta=1.0, want_grad=True):
     """mean-reduced loss (fp32 scalar tensor) and d loss / d a (same storage as a)."""
     require_device(a)
-    loss = torch.zeros(1, dtype=torch.float32, device=a.device)
+    loss = torch.empty(1, dtype=torch.float32, device=a.device)
+    ws = torch.empty(RED_MAX_BLOCKS, dtype=torch.float32, device=a.device)
     grad = empty5(a.shape, a.dtype, a.device) if want_grad else None
     check(lib().rg_loss_fwd_grad(C.c_int(kind), C.byref(t5(a)), ptr(a), C.byref(t5(b)) if b is not None else None,
                                  ptr(b), C.c_float(target), C.c_float(beta), C.c_float(1.0), ptr(loss), C.c_float(1.0),
-                                 C.byref(t5(grad)) if want_grad else None, ptr(grad), stream_ptr(a.device)),
+                                 C.byref(t5(grad)) if want_grad else None, ptr(grad), ptr(ws), stream_ptr(a.device)),
           "rg_loss_fwd_grad")
-    count_launch()
+    count_launch(2)
     return loss[0], grad
 
 

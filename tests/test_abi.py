@@ -21,11 +21,11 @@ def test_library_builds_and_exports_every_declared_symbol():
     lib = _C.lib()
     with open(os.path.join(ROOT, "include", "raygun_b200.h")) as f:
         header = f.read()
-    declared = set(re.findall(r"^(?:int|size_t|const char\*)\s+(rg_[a-z0-9_]+)\s*\(", header, flags=re.M))
+    declared = set(re.findall(r"^(?:int|size_t|long long|const char\*)\s+(rg_[a-z0-9_]+)\s*\(", header, flags=re.M))
     assert declared == set(_C.SYMBOLS), declared ^ set(_C.SYMBOLS)
     for s in declared:
         assert hasattr(lib, s), s
-    assert lib.rg_version() == 100
+    assert lib.rg_version() == 200
 
 
 def test_sass_contains_blackwell_tensor_core_and_tma_instructions():
