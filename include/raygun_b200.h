@@ -281,10 +281,24 @@ int rg_u8_normalise(const uint8_t* x, int64_t count, float scale, float shift, i
 /* out = uint8(trunc(clamp(x*255, 0, 255))) over a cropped strided view */
 int rg_denorm_clamp_u8(const rg_tensor5* xd, const void* x, uint8_t* out, void* stream);
 
+/* Block transfers of the worker loop (predict/worker.py:100 `source.to_ndarray(block.read_roi)`, :160
+ * `destination[block.write_roi] = out`): the (d,h,w) = ext sub-block at `origin` of a uint8 (D,H,W) = vol_dhw volume
+ * <-> a dense device block, as ONE strided 3-D DMA on `stream`.  h_vol: page-locked host memory (asynchronous) or a
+ * device pointer (resident volume).  rg_d2h_block copies the sub-block at blk_origin of a dense device block of
+ * extents blk_dhw (the halo is cropped by the copy itself).                                              */
+int rg_h2d_block(const uint8_t* h_vol, const int64_t vol_dhw[3], const int64_t origin[3], const int64_t ext[3],
+                 uint8_t* d_block, void* stream);
+int rg_d2h_block(const uint8_t* d_block, const int64_t blk_dhw[3], const int64_t blk_origin[3], uint8_t* h_vol,
+                 const int64_t vol_dhw[3], const int64_t origin[3], const int64_t ext[3], void* stream);
+
 /* ---- optimiser (torch.optim.Adam call sites losses/LinkCycleLoss.py:78,128) -------------
  * One fused pass over a flat fp32 parameter bucket: m,v,p update (no amsgrad, no decay). */
 int rg_adam_step(float* p, const float* g, float* m, float* v, int64_t count, float lr, float beta1,
                  float beta2, float eps, int step, float grad_scale, void* stream);
+/* The same update with the step counter in device memory (int64; incremented first, then read): the form a captured
+ * CUDA graph can replay.  16-byte aligned buckets; grad_scale folds the 1/world of a summed all-reduce.  */
+int rg_adam_flat(float* p, const float* g, float* m, float* v, int64_t count, float lr, float beta1,
+                 float beta2, float eps, long long* step_dev, float grad_scale, void* stream);
 
 #ifdef __cplusplus
 }

@@ -58,33 +58,130 @@ def out_size(i, k, s, p):
 
 
 # --------------------------------------------------------------------------------------------
-# packed-weight and plan caches
+# derived weight tensors (bf16 packs) and plan caches
 # --------------------------------------------------------------------------------------------
-_packs: "dict[int, tuple]" = {}
+# Every tensor the tensor-core kernels read instead of the fp32 checkpoint weight -- K-major fprop / dgrad packs, slice-ring
+# packs, the stem's [Cout][64] rows, the up-convolution's [8][Cout][Cin] classes, zero-padded variants for narrow layers --
+# is a DERIVED tensor registered here per source parameter.  The buffers are persistent: a refresh re-packs INTO them, so
+#   * a captured CUDA graph keeps reading valid addresses, and the re-pack kernels recorded after the optimiser step
+#     (optim.FlatAdam.step -> repack) refresh them on every replay -- an eager forward between replays never sees stale
+#     packs;
+#   * torch-side in-place updates (load_state_dict, torch.optim, init_weights) are caught through the parameter's
+#     version counter / data pointer, and a replayed graph that updated parameters behind Python's back through
+#     `invalidate_packs()` (a global epoch that is part of every entry's validity).
+_pack_epoch = 0
 
 
-def packed_weights(w: torch.Tensor):
-    """(w_fprop [Cout][tap][Cin], w_dgrad [Cin][tap][Cout]) bf16 packs of a conv-layout weight."""
+def invalidate_packs():
+    """Mark every derived weight tensor stale (they are re-packed in place on next use)."""
+    global _pack_epoch
+    _pack_epoch += 1
+
+
+class _Derived:
+    __slots__ = ("ref", "items")
+
+    def __init__(self, w):
+        self.ref = weakref.ref(w)
+        self.items = {}          # tag -> [tensor(s), build, version, data_ptr, epoch]
+
+
+_derived: "dict[int, _Derived]" = {}
+
+
+def derived(w: torch.Tensor, tag, build):
+    """The tensor(s) `build(w, out)` derives from parameter `w` (out = None: allocate; else refresh in place), cached until
+    `w` changes."""
     key = id(w)
-    ent = _packs.get(key)
-    ver = w._version
-    if ent is not None and ent[0]() is w and ent[1] == ver and ent[2] == w.data_ptr():
-        return ent[3], ent[4]
-    cout, cin = w.shape[0], w.shape[1]
-    taps = w.shape[2] * w.shape[3] * w.shape[4]
-    wsrc = w.detach()
-    if not wsrc.is_contiguous():
-        wsrc = wsrc.contiguous()
-    wf = torch.empty(cout, taps, cin, dtype=torch.bfloat16, device=w.device)
-    wd = torch.empty(cin, taps, cout, dtype=torch.bfloat16, device=w.device)
-    check(lib().rg_pack_weights(ptr(wsrc), C.c_int(cout), C.c_int(cin), C.c_int(taps), ptr(wf), ptr(wd),
-                                stream_ptr(w.device)), "rg_pack_weights")
-    count_launch()
-    if len(_packs) > 4096:
-        for k in [k for k, e in _packs.items() if e[0]() is None]:
-            del _packs[k]
-    _packs[key] = (weakref.ref(w), ver, w.data_ptr(), wf, wd)
-    return wf, wd
+    ent = _derived.get(key)
+    if ent is None or ent.ref() is not w:
+        for k in [k for k, e in _derived.items() if e.ref() is None]:      # purge dead entries on every insert
+            del _derived[k]
+        ent = _derived[key] = _Derived(w)
+    it = ent.items.get(tag)
+    ver, dptr = w._version, w.data_ptr()
+    if it is not None and it[2] == ver and it[3] == dptr and it[4] == _pack_epoch:
+        return it[0]
+    out = build(w, it[0] if it is not None else None)
+    ent.items[tag] = [out, build, ver, dptr, _pack_epoch]
+    return out
+
+
+def repack(params):
+    """Refresh, in place, every derived tensor of `params` (called by the optimiser right after it updated the fp32
+    weights through the C ABI, which does not touch Python's version counters)."""
+    n = 0
+    for w in params:
+        ent = _derived.get(id(w))
+        if ent is None or ent.ref() is not w:
+            continue
+        for it in ent.items.values():
+            it[0] = it[1](w, it[0])
+            it[2], it[3], it[4] = w._version, w.data_ptr(), _pack_epoch
+            n += 1
+    return n
+
+
+def _contig(w):
+    w = w.detach()
+    return w if w.is_contiguous() else w.contiguous()
+
+
+def _pad_rows(w, rows):
+    """w [Cout, ...] zero-padded to `rows` output channels (narrow layers run on the tensor cores with padded channels)."""
+    wp = torch.zeros(rows, *w.shape[1:], dtype=torch.float32, device=w.device)
+    wp[: w.shape[0]] = w.detach()
+    return wp
+
+
+def _pad_cin(w, cin):
+    wp = torch.zeros(w.shape[0], cin, *w.shape[2:], dtype=torch.float32, device=w.device)
+    wp[:, : w.shape[1]] = w.detach()
+    return wp
+
+
+class WeightSrc:
+    """A convolution weight as the kernels see it: `param` (the fp32 checkpoint tensor the packs are cached under), an
+    optional transform `fn` (zero-padding of channels, the stem's H/W-tap fold) with the resulting `shape`, and `tag`,
+    which names the transform in the cache.  Plain parameters are wrapped as WeightSrc(param)."""
+    __slots__ = ("param", "fn", "shape", "tag")
+
+    def __init__(self, param, fn=None, shape=None, tag=""):
+        self.param, self.fn, self.tag = param, fn, tag
+        self.shape = tuple(shape) if shape is not None else tuple(param.shape)
+
+    def fp32(self):
+        return _fp32_of(self.param, self.fn)
+
+    @property
+    def device(self):
+        return self.param.device
+
+
+def _fp32_of(param, fn):
+    return _contig(param) if fn is None else fn(param).contiguous()
+
+
+def _src(w):
+    return w if isinstance(w, WeightSrc) else WeightSrc(w)
+
+
+def packed_weights(w):
+    """(w_fprop [Cout][tap][Cin], w_dgrad [Cin][tap][Cout]) bf16 packs of a conv-layout weight."""
+    ws = _src(w)
+    cout, cin = ws.shape[0], ws.shape[1]
+    taps = ws.shape[2] * ws.shape[3] * ws.shape[4]
+    fn = ws.fn           # the builders must not hold the parameter itself (the registry keeps them; entries die with it)
+
+    def build(p_, out):
+        wf, wd = out if out is not None else (torch.empty(cout, taps, cin, dtype=torch.bfloat16, device=p_.device),
+                                              torch.empty(cin, taps, cout, dtype=torch.bfloat16, device=p_.device))
+        check(lib().rg_pack_weights(ptr(_fp32_of(p_, fn)), C.c_int(cout), C.c_int(cin), C.c_int(taps), ptr(wf), ptr(wd),
+                                    stream_ptr(p_.device)), "rg_pack_weights")
+        count_launch()
+        return wf, wd
+
+    return derived(ws.param, ("igemm", ws.tag), build)
 
 
 class _Plan:
@@ -133,7 +230,6 @@ def _get_plan(mode, n, cin, cout, in_dhw, out_dhw, kernel, stride, pad, xs, ys, 
 import os
 
 _ring_descs: "dict[tuple, IgemmDesc | None]" = {}
-_ring_packs: "dict[tuple, tuple]" = {}
 RING_MAX_PRODUCED = int(os.environ.get("RAYGUN_B200_RING_MAX_PRODUCED", "192"))   # 0 disables the ring kernel
 
 
@@ -161,7 +257,6 @@ def _ring_desc(mode, n, cin, cout, in_dhw, out_dhw, kernel, stride, pad, xs, ys,
 
 
 STEM_DIRECT = os.environ.get("RAYGUN_B200_STEM_DIRECT", "1") != "0"
-_stem_packs: "dict[int, tuple]" = {}
 
 
 def stem_direct_ok(w, want_stats):
@@ -187,14 +282,12 @@ def stem_conv_fprop(x, w, bias, pad, act=ACT_NONE, slope=0.0, out=None):
         y = K.empty5_arena((n, cout, *od), torch.bfloat16, x.device)
     else:
         y = K.empty5((n, cout, *od), torch.bfloat16, x.device)
-    ent = _stem_packs.get(id(w))
-    if ent is None or ent[0]() is not w or ent[1] != w._version or ent[2] != w.data_ptr():
-        w64 = torch.zeros(cout, 64, dtype=torch.bfloat16, device=w.device)
-        w64[:, : cin * kernel[0] * kernel[1] * kernel[2]] = w.detach().reshape(cout, -1).to(torch.bfloat16)
-        if len(_stem_packs) > 256:
-            for k in [k for k, e in _stem_packs.items() if e[0]() is None]:
-                del _stem_packs[k]
-        _stem_packs[id(w)] = ent = (weakref.ref(w), w._version, w.data_ptr(), w64)
+    def build(p_, out):
+        w64 = out if out is not None else torch.zeros(cout, 64, dtype=torch.bfloat16, device=p_.device)
+        w64[:, : cin * kernel[0] * kernel[1] * kernel[2]] = p_.detach().reshape(cout, -1)
+        return w64
+
+    w64 = derived(w, "stem64", build)
     d_ = IgemmDesc()
     d_.mode, d_.n, d_.cin, d_.cout = 0, n, cin, cout
     d_.in_dhw[:] = [d, h, wd_]
@@ -208,7 +301,7 @@ def stem_conv_fprop(x, w, bias, pad, act=ACT_NONE, slope=0.0, out=None):
     d_.has_bias = 1 if bias is not None else 0
     bias_f = bias.detach().float().contiguous() if bias is not None else None
     with _Timed("fprop", 2.0 * y.numel() * cin * kernel[0] * kernel[1] * kernel[2], x.device, "stem_conv_kernel"):
-        check(lib().rg_stem_conv_run(C.byref(d_), ptr(xb), C.c_longlong(xb.stride(1)), ptr(ent[3]), ptr(bias_f), ptr(y),
+        check(lib().rg_stem_conv_run(C.byref(d_), ptr(xb), C.c_longlong(xb.stride(1)), ptr(w64), ptr(bias_f), ptr(y),
                                      stream_ptr(x.device)), "rg_stem_conv_run")
     count_launch()
     stats["stem_direct"] = stats.get("stem_direct", 0) + 1
@@ -216,7 +309,6 @@ def stem_conv_fprop(x, w, bias, pad, act=ACT_NONE, slope=0.0, out=None):
 
 
 UPCONV2 = os.environ.get("RAYGUN_B200_UPCONV2", "1") != "0"
-_up_packs: "dict[int, tuple]" = {}
 
 
 def upconv2_ok(x, w, stride, pad, out_pad, want_stats):
@@ -240,13 +332,12 @@ def upconv2_fprop(x, w, bias, act=ACT_NONE, slope=0.0, out=None):
         y = K.empty5_arena(shape, torch.bfloat16, x.device)
     else:
         y = K.empty5(shape, torch.bfloat16, x.device)
-    ent = _up_packs.get(id(w))
-    if ent is None or ent[0]() is not w or ent[1] != w._version or ent[2] != w.data_ptr():
-        wp = w.detach().permute(2, 3, 4, 1, 0).reshape(8 * cout, cin).to(torch.bfloat16).contiguous()
-        if len(_up_packs) > 256:
-            for k in [k for k, e in _up_packs.items() if e[0]() is None]:
-                del _up_packs[k]
-        _up_packs[id(w)] = ent = (weakref.ref(w), w._version, w.data_ptr(), wp)
+    def build(p_, out):
+        wp = out if out is not None else torch.empty(8 * cout, cin, dtype=torch.bfloat16, device=p_.device)
+        wp.view(2, 2, 2, cout, cin).copy_(p_.detach().permute(2, 3, 4, 1, 0))
+        return wp
+
+    wpk = derived(w, "upconv2", build)
     d_ = Upconv2Desc()
     d_.n, d_.cin, d_.cout = n, cin, cout
     d_.in_dhw[:] = [d, h, wd_]
@@ -256,7 +347,7 @@ def upconv2_fprop(x, w, bias, act=ACT_NONE, slope=0.0, out=None):
     d_.has_bias = 1 if bias is not None else 0
     bias_f = bias.detach().float().contiguous() if bias is not None else None
     with _Timed("fprop", 2.0 * xb.numel() * cout * 8, x.device, "upconv2_kernel"):
-        check(lib().rg_upconv2_run(C.byref(d_), ptr(xb), ptr(ent[3]), ptr(bias_f), ptr(y), stream_ptr(x.device)),
+        check(lib().rg_upconv2_run(C.byref(d_), ptr(xb), ptr(wpk), ptr(bias_f), ptr(y), stream_ptr(x.device)),
               "rg_upconv2_run")
     count_launch()
     stats["upconv2"] = stats.get("upconv2", 0) + 1
@@ -288,25 +379,20 @@ def _halo_wgrad_desc(n, cin, cout, in_dhw, out_dhw, kernel, stride, pad, xs, ys)
     return _halo_descs[key]
 
 
-def ring_packed_weights(w: torch.Tensor, mode: int):
-    """bf16 slice-ring pack of a conv-layout weight for fprop (mode 0) or dgrad (mode 1); cached per version."""
-    key = (id(w), mode)
-    ent = _ring_packs.get(key)
-    ver = w._version
-    if ent is not None and ent[0]() is w and ent[1] == ver and ent[2] == w.data_ptr():
-        return ent[3]
-    wsrc = w.detach()
-    if not wsrc.is_contiguous():
-        wsrc = wsrc.contiguous()
-    out = torch.empty(w.numel(), dtype=torch.bfloat16, device=w.device)
-    check(lib().rg_ring_pack_weights(ptr(wsrc), C.c_int(w.shape[0]), C.c_int(w.shape[1]), i3(w.shape[2:]), C.c_int(mode),
-                                     ptr(out), stream_ptr(w.device)), "rg_ring_pack_weights")
-    count_launch()
-    if len(_ring_packs) > 4096:
-        for k in [k for k, e in _ring_packs.items() if e[0]() is None]:
-            del _ring_packs[k]
-    _ring_packs[key] = (weakref.ref(w), ver, w.data_ptr(), out)
-    return out
+def ring_packed_weights(w, mode: int):
+    """bf16 slice-ring pack of a conv-layout weight for fprop (mode 0) or dgrad (mode 1); persistent, refreshed in place."""
+    ws = _src(w)
+    shape, fn = ws.shape, ws.fn
+
+    def build(p_, out):
+        out = out if out is not None else torch.empty(shape[0] * shape[1] * shape[2] * shape[3] * shape[4],
+                                                      dtype=torch.bfloat16, device=p_.device)
+        check(lib().rg_ring_pack_weights(ptr(_fp32_of(p_, fn)), C.c_int(shape[0]), C.c_int(shape[1]), i3(shape[2:]), C.c_int(mode),
+                                         ptr(out), stream_ptr(p_.device)), "rg_ring_pack_weights")
+        count_launch()
+        return out
+
+    return derived(ws.param, ("ring", mode, ws.tag), build)
 
 
 def _stats_buffers(n_groups, nbytes, device):
@@ -390,16 +476,14 @@ def conv_fprop(x, w, bias, stride, pad, groups=1, act=ACT_NONE, slope=0.0, want_
     if _pw_ok(cin_t, cout, kernel, stride, pad, groups):
         xb = K.conv_operand(x)
         y = _alloc(cdt)
-        check(lib().rg_pw_conv_fprop(C.byref(t5(xb)), ptr(xb), ptr(w.detach().contiguous()), ptr(bias_f), C.c_int(act),
+        check(lib().rg_pw_conv_fprop(C.byref(t5(xb)), ptr(xb), ptr(_src(w).fp32()), ptr(bias_f), C.c_int(act),
                                      C.c_float(slope), C.byref(t5(y)), ptr(y), stream_ptr(x.device)), "rg_pw_conv_fprop")
         count_launch()
         stats["pointwise"] = stats.get("pointwise", 0) + 1
         return y, None, None
     y = _alloc(cdt)
     g = _geom(kernel, stride, pad, groups, act, slope)
-    wc = w.detach()
-    if not wc.is_contiguous():
-        wc = wc.contiguous()
+    wc = _src(w).fp32()
     check(lib().rg_conv3d_direct_fprop(C.byref(t5(x)), ptr(x), ptr(wc), ptr(bias_f), C.byref(t5(y)), ptr(y),
                                        C.byref(g), stream_ptr(x.device)), "rg_conv3d_direct_fprop")
     count_launch(groups)
@@ -451,7 +535,7 @@ def conv_dgrad(dy, w, x_shape, stride, pad, groups=1, bias=None, act=ACT_NONE, s
     if (_pw_ok(cin_t, cout_t, kernel, stride, pad, groups) and bias is None and act == ACT_NONE
             and cdt == torch.bfloat16):
         dx = K.empty5(tuple(x_shape), torch.bfloat16, dy.device)
-        check(lib().rg_pw_conv_dgrad(C.byref(t5(dy)), ptr(dy), ptr(w.detach().contiguous()), C.byref(t5(dx)), ptr(dx),
+        check(lib().rg_pw_conv_dgrad(C.byref(t5(dy)), ptr(dy), ptr(_src(w).fp32()), C.byref(t5(dx)), ptr(dx),
                                      stream_ptr(dy.device)), "rg_pw_conv_dgrad")
         count_launch()
         stats["pointwise"] = stats.get("pointwise", 0) + 1
@@ -461,8 +545,10 @@ def conv_dgrad(dy, w, x_shape, stride, pad, groups=1, bias=None, act=ACT_NONE, s
             and _igemm_ok(64, cout_t, kernel, stride, groups)):
         # few input channels, many taps (the U-Net stem under a cycle loss, UNet.py:52-87): tensor cores with the
         # produced channels zero-padded to 64 instead of streaming Cout * taps values per voxel
-        wp = torch.zeros(cout_t, 64, *kernel, dtype=w.dtype, device=w.device)
-        wp[:, :cin_t] = w.detach()
+        base = _src(w)
+        inner = base.fn
+        wp = WeightSrc(base.param, (lambda p_: _pad_cin(inner(p_) if inner else p_, 64)), (cout_t, 64, *kernel),
+                       base.tag + "+cin64")
         dxp, _, _ = conv_dgrad(dy, wp, (n, 64, *x_shape[2:]), stride, pad, groups, out_dtype=torch.bfloat16)
         dx = K.copy_into(K.empty5(tuple(x_shape), cdt, dy.device), dxp[:, :cin_t])
         return dx, None, None
@@ -470,7 +556,7 @@ def conv_dgrad(dy, w, x_shape, stride, pad, groups=1, bias=None, act=ACT_NONE, s
             and cin_t * cout_t * kernel[0] * kernel[1] * kernel[2] * 4 <= 48 * 1024):
         # few input channels (discriminator stem under the generator loss): streaming kernel instead of the tiled GEMM
         dx = K.empty5(tuple(x_shape), cdt, dy.device)
-        wc = w.detach().float().contiguous()
+        wc = _src(w).fp32()
         check(lib().rg_smallcin_dgrad(C.byref(t5(dy)), ptr(dy), ptr(wc), C.byref(t5(dx)), ptr(dx),
                                       C.byref(_geom(kernel, stride, pad, groups)), stream_ptr(dy.device)), "rg_smallcin_dgrad")
         count_launch()
@@ -478,9 +564,7 @@ def conv_dgrad(dy, w, x_shape, stride, pad, groups=1, bias=None, act=ACT_NONE, s
         return dx, None, None
     dx = K.empty5(tuple(x_shape), cdt, dy.device)
     g = _geom(kernel, stride, pad, groups, act, slope)
-    wc = w.detach()
-    if not wc.is_contiguous():
-        wc = wc.contiguous()
+    wc = _src(w).fp32()
     check(lib().rg_conv3d_direct_dgrad(C.byref(t5(dy)), ptr(dy), ptr(wc), ptr(bias_f), C.byref(t5(dx)), ptr(dx),
                                        C.byref(g), stream_ptr(dy.device)), "rg_conv3d_direct_dgrad")
     count_launch(groups)

@@ -239,6 +239,42 @@ __global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, 
   }
 }
 
+// Same update over a flat bucket with the step counter ON THE DEVICE (a captured CUDA graph replays with frozen kernel
+// arguments: the bias corrections must come from memory).  step_dev[0] is incremented by adam_step_inc_kernel first.
+__global__ void adam_step_inc_kernel(long long* step_dev) { step_dev[0] += 1; }
+
+__global__ void adam_flat_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
+                                 float* __restrict__ v, long long count, float lr, float b1, float b2, float eps,
+                                 const long long* __restrict__ step_dev, float gscale) {
+  const double step = (double)step_dev[0];
+  const float bc1 = (float)(1.0 - pow((double)b1, step));
+  const float bc2_sqrt = (float)sqrt(1.0 - pow((double)b2, step));
+  const float step_size = lr / bc1;
+  const long long n4 = count >> 2;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
+    float4 pp = reinterpret_cast<float4*>(p)[i];
+    const float4 gg4 = reinterpret_cast<const float4*>(g)[i];
+    float4 mm = reinterpret_cast<float4*>(m)[i], vv = reinterpret_cast<float4*>(v)[i];
+    float* pe = &pp.x; const float* ge = &gg4.x; float* me = &mm.x; float* ve = &vv.x;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float gg = ge[k] * gscale;
+      me[k] = me[k] * b1 + gg * (1.f - b1);
+      ve[k] = ve[k] * b2 + gg * gg * (1.f - b2);
+      pe[k] = pe[k] - step_size * (me[k] / (sqrtf(ve[k]) / bc2_sqrt + eps));
+    }
+    reinterpret_cast<float4*>(p)[i] = pp;
+    reinterpret_cast<float4*>(m)[i] = mm;
+    reinterpret_cast<float4*>(v)[i] = vv;
+  }
+  for (long long i = (n4 << 2) + blockIdx.x * (long long)blockDim.x + threadIdx.x; i < count; i += (long long)gridDim.x * blockDim.x) {
+    const float gg = g[i] * gscale;
+    const float mm = m[i] * b1 + gg * (1.f - b1), vv = v[i] * b2 + gg * gg * (1.f - b2);
+    m[i] = mm; v[i] = vv;
+    p[i] = p[i] - step_size * (mm / (sqrtf(vv) / bc2_sqrt + eps));
+  }
+}
+
 }  // namespace rg
 
 using namespace rg;
@@ -395,6 +431,20 @@ int rg_adam_step(float* p, const float* g, float* m, float* v, int64_t count, fl
   adam_kernel<<<grid_for(count, 256), 256, 0, st>>>(p, g, m, v, count, lr, beta1, beta2, eps, (float)bc1,
                                                     (float)sqrt(bc2), grad_scale);
   RG_LAUNCH_CHECK("rg_adam_step");
+  return RG_OK;
+}
+
+int rg_adam_flat(float* p, const float* g, float* m, float* v, int64_t count, float lr, float beta1, float beta2, float eps,
+                 long long* step_dev, float grad_scale, void* stream) {
+  RG_CHECK_ARG(p && g && m && v && step_dev && count >= 0, "rg_adam_flat: bad argument");
+  RG_CHECK_ARG((((uintptr_t)p | (uintptr_t)g | (uintptr_t)m | (uintptr_t)v) & 15) == 0, "rg_adam_flat: buckets must be 16-byte aligned");
+  cudaStream_t st = (cudaStream_t)stream;
+  adam_step_inc_kernel<<<1, 1, 0, st>>>(step_dev);
+  RG_LAUNCH_CHECK("rg_adam_flat(step)");
+  if (count == 0) return RG_OK;
+  adam_flat_kernel<<<grid_for((count + 3) / 4, 256, 148 * 8), 256, 0, st>>>(p, g, m, v, count, lr, beta1, beta2, eps, step_dev,
+                                                                           grad_scale);
+  RG_LAUNCH_CHECK("rg_adam_flat");
   return RG_OK;
 }
 

@@ -16,9 +16,11 @@ import itertools
 import torch
 import torch.nn as tnn
 
+from . import conv as CV
 from . import functional as F
 from . import networks as N
 from . import nn as L
+from .optim import FlatAdam
 
 
 # ---------------------------------------------------------------------------------------------
@@ -259,7 +261,7 @@ class LinkCycleLoss(tnn.Module):
 
     def backward_Ds(self, data_dict, n_loop=5):
         self.set_requires_grad([self.netG1, self.netG2], False)
-        self.optimizer_D.zero_grad(set_to_none=True)
+        self.optimizer_D.zero_grad(set_to_none=True)      # once, BEFORE the wgangp loop, as LinkCycleLoss.py:66 does
         loops = n_loop if self.gan_mode.lower() == "wgangp" else 1
         for _ in range(loops):
             loss_D1 = self.backward_D("B", self.netD1, data_dict["B"])
@@ -299,7 +301,11 @@ class LinkCycleLoss(tnn.Module):
         loss.backward(retain_graph=True)
         return loss
 
-    def backward_Gs(self, data_dict):
+    def backward_Gs(self, data_dict, defer_step=False):
+        """LinkCycleLoss.py:116-135.  defer_step (data-parallel overlap): the generator gradients' all-reduce is only
+        STARTED here; `finish_Gs` waits for it and steps the optimizer after the discriminator phase, which reads neither
+        the generator weights nor their gradients (it works on the detached, pre-step fakes) -- same results, with the
+        exchange hidden behind the discriminators' forward and backward."""
         self.set_requires_grad([self.netD1, self.netD2], False)
         self.optimizer_G.zero_grad(set_to_none=True)
         if self.single_backward:
@@ -309,11 +315,18 @@ class LinkCycleLoss(tnn.Module):
         else:
             loss_G1 = self.backward_G("B", self.netG1, self.netD1, data_dict["B"])
             loss_G2 = self.backward_G("A", self.netG2, self.netD2, data_dict["A"])
-        if self.grad_sync is not None:
-            self.grad_sync("G")
-        self.optimizer_G.step()
+        if defer_step:
+            self.grad_sync.begin("G")
+        else:
+            if self.grad_sync is not None:
+                self.grad_sync("G")
+            self.optimizer_G.step()
         self.set_requires_grad([self.netD1, self.netD2], True)
         return loss_G1, loss_G2
+
+    def finish_Gs(self):
+        self.grad_sync.finish("G")
+        self.optimizer_G.step()
 
     def forward(self, real_A, fake_A, cycled_A, real_B, fake_B, cycled_B):
         self.data_dict.update(real_A=real_A, fake_A=fake_A, cycled_A=cycled_A, real_B=real_B, fake_B=fake_B,
@@ -323,8 +336,12 @@ class LinkCycleLoss(tnn.Module):
             real_B = self.crop(real_B, fake_B.shape[-self.dims:])
         data = {"A": {"real": real_A, "fake": fake_A, "cycled": cycled_A},
                 "B": {"real": real_B, "fake": fake_B, "cycled": cycled_B}}
-        loss_G1, loss_G2 = self.backward_Gs(data)
+        overlap = (self.grad_sync is not None and hasattr(self.grad_sync, "begin") and type(self) is LinkCycleLoss
+                   and "G" in getattr(self.grad_sync, "flat", {}))
+        loss_G1, loss_G2 = self.backward_Gs(data, defer_step=True) if overlap else self.backward_Gs(data)
         loss_D1, loss_D2 = self.backward_Ds(data)
+        if overlap:
+            self.finish_Gs()
         # one host sync for the four logged scalars (the reference does four float() calls); under CUDA-graph capture
         # (CycleGANStep(graph=True)) the read is deferred to after the replay: log_totals()
         self.loss_vec = torch.stack([loss_D1.detach(), loss_D2.detach(), loss_G1.detach(), loss_G2.detach()])
@@ -396,10 +413,27 @@ class CycleGANStep:
     def __init__(self, g1, g2, d1, d2, lr=1e-5, betas=(0.9, 0.999), l1_loss=None, g_lambda_dict=None,
                  d_lambda_dict=None, gan_mode="lsgan", grad_sync=None, single_backward=False, dims=3,
                  optimizer_cls=None, graph=False, graph_warmup=3):
-        opt = optimizer_cls or (functools.partial(torch.optim.Adam, capturable=True) if graph else torch.optim.Adam)
+        """optimizer_cls: None = `optim.FlatAdam` (flat fp32 buckets, one fused Adam kernel, tensor-core packs re-packed
+        in place; parameters on a CUDA device) -- "torch" = `torch.optim.Adam` (capturable under `graph`), or any
+        optimizer class.  grad_sync: a `dist.GradSync`, or "auto" to build one over the two optimizers when
+        torch.distributed is initialised."""
+        on_gpu = next(g1.parameters()).is_cuda
+        if optimizer_cls is None and on_gpu:
+            opt = FlatAdam
+        elif optimizer_cls in (None, "torch"):
+            opt = functools.partial(torch.optim.Adam, capturable=True) if graph else torch.optim.Adam
+        else:
+            opt = optimizer_cls
         self.nets = (g1, g2, d1, d2)
         self.optimizer_G = opt(itertools.chain(g1.parameters(), g2.parameters()), lr=lr, betas=betas)
         self.optimizer_D = opt(itertools.chain(d1.parameters(), d2.parameters()), lr=lr, betas=betas)
+        self.managed_packs = isinstance(self.optimizer_G, FlatAdam) and isinstance(self.optimizer_D, FlatAdam)
+        if grad_sync == "auto":
+            from .dist import GradSync
+            grad_sync = GradSync({"G": self.optimizer_G if isinstance(self.optimizer_G, FlatAdam) else
+                                  list(g1.parameters()) + list(g2.parameters()),
+                                  "D": self.optimizer_D if isinstance(self.optimizer_D, FlatAdam) else
+                                  list(d1.parameters()) + list(d2.parameters())}) if torch.distributed.is_initialized() else None
         self.model = CycleModel(g1, g2)
         self.loss = LinkCycleLoss(d1, g1, d2, g2, self.optimizer_G, self.optimizer_D, dims, l1_loss=l1_loss,
                                   g_lambda_dict=g_lambda_dict, d_lambda_dict=d_lambda_dict, gan_mode=gan_mode,
@@ -428,6 +462,7 @@ class CycleGANStep:
         self.loss.data_dict.clear()
         self.loss.loss_vec = None
         gc.collect()
+        CV.invalidate_packs()             # every weight pack is (re)built inside the capture: no pack kernel is skipped
         torch.cuda.synchronize()
         self._in_a, self._in_b = real_A.clone(), real_B.clone()
         graph = torch.cuda.CUDAGraph()
@@ -456,6 +491,10 @@ class CycleGANStep:
             self._in_a.copy_(real_A, non_blocking=True)
             self._in_b.copy_(real_B, non_blocking=True)
             self.graph.replay()
+            if not self.managed_packs:
+                # a torch optimizer updated the weights inside the graph without touching Python's version counters:
+                # eager forwards after this replay must not trust their cached packs (FlatAdam re-packs in place instead)
+                CV.invalidate_packs()
             self.loss.log_totals()
             return self._totals()
         self._eager_steps += 1

@@ -29,18 +29,58 @@ def init_from_env(backend: str | None = None):
 
 
 class GradSync:
-    """Average the gradients of parameter groups across ranks with ONE all-reduce per group.
+    """Average the gradients of parameter groups across ranks.
 
-    groups: {"G": [params of G1 and G2], "D": [params of D1 and D2]}.  ``sync("G")`` flattens the existing
-    ``.grad`` tensors into a persistent fp32 bucket, all-reduces it (sum), scales by 1/world and scatters the
-    result back in place.  Parameters without a gradient contribute zeros (so every rank reduces the same bytes)."""
+    groups: {"G": optimizer or [params of G1 and G2], "D": ...}.
 
-    def __init__(self, groups, group=None):
-        self.groups = {k: [p for p in v] for k, v in groups.items()}
+    * A group given as an ``optim.FlatAdam`` is reduced IN PLACE in its flat gradient bucket (every ``.grad`` is a view of
+      it): ``begin(name)`` issues one asynchronous all-reduce per ~25 MB chunk -- NCCL runs them on its own stream, after
+      everything queued so far, concurrently with whatever the caller launches next (LinkCycleLoss launches the whole
+      discriminator phase, which does not depend on the generator update: the exchange is hidden behind its forward and
+      backward) -- and ``finish(name)`` makes the current stream wait for them.  The 1/world of the average is folded
+      into the Adam update (``FlatAdam.grad_scale``): no scaling pass.  Both calls are capturable in a CUDA graph.
+    * A group given as a parameter list (any other optimizer) is flattened into a persistent bucket, reduced with one
+      blocking all-reduce, scaled and scattered back: ``sync(name)``.
+    ``__call__(name)`` = begin + finish (or sync)."""
+
+    CHUNK_BYTES = 25 << 20
+
+    def __init__(self, groups, group=None, chunk_bytes=None):
         self.pg = group
+        self.flat, self.groups = {}, {}
+        for k, v in groups.items():
+            if hasattr(v, "flat_g"):
+                self.flat[k] = v
+                if dist.is_initialized():
+                    v.grad_scale = 1.0 / dist.get_world_size(self.pg)
+            else:
+                self.groups[k] = [p for p in v]
+        self.chunk = int(chunk_bytes or self.CHUNK_BYTES) // 4
         self.buckets = {}
+        self.pending = {}
         self.bytes_reduced = 0
 
+    def _active(self):
+        return dist.is_initialized() and dist.get_world_size(self.pg) > 1
+
+    # -- flat buckets: asynchronous, chunked ----------------------------------------------------------------------
+    def begin(self, name):
+        if not self._active():
+            return
+        if name not in self.flat:
+            return self.sync(name)
+        flat = self.flat[name].flat_g
+        works = []
+        for off in range(0, flat.numel(), self.chunk):
+            works.append(dist.all_reduce(flat[off: off + self.chunk], group=self.pg, async_op=True))
+        self.pending[name] = works
+        self.bytes_reduced += flat.numel() * 4
+
+    def finish(self, name):
+        for w in self.pending.pop(name, ()):
+            w.wait()
+
+    # -- parameter lists: one blocking bucket ---------------------------------------------------------------------
     def _bucket(self, name):
         if name not in self.buckets:
             ps = self.groups[name]
@@ -48,9 +88,12 @@ class GradSync:
             self.buckets[name] = torch.zeros(n, dtype=torch.float32, device=ps[0].device)
         return self.buckets[name]
 
-    def __call__(self, name):
-        if not dist.is_initialized() or dist.get_world_size(self.pg) == 1:
+    def sync(self, name):
+        if not self._active():
             return
+        if name in self.flat:
+            self.begin(name)
+            return self.finish(name)
         flat = self._bucket(name)
         off = 0
         for p in self.groups[name]:
@@ -70,7 +113,7 @@ class GradSync:
                 p.grad.copy_(flat[off: off + n].view_as(p.grad))
             off += n
 
-    sync = __call__
+    __call__ = sync
 
 
 def shard_batch(x: torch.Tensor, rank: int, world: int) -> torch.Tensor:

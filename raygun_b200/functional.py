@@ -9,6 +9,7 @@ import torch
 
 from . import conv as CV
 from . import kernels as K
+from .optim import bucket_grad
 from ._C import (ACT_LEAKY, ACT_NONE, ACT_RELU, ACT_SIGMOID, ACT_TANH, LOSS_L1, LOSS_MEAN, LOSS_MSE_CONST, LOSS_SMOOTHL1,
                  NORM_BATCH, NORM_INSTANCE, PAD_REFLECT, PAD_REPLICATE, PAD_ZEROS)
 
@@ -73,8 +74,7 @@ class _Conv3d(torch.autograd.Function):
         ctx.narrow = _Conv3d._narrow_out(x, w, stride, groups, want_stats)
         if ctx.narrow:
             cout = w.shape[0]
-            wp = torch.zeros(64, *w.shape[1:], dtype=w.dtype, device=w.device)
-            wp[:cout] = w.detach()
+            wp = CV.WeightSrc(w, lambda p_: CV._pad_rows(p_, 64), (64, *w.shape[1:]), "rows64")
             bp = None
             if bias is not None:
                 bp = torch.zeros(64, dtype=torch.float32, device=w.device)
@@ -108,8 +108,7 @@ class _Conv3d(torch.autograd.Function):
             dyp = torch.zeros(dy.shape[0], 64, *dy.shape[2:], dtype=torch.bfloat16, device=dy.device).contiguous(
                 memory_format=torch.channels_last_3d)
             K.copy_into(dyp[:, :cout], dy)
-            wp = torch.zeros(64, *w.shape[1:], dtype=w.dtype, device=w.device)
-            wp[:cout] = w.detach()
+            wp = CV.WeightSrc(w, lambda p_: CV._pad_rows(p_, 64), (64, *w.shape[1:]), "rows64")
             if ctx.needs_input_grad[0]:
                 dx, _, _ = CV.conv_dgrad(dyp, wp, x.shape, stride, pad, groups, out_dtype=x.dtype)
             if ctx.needs_input_grad[1] or (ctx.has_bias and ctx.needs_input_grad[2]):
@@ -120,8 +119,11 @@ class _Conv3d(torch.autograd.Function):
         if ctx.needs_input_grad[0]:
             dx, _, _ = CV.conv_dgrad(dy, w, x.shape, stride, pad, groups, out_dtype=x.dtype)
         if ctx.needs_input_grad[1] or (ctx.has_bias and ctx.needs_input_grad[2]):
-            dw, db = CV.conv_wgrad(x, dy, w.shape, stride, pad, groups, want_bias=ctx.has_bias, db=db_pre)
-            if not ctx.needs_input_grad[1]:
+            # a live gradient bucket (optim.FlatAdam): the kernel accumulates into its view, autograd gets None
+            bg = bucket_grad(w) if ctx.needs_input_grad[1] else None
+            dw, db = CV.conv_wgrad(x, dy, w.shape, stride, pad, groups, want_bias=ctx.has_bias, db=db_pre, dw_out=bg,
+                                   accumulate=bg is not None)
+            if not ctx.needs_input_grad[1] or bg is not None:
                 dw = None
         return dx, dw, db, None, None, None, None, None, None, None
 
@@ -142,8 +144,12 @@ class _StemConv3d(torch.autograd.Function):
             y, s, q = CV.stem_conv_fprop(x, w, bias, pad, act, slope, out=out), None, None
         else:
             xc = K.im2col_hw(x, kh, kw, pad[1], pad[2], 64)
-            w2 = w.detach().permute(0, 2, 1, 3, 4).reshape(cout, kd, cf)          # [co][kd][(ci,kh,kw)]
-            w2 = torch.nn.functional.pad(w2, (0, 64 - cf)).permute(0, 2, 1).reshape(cout, 64, kd, 1, 1).contiguous()
+
+            def fold(p_):          # [co][ci][kd][kh][kw] -> [co][(ci,kh,kw) padded to 64][kd][1][1]
+                w2 = p_.detach().permute(0, 2, 1, 3, 4).reshape(cout, kd, cf)
+                return torch.nn.functional.pad(w2, (0, 64 - cf)).permute(0, 2, 1).reshape(cout, 64, kd, 1, 1).contiguous()
+
+            w2 = CV.WeightSrc(w, fold, (cout, 64, kd, 1, 1), "stemfold")
             y, s, q = CV.conv_fprop(xc, w2, bias, (1, 1, 1), (pad[0], 0, 0), 1, act, slope, want_stats, out=out)
         ctx.cfg = (pad, act, slope, tuple(w.shape), (cout, 64, kd, 1, 1))
         ctx.has_bias = bias is not None
@@ -232,11 +238,12 @@ class _ConvTranspose3d(torch.autograd.Function):
             dx, _, _ = CV.conv_fprop(dy, w, None, stride, pad, 1, out_dtype=x.dtype)
         if ctx.needs_input_grad[1] or (ctx.has_bias and ctx.needs_input_grad[2]):
             # conv' : dy (Cout_T) -> x (Cin_T); its wgrad has "x" = dy and "dy" = x; bias grad = sum(dy)
-            dw, _ = CV.conv_wgrad(dy, x, w.shape, stride, pad, 1, want_bias=False)
+            bg = bucket_grad(w) if ctx.needs_input_grad[1] else None
+            dw, _ = CV.conv_wgrad(dy, x, w.shape, stride, pad, 1, want_bias=False, dw_out=bg, accumulate=bg is not None)
             if ctx.has_bias:
                 s, _ = K.norm_stats(dy, NORM_BATCH)
                 db = s
-            if not ctx.needs_input_grad[1]:
+            if not ctx.needs_input_grad[1] or bg is not None:
                 dw = None
         return dx, dw, db, None, None, None, None, None, None, None
 

@@ -390,10 +390,13 @@ def u8_normalise(u8: torch.Tensor, scale=2.0, shift=-1.0, dtype=None):
     return y
 
 
-def denorm_clamp_u8(x: torch.Tensor):
-    """x: 5-D view (any strides, e.g. a cropped slice) -> contiguous uint8 of the same shape."""
+def denorm_clamp_u8(x: torch.Tensor, out: torch.Tensor | None = None):
+    """x: 5-D view (any strides, e.g. a cropped slice) -> contiguous uint8 of the same shape (`out`: preallocated)."""
     require_device(x)
-    out = torch.empty(x.shape, dtype=torch.uint8, device=x.device)
+    if out is None:
+        out = torch.empty(x.shape, dtype=torch.uint8, device=x.device)
+    elif tuple(out.shape) != tuple(x.shape) or out.dtype != torch.uint8 or not out.is_contiguous():
+        raise ValueError("denorm_clamp_u8: out must be a contiguous uint8 tensor of x's shape")
     check(lib().rg_denorm_clamp_u8(C.byref(t5(x)), ptr(x), ptr(out), stream_ptr(x.device)), "rg_denorm_clamp_u8")
     count_launch()
     return out

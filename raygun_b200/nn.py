@@ -262,7 +262,9 @@ def run_layers(layers, x, residual=None, out=None):
                 y, st = m.fused(x, want_stats=True)
                 a = layers[i + 2] if i + 2 < n else None
                 ac = act_code(a) if a is not None else None
-                last = (i + 2 >= n) if ac is None else (i + 3 >= n)
+                # the residual is added right after the LAST layer: fused only when that layer is this norm (a list that
+                # ends in norm -> activation keeps act(norm(x)) + residual: the trailing add below)
+                last = (i + 2 >= n) and ac is None
                 res = residual if last else None
                 if ac is not None:
                     x = nxt.fused(y, st, ac[0], ac[1], residual=res)
