@@ -106,7 +106,7 @@ struct RingWalk {
     // Slice groups are anchored on the ABSOLUTE plane index (group boundaries where z + pd is a multiple of S), not on the
     // unit's first plane: the order in which an output voxel receives its (slice, chunk, tap) contributions -- hence its
     // fp32 rounding -- is then independent of how the depth axis was cut into units, and of the read-block geometry of a
-    // blockwise prediction whenever block origins are multiples of S at this resolution level (S <= 2 by default).
+    // blockwise prediction whenever block origins are multiples of S at this resolution level (S <= 3: ring_geometry).
     r.zg0 = r.z_begin - (r.d0 % p.S);
     return true;
   }
@@ -530,12 +530,15 @@ static int ring_geometry(const rg_igemm_desc* d, RingGeom* g) {
   p.slice_tx = hb * p.wb * 128;
   p.slice_bytes = (p.slice_tx + 1023) & ~1023;
   p.stage_bytes = (p.kd < STAGE_KD ? p.kd : STAGE_KD) * WBLK_BYTES;
-  // slices per weight stage: prefer a configuration with one group of drain slack (2S + KD - 1 <= 8).  S is a power of
-  // two, 2 by default (groups are anchored on absolute plane indices: see RingWalk), RAYGUN_B200_RING_S=4 allows 4.
-  static const int s_cap = [] { const char* e = getenv("RAYGUN_B200_RING_S"); const int v = e ? atoi(e) : 2; return v >= 4 ? 4 : (v >= 2 ? 2 : 1); }();
+  // slices per weight stage (S + KD - 1 accumulator blocks in flight; one group of drain slack when 2S + KD - 1 <= 8).
+  // Groups are anchored on absolute plane indices (RingWalk), so results are independent of the block geometry of a
+  // blockwise prediction when block origins are multiples of S at every resolution level.  S <= 3 by default: with the
+  // 24-voxel halo, any write size that is a multiple of 12 keeps the read origins multiples of 12 = 3 * 4 (S = 3 at the
+  // coarsest of three U-Net levels; the 7^3 layers run S = 2).  RAYGUN_B200_RING_S = 2 relaxes that to multiples of 8
+  // at ~5 % more weight traffic per slice (measured: 455 vs 480 Mvoxel/s on cfg4); 4 is for experiments.
+  static const int s_cap = [] { const char* e = getenv("RAYGUN_B200_RING_S"); const int v = e ? atoi(e) : 3; return v < 1 ? 1 : (v > 4 ? 4 : v); }();
   p.S = RING_BLOCKS - (p.kd - 1);
   if (p.S > s_cap) p.S = s_cap;
-  if (p.S >= 4) p.S = 4; else if (p.S >= 2) p.S = 2; else p.S = 1;
   p.lag = (2 * p.S + p.kd - 1 <= RING_BLOCKS) ? 2 : 1;
   for (;;) {
     p.nb = 3;
@@ -545,7 +548,7 @@ static int ring_geometry(const rg_igemm_desc* d, RingGeom* g) {
     if (na > MAX_NA) na = MAX_NA;
     if (na >= p.S + 1 || (na >= p.S && p.S == 1)) { p.na = na; break; }
     RG_UNSUPPORTED(p.S == 1, "ring conv: slice does not fit shared memory");
-    p.S /= 2;
+    --p.S;
     p.lag = (2 * p.S + p.kd - 1 <= RING_BLOCKS) ? 2 : 1;
   }
   g->smem_bytes = 1024 + p.na * p.slice_bytes + p.nb * p.stage_bytes + RING_TAIL_BYTES;

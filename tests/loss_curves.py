@@ -64,11 +64,12 @@ def cyclegan_curve(mode, steps, dev, side=32, pool=4, lr=1e-5):
     D_KW = dict(input_nc=1, ngf=64, n_layers=3, kw=3, downsampling_kw=2)
     torch.manual_seed(11)
     IN = functools.partial(torch.nn.InstanceNorm3d, affine=False, track_running_stats=False)
-    with contextlib.redirect_stdout(sys.stderr):
-        g1, g2 = (make_generator("unet", dict(G_KW)).to(dev) for _ in range(2))
-        d1, d2 = (N.NLayerDiscriminator(3, norm_layer=IN, **D_KW).to(dev) for _ in range(2))
+    with contextlib.redirect_stdout(sys.stderr):          # initialised on the CPU (the RNG stream the oracle twin uses)
+        g1, g2 = (make_generator("unet", dict(G_KW)) for _ in range(2))
+        d1, d2 = (N.NLayerDiscriminator(3, norm_layer=IN, **D_KW) for _ in range(2))
         for d in (d1, d2):
             N.init_weights(d, "kaiming")
+    g1, g2, d1, d2 = (m.to(dev) for m in (g1, g2, d1, d2))
     a = em_like(pool, side, 200).to(dev)
     b = (-em_like(pool, side, 201)).to(dev)
     out = {k: [] for k in ("G1", "G2", "D1", "D2")}
@@ -89,7 +90,12 @@ def _oracle_backend(variant):
     torch.backends.cudnn.allow_tf32 = False
     torch.backends.cuda.matmul.allow_tf32 = False
     torch.backends.cudnn.deterministic = variant == 0
-    torch.backends.cudnn.benchmark = variant == 1
+    torch.backends.cudnn.benchmark = variant != 0
+
+
+def _amp(variant):
+    """variant 2: the reference's own reduced-precision mode, torch.autocast(bfloat16) -- the yardstick for a bf16 path."""
+    return torch.autocast("cuda", dtype=torch.bfloat16, enabled=variant == 2)
 
 
 def oracle_generator_curve(steps, dev, side=32, pool=4, lr=2e-5, variant=0):
@@ -112,7 +118,9 @@ def oracle_generator_curve(steps, dev, side=32, pool=4, lr=2e-5, variant=0):
         names = list(opt.p)
         for k in names:
             opt.p[k].requires_grad_(True)
-        loss = O.smooth_l1(ts[i:i + 1], O.generator_forward(sd, "resnet", spec, xs[i:i + 1], final_activation="Tanh"))
+        with _amp(variant):
+            y = O.generator_forward(sd, "resnet", spec, xs[i:i + 1], final_activation="Tanh")
+        loss = O.smooth_l1(ts[i:i + 1], y.float())
         grads = torch.autograd.grad(loss, [opt.p[k] for k in names], allow_unused=True)
         for k in names:
             opt.p[k].requires_grad_(False)
@@ -140,8 +148,15 @@ def oracle_cyclegan_curve(steps, dev, side=32, pool=4, lr=1e-5, variant=0):
     uspec = O.unet_spec(input_nc=1, ngf=64, fmap_inc_factor=2, downsample_factors=[(2, 2, 2)] * 2, padding_type="same")
     dspec = O.nld_spec(input_nc=1, ngf=64, n_layers=3, norm=dict(kind="instance", affine=False), kw=3, downsampling_kw=2)
     _oracle_backend(variant)
-    cs = O.CycleStep(*sds, g_fwd=lambda sd, x: O.generator_forward(sd, "unet", uspec, x, final_activation="Tanh"),
-                     d_fwd=lambda sd, x: O.nld3d_forward(sd, dspec, x), lr=lr)
+    def g_fwd(sd, x):
+        with _amp(variant):
+            return O.generator_forward(sd, "unet", uspec, x, final_activation="Tanh").float()
+
+    def d_fwd(sd, x):
+        with _amp(variant):
+            return O.nld3d_forward(sd, dspec, x).float()
+
+    cs = O.CycleStep(*sds, g_fwd=g_fwd, d_fwd=d_fwd, lr=lr)
     a = em_like(pool, side, 200).to(dev)
     b = (-em_like(pool, side, 201)).to(dev)
     out = {k: [] for k in ("G1", "G2", "D1", "D2")}
@@ -178,18 +193,21 @@ def main():
     if "gen" in what:
         o = oracle_generator_curve(args.steps, dev, side=args.side)
         o2 = oracle_generator_curve(args.steps, dev, side=args.side, variant=1)
+        o3 = oracle_generator_curve(args.steps, dev, side=args.side, variant=2)
         f = generator_curve("fp32", args.steps, dev, side=args.side)
         h = generator_curve("bf16", args.steps, dev, side=args.side)
         f2 = generator_curve("fp32", args.steps, dev, side=args.side)
         h2 = generator_curve("bf16", args.steps, dev, side=args.side)
         print(json.dumps(dict(workload="generator", steps=args.steps, fp32_vs_oracle=deviation(o, f),
                               bf16_vs_oracle=deviation(o, h), oracle_vs_oracle_other_cudnn_algos=deviation(o, o2),
+                              oracle_autocast_bf16_vs_oracle=deviation(o, o3),
                               fp32_rerun_identical=f == f2, bf16_rerun_identical=h == h2,
                               first_step_over_1pct=dict(fp32=first_over(o, f), bf16=first_over(o, h), oracle2=first_over(o, o2)),
                               oracle=o[::20], fp32=f[::20], bf16=h[::20])), flush=True)
     if "cycle" in what:
         o = oracle_cyclegan_curve(args.steps, dev, side=args.side)
         o2 = oracle_cyclegan_curve(args.steps, dev, side=args.side, variant=1)
+        o3 = oracle_cyclegan_curve(args.steps, dev, side=args.side, variant=2)
         f = cyclegan_curve("fp32", args.steps, dev, side=args.side)
         h = cyclegan_curve("bf16", args.steps, dev, side=args.side)
         f2 = cyclegan_curve("fp32", args.steps, dev, side=args.side)
@@ -198,9 +216,11 @@ def main():
                               fp32_vs_oracle={k: deviation(o[k], f[k]) for k in f},
                               bf16_vs_oracle={k: deviation(o[k], h[k]) for k in f},
                               oracle_vs_oracle_other_cudnn_algos={k: deviation(o[k], o2[k]) for k in f},
+                              oracle_autocast_bf16_vs_oracle={k: deviation(o[k], o3[k]) for k in f},
                               fp32_rerun_identical=f == f2, bf16_rerun_identical=h == h2,
                               first_step_over_1pct={k: dict(fp32=first_over(o[k], f[k]), bf16=first_over(o[k], h[k]),
-                                                            oracle2=first_over(o[k], o2[k])) for k in f},
+                                                            oracle2=first_over(o[k], o2[k]), oracle_autocast=first_over(o[k], o3[k]))
+                                                    for k in f},
                               oracle={k: v[::20] for k, v in o.items()}, fp32={k: v[::20] for k, v in f.items()},
                               bf16={k: v[::20] for k, v in h.items()})), flush=True)
 

@@ -149,9 +149,9 @@ def test_flat_adam_follows_torch_adam_and_single_backward_equals_the_reference_s
 
 
 def test_blockwise_prediction_is_bitwise_independent_of_block_geometry_and_equals_the_whole_volume():
-    """cfg4 property: halo 24 >= 22, origins = 0 mod 8 -> the uint8 output does not depend on the read-block
-    geometry, and with fit="clip" (read rois clipped at the volume faces) the stitched volume EQUALS the whole-volume
-    forward, face voxels included -- on the bf16 tensor-core path, bit for bit."""
+    """cfg4 property: halo 24 >= 22, write sizes (hence read origins) multiples of 12 -> the uint8 output does
+    not depend on the read-block geometry, and with fit="clip" (read rois clipped at the volume faces) the stitched
+    volume EQUALS the whole-volume forward, face voxels included -- on the bf16 tensor-core path, bit for bit."""
     import raygun_b200 as rb
     from raygun_b200 import kernels as K
     from raygun_b200 import predict as P
@@ -161,10 +161,10 @@ def test_blockwise_prediction_is_bitwise_independent_of_block_geometry_and_equal
     with rb.precision("bf16"), torch.no_grad():
         with _quiet():
             g = make_generator("unet", dict(G_KW)).to(DEV).eval()
-        vol = torch.from_numpy(em_like_u8((192, 160, 176), seed=7)).to(DEV)
+        vol = torch.from_numpy(em_like_u8((192, 168, 192), seed=7)).to(DEV)
         whole = K.denorm_clamp_u8(g(K.u8_normalise(vol, dtype=torch.bfloat16)[None, None]))[0, 0]
         outs = []
-        for read, write in (((112,) * 3, (64,) * 3), ((96, 128, 80), (48, 80, 32)), ((176, 160, 176), (128, 112, 128))):
+        for read, write in (((120,) * 3, (72,) * 3), ((96, 144, 84), (48, 96, 36)), ((180, 168, 192), (132, 120, 144))):
             out, nb, vox = P.predict_volume(g, vol, read, write, out=torch.zeros_like(vol), dtype=torch.bfloat16, fit="clip")
             assert vox == vol.numel() and nb == len(P.block_list(vol.shape, read, write, "clip"))
             outs.append(out)
@@ -173,6 +173,6 @@ def test_blockwise_prediction_is_bitwise_independent_of_block_geometry_and_equal
         # two "ranks": cost-balanced disjoint shares fill one output volume
         out2 = torch.zeros_like(vol)
         for r in range(2):
-            P.predict_volume(g, vol, (112,) * 3, (64,) * 3, out=out2, rank=r, world=2, dtype=torch.bfloat16, fit="clip")
+            P.predict_volume(g, vol, (120,) * 3, (72,) * 3, out=out2, rank=r, world=2, dtype=torch.bfloat16, fit="clip")
         assert torch.equal(out2, whole)
         assert float(whole.float().std()) > 1.0
