@@ -73,7 +73,9 @@ def make_generator(net_type, net_kwargs, output_nc=None, final_activation=None, 
     conv = L.Conv3d if ndims == 3 else tnn.Conv2d
     layers = [net, conv(kw.get("ngf", 64), output_nc, (1,) * ndims, padding=kw.get("padding_type", "valid")
                         if kw.get("padding_type", "valid") in ("same", "valid") else 0)]
-    if final_activation is not None:
+    if isinstance(final_activation, tnn.Module):
+        layers.append(final_activation)               # an instance, e.g. from a "#torch.nn.Tanh()#" config expression
+    elif final_activation is not None:
         layers.append(L.make_activation(final_activation) if ndims == 3 else
                       (getattr(tnn, final_activation) if isinstance(final_activation, str) else final_activation)())
     g = Generator(*layers)

@@ -34,7 +34,9 @@ class FlatAdam(torch.optim.Optimizer):
     buckets (a later ``module.to(...)`` would detach them again).  ``zero_grad`` clears the bucket and KEEPS the views,
     whatever ``set_to_none`` says -- the gradient kernels accumulate into them."""
 
-    def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, grad_scale=1.0):
+    def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0, amsgrad=False, grad_scale=1.0):
+        if weight_decay or amsgrad:     # default_cycleGAN_conf.json passes weight_decay = 0 explicitly
+            raise NotImplementedError("FlatAdam: weight_decay / amsgrad are not implemented (raygun's configs use neither)")
         params = list(params)
         if not params:
             raise ValueError("FlatAdam: empty parameter list")

@@ -229,35 +229,6 @@ def test_split_cyclegan_training_steps_match_reference_losses():
                 assert abs(gv - rv) <= 2e-3 * max(1.0, abs(rv)), (it, got, ref[it].tolist())
 
 
-def test_bf16_loss_curves_follow_fp32_over_200_steps():
-    """north_star: "loss curves within 1% over 200 steps" (bf16 tensor-core path vs fp32; the fp32 path of the same
-    library is pinned to the reference by the tests above).  Workloads and statistics: scripts/loss_curve.py, measured
-    numbers: profiles/r01_loss_curves.jsonl.
-
-    Both trainings amplify perturbations exponentially: two fp32 runs of the SAME kernels (the fp32 weight-gradient
-    atomics change the summation order run to run) start 1e-5 apart at step 3 and are 1-3 % apart per step by step 20
-    (CycleGAN, growth ~x1.5 per step), 5-7 % apart per step after 200 steps, 25 % for the supervised generator (Adam
-    loss spikes once the loss is ~0.01); their 200-step means differ by 0.01-0.8 %.  bf16 starts 3e-4 apart and so
-    reaches 1 % per step around step 8.  Measured bf16 vs fp32 (two sessions): 200-step means within 0.07 % (generator)
-    and 0.06-1.7 % (CycleGAN G1/G2/D1/D2), first three steps within 0.25 % per step (0.7-1.0 % by step 5), 10-step windows within 17 % / 10 %.
-    A 1 % per-step bound over 200 steps is therefore not a property even of the fp32 path against itself; the test
-    bounds what is stable: first 3 steps <= 1 % per step, 200-step mean <= 4 %, smoothed curves inside a loose
-    envelope (no drift, no blow-up).
-    """
-    from tests import loss_curves as LC
-    f = LC.generator_curve("fp32", 200, DEV)
-    h = LC.generator_curve("bf16", 200, DEV)
-    assert f[-1] < 0.2 * f[0] and h[-1] < 0.2 * h[0], "the supervised workload must actually train"
-    curves = {"generator": (f, h, 0.40)}
-    f = LC.cyclegan_curve("fp32", 200, DEV)
-    h = LC.cyclegan_curve("bf16", 200, DEV)
-    curves.update({k: (f[k], h[k], 0.20) for k in f})
-    for k, (a, b, envelope) in curves.items():
-        assert LC.deviation(a[:3], b[:3], window=1)["per_step_max_rel"] <= 1e-2, k
-        d = LC.deviation(a, b)
-        assert d["mean_rel"] <= 4e-2 and d["smoothed_max_rel"] <= envelope, (k, d)
-
-
 def test_deep_unet_cfg5_bf16_path_follows_the_fp32_path():
     """cfg5 architecture (4 down-sampling levels, fmap_inc_factor 3, ngf 64: 64..5184 channels, 1.78 B parameters) on
     one 32^3 patch: bf16 tensor-core forward within 2e-2 of the fp32 path (north_star), every parameter gradient

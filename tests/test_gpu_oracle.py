@@ -1,0 +1,248 @@
+"""The bf16 tensor-core path against the ORACLE (oracle/restate.py, the reference's algorithm restated; pinned to the
+reference by tests/test_oracle_pinned.py) at BASELINE sizes and widths -- ngf 64, where every layer runs a tcgen05 kernel
+(r01's goldens were ngf 4-8 and exercised the CUDA-core kernels only).
+
+Tolerances (north_star): bf16 path <= 2e-2 relative on generator outputs; loss curves within 1 % over 200 steps -- see
+`test_loss_curves_against_the_oracle_over_200_steps` for what that bound can and cannot mean for a chaotic GAN training.
+The oracle runs on the CPU for the forward checks and through stock torch fp32 ops on the GPU (TF32 off) where a CPU
+run would take minutes."""
+import contextlib
+import functools
+import sys
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+IN = functools.partial(torch.nn.InstanceNorm3d, affine=False, track_running_stats=False)
+G_KW = dict(input_nc=1, output_nc=1, ngf=64, fmap_inc_factor=2, num_downs=3, padding_type="same", final_activation="Tanh")
+D_KW = dict(input_nc=1, ngf=64, n_layers=3, kw=3, downsampling_kw=2)
+
+
+def _quiet():
+    return contextlib.redirect_stdout(sys.stderr)
+
+
+def _fp32_backend():
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.deterministic = True
+    torch.backends.cudnn.benchmark = False
+
+
+def _specs():
+    from oracle import restate as O
+    uspec = O.unet_spec(input_nc=1, ngf=64, fmap_inc_factor=2, downsample_factors=[(2, 2, 2)] * 2, padding_type="same")
+    dspec = O.nld_spec(input_nc=1, ngf=64, n_layers=3, norm=dict(kind="instance", affine=False), kw=3, downsampling_kw=2)
+    return uspec, dspec
+
+
+def _u8_patch(n, side, seed):
+    import numpy as np
+    from oracle import restate as O
+    from raygun_b200.synth import em_like_u8
+    return O.u8_normalise(torch.from_numpy(np.stack([em_like_u8((side,) * 3, seed=seed + i)[None] for i in range(n)])))
+
+
+def test_cfg1_gunet_forward_1x1x64_bf16_vs_cpu_oracle():
+    """BASELINE configs[0] (cfg1): G-UNet forward on a synthetic 1x1x64^3 uint8 patch.  Oracle: fp32 on the CPU.
+    bf16 path: relative error (rms over rms) <= 2e-2, and no single voxel further than 5e-2 of the output range from the
+    oracle; the fp32 parity mode of the same modules: max-abs <= 1e-4."""
+    import raygun_b200 as rb
+    from oracle import restate as O
+    from raygun_b200 import conv as CV
+    from raygun_b200.cyclegan import make_generator
+    torch.manual_seed(42)
+    with _quiet():
+        g = make_generator("unet", dict(G_KW))
+    sd = {k: v.detach().clone() for k, v in g.state_dict().items()}
+    uspec, _ = _specs()
+    x = _u8_patch(1, 64, 42)
+    with torch.no_grad():
+        ref = O.generator_forward(sd, "unet", uspec, x, final_activation="Tanh")
+    g = g.to(DEV).eval()
+    before = dict(CV.stats)
+    with torch.no_grad():
+        with rb.precision("bf16"):
+            y16 = g(x.to(DEV)).float().cpu()
+        with rb.precision("fp32"):
+            y32 = g(x.to(DEV)).float().cpu()
+    assert CV.stats.get("ring", 0) > before.get("ring", 0) and CV.stats.get("stem_direct", 0) > before.get("stem_direct", 0)
+    assert tuple(y16.shape) == (1, 1, 64, 64, 64)
+    rel_rms = float((y16 - ref).norm() / ref.norm())
+    max_abs = float((y16 - ref).abs().max())
+    print(f"cfg1 bf16 vs oracle: rel-rms {rel_rms:.3e}, max-abs {max_abs:.3e} (output range {float(ref.min()):.2f}..{float(ref.max()):.2f})")
+    assert rel_rms <= 2e-2, rel_rms
+    assert max_abs <= 5e-2 * max(1.0, float(ref.abs().max())), max_abs
+    assert float((y32 - ref).abs().max()) <= 1e-4
+
+
+def _gpu_oracle_grads(kind, sd_cpu, spec, x, target=None):
+    """Oracle forward + loss + every parameter gradient through stock torch fp32 ops on the GPU."""
+    from oracle import restate as O
+    _fp32_backend()
+    sd = {k: v.detach().clone().to(DEV).requires_grad_(v.is_floating_point()) for k, v in sd_cpu.items()}
+    if kind == "unet":
+        y = O.generator_forward(sd, "unet", spec, x, final_activation="Tanh")
+        loss = O.smooth_l1(target, y)
+    else:
+        y = O.nld3d_forward(sd, spec, x)
+        loss = O.gan_loss(y, True)
+    names = [k for k, v in sd.items() if v.requires_grad]
+    grads = torch.autograd.grad(loss, [sd[k] for k in names], allow_unused=True)
+    return y.detach(), float(loss), dict(zip(names, grads))
+
+
+def _compare_grads(module, ref_grads, min_cos, norm_tol):
+    """Every parameter gradient vs the oracle's: direction (cosine) and norm.  Biases directly in front of an InstanceNorm
+    have an exactly zero gradient in exact arithmetic -- both sides are rounding noise there -- so gradients whose oracle
+    norm is below 1e-4 of the largest gradient norm are only required to be equally negligible."""
+    gmax = max(float(g.norm()) for g in ref_grads.values() if g is not None)
+    worst_cos, worst_ratio = 1.0, 0.0
+    for name, p in module.named_parameters():
+        r = ref_grads[name]
+        if r is None:
+            assert p.grad is None or float(p.grad.abs().max()) == 0.0, name
+            continue
+        a, b = p.grad.detach().double().flatten(), r.double().flatten()
+        if float(b.norm()) <= 1e-4 * gmax:
+            assert float(a.norm()) <= 1e-2 * gmax, (name, float(a.norm()), gmax)
+            continue
+        cos = float(torch.dot(a, b) / (a.norm() * b.norm()))
+        ratio = float(a.norm() / b.norm())
+        worst_cos, worst_ratio = min(worst_cos, cos), max(worst_ratio, abs(ratio - 1))
+        assert cos >= min_cos, (name, cos)
+        assert abs(ratio - 1) <= norm_tol, (name, ratio)
+    return worst_cos, worst_ratio
+
+
+def test_gunet_ngf64_forward_backward_every_parameter_gradient_vs_oracle():
+    """G-UNet (ngf 64) forward + SmoothL1 + backward on 2x1x32^3: output within 2e-2 relative, loss within 1 %, and EVERY
+    parameter gradient aligned with the oracle's (cosine >= 0.98) with the same norm (+-5 %): stem wgrad, ring dgrad,
+    halo wgrad through pad arenas / in-place pad folds, up-convolution backward, max-pool routing, the 1x1x1 head."""
+    import raygun_b200 as rb
+    from raygun_b200 import functional as F
+    from raygun_b200.cyclegan import make_generator
+    torch.manual_seed(7)
+    with _quiet():
+        g = make_generator("unet", dict(G_KW))
+    sd = {k: v.detach().clone() for k, v in g.state_dict().items()}
+    uspec, _ = _specs()
+    x, t = _u8_patch(2, 32, 42).to(DEV), _u8_patch(2, 32, 52).to(DEV)
+    yr, lr_, gr = _gpu_oracle_grads("unet", sd, uspec, x, t)
+    g = g.to(DEV)
+    with rb.precision("bf16"):
+        y = g(x)
+        loss = F.smooth_l1_loss(t, y)
+        loss.backward()
+    rel = float((y.detach().float() - yr).norm() / yr.norm())
+    assert rel <= 2e-2, rel
+    assert abs(float(loss) - lr_) <= 1e-2 * abs(lr_), (float(loss), lr_)
+    cos, ratio = _compare_grads(g, gr, 0.98, 0.05)
+    print(f"G-UNet ngf64 bf16 vs oracle: out rel-rms {rel:.3e}, loss {float(loss):.6f} vs {lr_:.6f}, worst grad cosine {cos:.4f}, "
+          f"worst norm deviation {ratio:.3e}")
+
+
+def test_nlayer_discriminator_ngf64_at_64_vs_oracle():
+    """NLayerDiscriminator (ngf 64, n_layers 3, kw 3, downsampling_kw 2: the cfg3 discriminator) on 2x1x64^3 -> (2,1,9^3):
+    LSGAN loss and every parameter gradient vs the oracle (odd extents 33 / 17 / 9, stride-2 k=2 convolutions, the
+    512 -> 1 tail on zero-padded tensor-core tiles)."""
+    import raygun_b200 as rb
+    from raygun_b200 import functional as F
+    from raygun_b200 import networks as N
+    torch.manual_seed(9)
+    with _quiet():
+        d = N.NLayerDiscriminator(3, norm_layer=IN, **D_KW)
+        N.init_weights(d, "kaiming")
+    sd = {k: v.detach().clone() for k, v in d.state_dict().items()}
+    _, dspec = _specs()
+    x = _u8_patch(2, 64, 44).to(DEV)
+    yr, lr_, gr = _gpu_oracle_grads("nld", sd, dspec, x)
+    d = d.to(DEV)
+    with rb.precision("bf16"):
+        y = d(x)
+        loss = F.mse_const_loss(y, 1.0)
+        loss.backward()
+    assert tuple(y.shape) == (2, 1, 9, 9, 9)
+    rel = float((y.detach().float() - yr).norm() / yr.norm())
+    assert rel <= 2e-2, rel
+    assert abs(float(loss) - lr_) <= 1e-2 * abs(lr_), (float(loss), lr_)
+    cos, ratio = _compare_grads(d, gr, 0.98, 0.05)
+    print(f"NLD ngf64 bf16 vs oracle: out rel-rms {rel:.3e}, loss {float(loss):.6f} vs {lr_:.6f}, worst grad cosine {cos:.4f}, "
+          f"worst norm deviation {ratio:.3e}")
+
+
+def test_one_cyclegan_step_four_losses_vs_oracle_at_64():
+    """One full LinkCycleLoss step of the cfg3 networks (2 x G-UNet + 2 x NLayerDiscriminator, ngf 64) on one 1x64^3 sample
+    pair: the four logged losses vs oracle.CycleStep (LinkCycleLoss.py:137-176 semantics) -- fp32 parity mode 1e-4
+    relative, bf16 path 1 %; then a second step (weights after one Adam update of every network) within the same bounds."""
+    import copy
+    import raygun_b200 as rb
+    from oracle import restate as O
+    from raygun_b200 import networks as N
+    from raygun_b200.cyclegan import CycleGANStep, make_generator
+    torch.manual_seed(11)
+    with _quiet():
+        nets = [make_generator("unet", dict(G_KW)) for _ in range(2)]
+        nets += [N.NLayerDiscriminator(3, norm_layer=IN, **D_KW) for _ in range(2)]
+        for d in nets[2:]:
+            N.init_weights(d, "kaiming")
+    uspec, dspec = _specs()
+    _fp32_backend()
+    sds = [{k: v.detach().clone().to(DEV) for k, v in m.state_dict().items()} for m in nets]
+    cs = O.CycleStep(*sds, g_fwd=lambda sd, x: O.generator_forward(sd, "unet", uspec, x, final_activation="Tanh"),
+                     d_fwd=lambda sd, x: O.nld3d_forward(sd, dspec, x), lr=1e-5)
+    a, b = _u8_patch(1, 64, 42).to(DEV), _u8_patch(1, 64, 43).to(DEV)
+    ref = [cs.step(a, b), cs.step(a, b)]
+    for mode, tol in (("fp32", 1e-4), ("bf16", 1e-2)):
+        mine = [m.to(DEV) for m in copy.deepcopy(nets)]
+        with rb.precision(mode):
+            step = CycleGANStep(*mine, lr=1e-5)
+            got = [step.step(a, b), step.step(a, b)]
+        for i in range(2):
+            for k in ("G1", "G2", "D1", "D2"):
+                assert abs(float(got[i][k]) - ref[i][k]) <= tol * abs(ref[i][k]), (mode, i, k, float(got[i][k]), ref[i][k])
+        print(mode, "step losses", {k: float(v) for k, v in got[0].items()}, "oracle", ref[0])
+
+
+def test_loss_curves_against_the_oracle_over_200_steps():
+    """north_star: "loss curves within 1 % over 200 steps".  200 LinkCycleLoss steps (cfg3 networks, ngf 64, lr 1e-5, four
+    32^3 sample pairs in rotation) of (a) the fp32 parity mode and (b) the bf16 tensor-core path, against the ORACLE's curve
+    (oracle.CycleStep through stock fp32 torch ops, deterministic cuDNN algorithms, TF32 off).
+
+    What is asserted, and why: GAN training amplifies perturbations exponentially, so "within 1 % at every one of 200
+    steps" is not a property of the REFERENCE against itself.  Two yardsticks are measured in the same test run:
+      Y1 = the oracle re-run with cuDNN's benchmark-selected algorithms (the reference's own setting,
+           systems/CycleGAN.py:11) -- an equally valid fp32 evaluation of the same algorithm;
+      Y2 = the oracle under torch.autocast(bfloat16) -- the reference's own reduced-precision mode.
+    Measured (profiles/r02_loss_curves.jsonl): Y1 leaves the 1 % band at step 19-44 and reaches 6-7 % per step; our
+    fp32 mode leaves it at step 28-31 and reaches 6-8 %.  Both runs of our path are bit-reproducible (asserted).
+    Bounds: * step 0: fp32 within 1e-5, bf16 within 1 % of the oracle;
+            * fp32: every loss within 1 % per step over the first 15 steps;
+            * the 200-step MEAN of every loss within 1 % + the yardstick's own deviation (Y1 for fp32, Y2 for bf16);
+            * per-step maximum and 10-step-smoothed maximum within 2x the yardstick + 1 %."""
+    from tests import loss_curves as LC
+    dev = torch.device(DEV)
+    o = LC.oracle_cyclegan_curve(200, dev)
+    y1 = LC.oracle_cyclegan_curve(200, dev, variant=1)
+    y2 = LC.oracle_cyclegan_curve(200, dev, variant=2)
+    f = LC.cyclegan_curve("fp32", 200, dev)
+    f2 = LC.cyclegan_curve("fp32", 200, dev)
+    h = LC.cyclegan_curve("bf16", 200, dev)
+    h2 = LC.cyclegan_curve("bf16", 200, dev)
+    assert f == f2 and h == h2, "two runs of the same path must produce identical loss curves"
+    report = {}
+    for k in ("G1", "G2", "D1", "D2"):
+        assert abs(f[k][0] - o[k][0]) <= 1e-5 * abs(o[k][0]), (k, f[k][0], o[k][0])
+        assert abs(h[k][0] - o[k][0]) <= 1e-2 * abs(o[k][0]), (k, h[k][0], o[k][0])
+        assert LC.deviation(o[k][:15], f[k][:15], window=1)["per_step_max_rel"] <= 1e-2, k
+        for name, mine, yard in (("fp32", f, y1), ("bf16", h, y2)):
+            d, y = LC.deviation(o[k], mine[k]), LC.deviation(o[k], yard[k])
+            report[(name, k)] = (d, y)
+            assert d["mean_rel"] <= 1e-2 + y["mean_rel"], (name, k, d, y)
+            assert d["per_step_max_rel"] <= 2 * y["per_step_max_rel"] + 1e-2, (name, k, d, y)
+            assert d["smoothed_max_rel"] <= 2 * y["smoothed_max_rel"] + 1e-2, (name, k, d, y)
+    for (name, k), (d, y) in report.items():
+        print(f"{name} {k}: mean {d['mean_rel']:.4f} (yardstick {y['mean_rel']:.4f}); per-step max {d['per_step_max_rel']:.4f} "
+              f"({y['per_step_max_rel']:.4f}); smoothed max {d['smoothed_max_rel']:.4f} ({y['smoothed_max_rel']:.4f})")
