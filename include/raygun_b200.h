@@ -264,6 +264,13 @@ int rg_upsample_nearest_fwd(const rg_tensor5* xd, const void* x, const int32_t f
 int rg_upsample_nearest_bwd(const rg_tensor5* dyd, const void* dy, const int32_t f[3], const rg_tensor5* dxd,
                             void* dx, void* stream);
 
+/* ---- sampling bottleneck (models/CycleModel.py:24-30: F.interpolate(..., mode="trilinear", align_corners=True), down by
+ *      scale_factor then back up to the original size) ---------------------------------------------------------------
+ * y = trilinear resize of x to y's spatial extents (align_corners = True); bwd = its adjoint as a deterministic gather:
+ * dx[i] = sum over the dy voxels that sampled x[i].  Any strides, f32 / bf16.                                      */
+int rg_resize_trilinear_fwd(const rg_tensor5* xd, const void* x, const rg_tensor5* yd, void* y, void* stream);
+int rg_resize_trilinear_bwd(const rg_tensor5* dyd, const void* dy, const rg_tensor5* dxd, void* dx, void* stream);
+
 /* ---- losses (losses/GANLoss.py:24-25,48-64 MSELoss vs constant label;
  *      losses/LinkCycleLoss.py:22,99-105 SmoothL1Loss / L1Loss), warp-shuffle reductions ----
  * loss[0] = scale_loss * mean(f(a, b|target)); grad_a = scale_grad * d mean/da (may be NULL).

@@ -35,7 +35,7 @@ SYMBOLS = [
     "rg_reduce_ws_floats", "rg_rows_sum", "rg_norm_stats", "rg_norm_finalize", "rg_norm_apply", "rg_norm_bwd",
     "rg_act_fwd", "rg_act_bwd", "rg_act_bwd_bias",
     "rg_maxpool3d_fwd", "rg_maxpool3d_bwd", "rg_upsample_nearest_fwd", "rg_upsample_nearest_bwd",
-    "rg_loss_fwd_grad", "rg_u8_normalise", "rg_denorm_clamp_u8", "rg_h2d_block", "rg_d2h_block", "rg_adam_step", "rg_adam_flat",
+    "rg_resize_trilinear_fwd", "rg_resize_trilinear_bwd", "rg_loss_fwd_grad", "rg_u8_normalise", "rg_denorm_clamp_u8", "rg_h2d_block", "rg_d2h_block", "rg_adam_step", "rg_adam_flat",
 ]
 
 

@@ -142,7 +142,7 @@ def _cycle_loss_fn(l1_loss):
 
 
 class CycleModel(tnn.Module):
-    """models/CycleModel.py:7-89 (sampling_bottleneck is delegated to torch's interpolate: off by default)."""
+    """models/CycleModel.py:7-89; the trilinear sampling bottleneck of 3-D models runs csrc/resize.cu (2-D: torch)."""
 
     def __init__(self, netG1, netG2, scale_factor_A=None, scale_factor_B=None, split=False, freeze_norms_at=None,
                  **kwargs):
@@ -158,6 +158,8 @@ class CycleModel(tnn.Module):
             setattr(self, k, v)
 
     def sampling_bottleneck(self, array, scale_factor):
+        if array.dim() == 5 and array.is_cuda and len(scale_factor) == 3:
+            return F.sampling_bottleneck(array, scale_factor)      # rg_resize_trilinear_fwd / _bwd (csrc/resize.cu)
         size = array.shape[-len(scale_factor):]
         mode = {2: "bilinear", 3: "trilinear"}[len(size)]
         down = tnn.functional.interpolate(array, scale_factor=scale_factor, mode=mode, align_corners=True)

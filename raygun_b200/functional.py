@@ -433,6 +433,36 @@ def upsample_nearest(x, f):
     return _UpsampleNearest.apply(x, _t3(f))
 
 
+class _ResizeTrilinear(torch.autograd.Function):
+    """F.interpolate(x, size, mode="trilinear", align_corners=True) and its adjoint (models/CycleModel.py:24-30)."""
+
+    @staticmethod
+    def forward(ctx, x, size):
+        ctx.in_size = tuple(x.shape[2:])
+        return K.resize_trilinear_fwd(x, size)
+
+    @staticmethod
+    def backward(ctx, dy):
+        return K.resize_trilinear_bwd(dy, ctx.in_size), None
+
+
+def resize_trilinear(x, size):
+    size = tuple(int(s) for s in size)
+    if tuple(x.shape[2:]) == size:
+        return x
+    return _ResizeTrilinear.apply(x, size)
+
+
+def sampling_bottleneck(x, scale_factor):
+    """CycleModel.sampling_bottleneck for a 3-D network: down by `scale_factor` (output extent floor(in * s), as
+    F.interpolate computes it), then back up to the original extents."""
+    import math
+    sf = (scale_factor,) * 3 if not isinstance(scale_factor, (tuple, list)) else tuple(scale_factor)
+    size = tuple(x.shape[2:])
+    down = tuple(max(1, int(math.floor(float(s) * float(f)))) for s, f in zip(size, sf))
+    return resize_trilinear(resize_trilinear(x, down), size)
+
+
 # ---------------------------------------------------------------------------------------------
 # crop / concat
 # ---------------------------------------------------------------------------------------------

@@ -285,6 +285,26 @@ def upsample_bwd(dy, f):
     return dx
 
 
+def resize_trilinear_fwd(x, size):
+    """F.interpolate(x, size=size, mode="trilinear", align_corners=True) (CycleModel.py:24-30)."""
+    require_device(x)
+    y = torch.empty((x.shape[0], x.shape[1], *size), dtype=x.dtype, device=x.device)
+    check(lib().rg_resize_trilinear_fwd(C.byref(t5(x)), ptr(x), C.byref(t5(y)), ptr(y), stream_ptr(x.device)),
+          "rg_resize_trilinear_fwd")
+    count_launch()
+    return y
+
+
+def resize_trilinear_bwd(dy, in_size):
+    """Adjoint of resize_trilinear_fwd: gradient w.r.t. an input of spatial extents `in_size`."""
+    require_device(dy)
+    dx = torch.empty((dy.shape[0], dy.shape[1], *in_size), dtype=dy.dtype, device=dy.device)
+    check(lib().rg_resize_trilinear_bwd(C.byref(t5(dy)), ptr(dy), C.byref(t5(dx)), ptr(dx), stream_ptr(dy.device)),
+          "rg_resize_trilinear_bwd")
+    count_launch()
+    return dx
+
+
 # --------------------------------------------------------------------------------------------
 # normalisation
 # --------------------------------------------------------------------------------------------

@@ -547,3 +547,30 @@ def test_training_pad_arenas_and_in_place_fold_match_the_copying_path():
     assert rel(y_a, yr.detach()) <= 2e-2
     for a, b in zip(g_a, gr):
         assert rel(a, b) <= 1e-1          # bf16 activations through two layers (the copying path shows the same)
+
+
+@pytest.mark.parametrize("shape,scale", [((2, 1, 16, 16, 16), (0.5, 0.5, 0.5)), ((1, 1, 20, 13, 17), (0.5, 0.75, 0.3)),
+                                         ((1, 3, 9, 8, 7), (1.0, 0.5, 0.25)), ((1, 1, 5, 6, 4), (0.2, 0.2, 0.3))])
+def test_sampling_bottleneck_trilinear_kernels_vs_interpolate(shape, scale):
+    """CycleModel.sampling_bottleneck (CycleModel.py:24-30): down by scale_factor and back up, trilinear with
+    align_corners=True, forward and adjoint (deterministic gather) vs F.interpolate / its autograd; and the CycleModel
+    mirror routes 3-D CUDA tensors through the kernels."""
+    from raygun_b200 import functional as F
+    from raygun_b200.cyclegan import CycleModel
+    dev = _dev()
+    torch.manual_seed(21)
+    x = torch.randn(*shape, device=dev, requires_grad=True)
+    xr = x.detach().clone().requires_grad_(True)
+    y = F.sampling_bottleneck(x, scale)
+    down = TF.interpolate(xr, scale_factor=scale, mode="trilinear", align_corners=True)
+    yr = TF.interpolate(down, size=shape[2:], mode="trilinear", align_corners=True)
+    _close(y, yr, 1e-5, "bottleneck fwd")
+    g = torch.randn_like(yr)
+    y.backward(g)
+    yr.backward(g)
+    _close(x.grad, xr.grad, 1e-5, "bottleneck adjoint")
+    y2 = F.sampling_bottleneck(x.detach(), scale)
+    assert torch.equal(y2, y.detach())                       # bit-reproducible
+    m = CycleModel(torch.nn.Identity(), torch.nn.Identity(), scale_factor_A=scale, scale_factor_B=scale)
+    fake_B, cycled_B, fake_A, cycled_A = m(x.detach(), x.detach())
+    assert torch.equal(fake_B, y.detach()) and torch.equal(cycled_A, fake_B)
