@@ -614,7 +614,7 @@ def bench_cyclegan(args, ctx, steps, warmup, with_cpu=True):
     from raygun_b200 import networks as N
     from raygun_b200.cyclegan import CycleGANStep, make_generator
     world, rank, dev = ctx.world, ctx.rank, ctx.dev
-    GLOBAL_BATCH, SIDE = 8, 64
+    GLOBAL_BATCH, SIDE = int(args.global_batch), 64      # BASELINE configs[2]: batch 8 (other values: scaling experiments)
     if GLOBAL_BATCH % world:
         raise SystemExit("cfg3: the global batch of 8 must divide over the ranks")
     per = GLOBAL_BATCH // world
@@ -857,6 +857,7 @@ def main():
                     help="one workload only (default: cfg4 as the headline with cfg3 and cfg2 nested)")
     ap.add_argument("--write", type=int, default=516, help="cfg4: write block size (multiple of 12); read block = write + 48")
     ap.add_argument("--volume", default="1024,2048,2048", help="cfg4: volume extents D,H,W")
+    ap.add_argument("--global-batch", type=int, default=8, help="cfg3: global batch (8 = BASELINE configs[2])")
     ap.add_argument("--no-graph", action="store_true", help="launch every kernel eagerly instead of replaying one CUDA graph")
     ap.add_argument("--no-comparator", action="store_true", help="skip the stock-PyTorch/cuDNN comparator leg")
     args = ap.parse_args()

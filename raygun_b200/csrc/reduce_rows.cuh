@@ -24,9 +24,20 @@ static __global__ void __launch_bounds__(256) rows_sum_kernel(const float* __res
   __shared__ double sh[8][33];
   const int gx = threadIdx.x & 31, ry = threadIdx.x >> 5;
   const long long g = blockIdx.x * 32LL + gx;
-  double a = 0.0;
-  if (g < groups)
-    for (int r = ry; r < rows; r += 8) a += (double)part[(long long)r * ld + g];
+  // four independent partial sums per row lane (loads in flight instead of one dependent chain), combined in a fixed order
+  double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+  if (g < groups) {
+    const float* p = part + g;
+    int r = ry;
+    for (; r + 24 < rows; r += 32) {
+      a0 += (double)p[(long long)r * ld];
+      a1 += (double)p[(long long)(r + 8) * ld];
+      a2 += (double)p[(long long)(r + 16) * ld];
+      a3 += (double)p[(long long)(r + 24) * ld];
+    }
+    for (; r < rows; r += 8) a0 += (double)p[(long long)r * ld];
+  }
+  const double a = (a0 + a1) + (a2 + a3);
   sh[ry][gx] = a;
   __syncthreads();
   if (ry == 0 && g < groups) {

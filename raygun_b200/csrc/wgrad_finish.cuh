@@ -21,7 +21,13 @@ static __global__ void halo_wgrad_finish_kernel(const float* __restrict__ ws, Hw
       const float* src = ws + ((size_t)t * cin + ci) * cout + co;
       const size_t slab = (size_t)taps * cin * cout;
       const int n_splits = splits.of_kd[t / taps_hw];
-      for (int sidx = 0; sidx < n_splits; ++sidx) a += src[sidx * slab];
+      float a1 = 0.f, a2 = 0.f, a3 = 0.f;       // four loads in flight per thread; fixed combination order
+      int sidx = 0;
+      for (; sidx + 3 < n_splits; sidx += 4) {
+        a += src[sidx * slab]; a1 += src[(sidx + 1) * slab]; a2 += src[(sidx + 2) * slab]; a3 += src[(sidx + 3) * slab];
+      }
+      for (; sidx < n_splits; ++sidx) a += src[sidx * slab];
+      a = (a + a1) + (a2 + a3);
     }
     tile[r][threadIdx.x] = a;
   }
