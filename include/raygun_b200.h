@@ -222,6 +222,16 @@ long long rg_reduce_ws_floats(long long n, long long c);
 /* out[g] (+)= sum over r < rows of part[r * groups + g], r ascending (the second stage, for partial rows the caller owns) */
 int rg_rows_sum(const float* part, int rows, long long groups, float* out, int accumulate, void* stream);
 int rg_norm_stats(const rg_tensor5* xd, const void* x, int kind, float* sum, float* sqsum, float* ws, void* stream);
+/* rg_norm_stats without a workspace argument and without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  The partial rows live in a library-owned `static __device__` array of
+ * RG_NORM_STATS_STATIC_MAX_FLOATS fp32 elements (4 MiB per GPU that loads the library, held until exit); shapes whose
+ * rg_reduce_ws_floats(N, C) exceeds that are rejected with RG_E_BADARG and a message (e.g. N = 2: C <= 439).  The device
+ * owning `x` must be current.  Every call on a device shares the array (it keeps the last call's contents; nothing in it
+ * needs clearing): calls that overlap on the GPU -- different streams without an ordering event -- RACE.  Same results as
+ * rg_norm_stats, bit for bit.                                                                                     */
+#define RG_NORM_STATS_STATIC_MAX_FLOATS (1 << 20)
+int rg_norm_stats_static(const rg_tensor5* xd, const void* x, int kind, float* sum, float* sqsum, void* stream);
 /* mean/rstd from sum/sqsum: count elements per group, biased variance, eps inside sqrt. */
 int rg_norm_finalize(const float* sum, const float* sqsum, int groups, double count, float eps,
                      float* mean, float* rstd, float* var_out, void* stream);

@@ -32,7 +32,7 @@ SYMBOLS = [
     "rg_halo_wgrad_supported", "rg_halo_wgrad_workspace_bytes", "rg_halo_wgrad",
     "rg_pw_conv_fprop", "rg_pw_conv_dgrad", "rg_pw_conv_wgrad_workspace_bytes", "rg_pw_conv_wgrad", "rg_smallcin_dgrad",
     "rg_copy5", "rg_im2col_hw", "rg_pad3d_fwd", "rg_pad3d_bwd", "rg_pad3d_fold", "rg_pad_border_fill",
-    "rg_reduce_ws_floats", "rg_rows_sum", "rg_norm_stats", "rg_norm_finalize", "rg_norm_apply", "rg_norm_bwd",
+    "rg_reduce_ws_floats", "rg_rows_sum", "rg_norm_stats", "rg_norm_stats_static", "rg_norm_finalize", "rg_norm_apply", "rg_norm_bwd",
     "rg_act_fwd", "rg_act_bwd", "rg_act_bwd_bias",
     "rg_maxpool3d_fwd", "rg_maxpool3d_bwd", "rg_upsample_nearest_fwd", "rg_upsample_nearest_bwd",
     "rg_resize_trilinear_fwd", "rg_resize_trilinear_bwd", "rg_loss_fwd_grad", "rg_u8_normalise", "rg_denorm_clamp_u8", "rg_h2d_block", "rg_d2h_block", "rg_adam_step", "rg_adam_flat",

@@ -481,6 +481,56 @@ int rg_norm_stats(const rg_tensor5* xd, const void* x, int kind, float* sum, flo
   return RG_OK;
 }
 
+// ---- rg_norm_stats_static: the same statistics with NO caller workspace and no allocation ----------------------------------
+// For callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc): the partial
+// rows of the two-stage reduction live in a file-scope device array instead of a caller-provided `ws`.  Every GPU that loads
+// the library holds RG_NORM_STATS_STATIC_MAX_FLOATS * 4 bytes (4 MiB) until exit.  In HOST code `norm_static_scratch` is only
+// a stand-in for the symbol, not a device address: its address is resolved once per device, with that device current, by
+// cudaGetSymbolAddress, and that pointer is what the kernels receive.  All calls on a device share the array: calls that
+// overlap on the GPU (two streams) race.  Nothing in it has to start at zero -- every partial row the second stage reads
+// is written by the first stage of the same call -- so stale contents of an earlier call are harmless.
+static __device__ __align__(256) float norm_static_scratch[RG_NORM_STATS_STATIC_MAX_FLOATS];
+
+static int norm_static_scratch_ptr(float** out) {
+  constexpr int MAX_DEV = 64;
+  static float* table[MAX_DEV] = {nullptr};      // one resolved address per device; written once (idempotent if raced)
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return cuda_fail(e, "rg_norm_stats_static: cudaGetDevice");
+  if (dev < 0 || dev >= MAX_DEV) { set_error("rg_norm_stats_static: device index %d out of range", dev); return RG_E_BADARG; }
+  if (!table[dev]) {
+    float* p = nullptr;
+    e = cudaGetSymbolAddress((void**)&p, norm_static_scratch);      // of the CURRENT device's copy of the symbol
+    if (e != cudaSuccess) return cuda_fail(e, "rg_norm_stats_static: cudaGetSymbolAddress");
+    if (!p) { set_error("rg_norm_stats_static: cudaGetSymbolAddress returned a null address"); return RG_E_CUDA; }
+    table[dev] = p;
+  }
+  *out = table[dev];
+  return RG_OK;
+}
+
+int rg_norm_stats_static(const rg_tensor5* xd, const void* x, int kind, float* sum, float* sqsum, void* stream) {
+  RG_CHECK_ARG(xd && x && sum && sqsum, "rg_norm_stats_static: null argument");
+  RG_CHECK_ARG(kind == RG_NORM_INSTANCE || kind == RG_NORM_BATCH, "rg_norm_stats_static: bad kind");
+  const long long need = red_ws_floats(xd->n, xd->c);
+  RG_CHECK_ARG(xd->n >= 0 && xd->c >= 0 && need <= (long long)RG_NORM_STATS_STATIC_MAX_FLOATS,
+               "rg_norm_stats_static: N = %lld, C = %lld needs %lld floats of scratch, the built-in array holds %lld "
+               "(use rg_norm_stats with a caller workspace)", (long long)xd->n, (long long)xd->c, need,
+               (long long)RG_NORM_STATS_STATIC_MAX_FLOATS);
+  if (view(xd).numel() == 0) return RG_OK;
+  float* ws = nullptr;
+  int rc = norm_static_scratch_ptr(&ws);
+  if (rc) return rc;
+  NormCtx cx{kind, RG_ACT_NONE, 0.f, nullptr, nullptr, nullptr};
+  cudaStream_t st = (cudaStream_t)stream;
+  RG_DISPATCH_FLOAT(xd->dtype, TX, {
+    rc = launch_reduce2<0, TX, TX>(cx, xd, (const TX*)x, nullptr, nullptr, nullptr, nullptr, sum, sqsum, ws, st);
+  })
+  if (rc) return rc;
+  RG_LAUNCH_CHECK("rg_norm_stats_static");
+  return RG_OK;
+}
+
 int rg_norm_finalize(const float* sum, const float* sqsum, int groups, double count, float eps, float* mean,
                      float* rstd, float* var_out, void* stream) {
   RG_CHECK_ARG(sum && sqsum && mean && rstd && groups > 0 && count > 0, "rg_norm_finalize: bad argument");
