@@ -18,6 +18,13 @@ else
     python scripts/ncu_targets.py $2 > $O/r02_$1_plain.log 2>&1 && \
     $NCU --set full ${6:-} -k regex:$5 -s $3 -c $4 -o $O/r02_ncu_full_$1 -f python scripts/ncu_targets.py $2 > $O/r02_ncu_full_$1.log 2>&1
     echo "$1 rc=$?"
+    # gpurun copies back at most 64 MiB: condense the report on the box (metrics; top stall lines where the source was
+    # imported) and drop it
+    if [ -f $O/r02_ncu_full_$1.ncu-rep ]; then
+      python scripts/ncu_summary.py $O/r02_ncu_full_$1.ncu-rep --json > $O/r02_ncu_full_$1_summary.txt 2>&1
+      if [ -n "${6:-}" ]; then python scripts/ncu_top.py $O/r02_ncu_full_$1.ncu-rep 30 > $O/r02_ncu_full_$1_top.txt 2>&1; fi
+      rm -f $O/r02_ncu_full_$1.ncu-rep
+    fi
   }
   run ring_cfg4      "cfg4block 256"   7 4 ring_conv "--import-source on"
   run igemm_cfg2     cfg2step        114 8 igemm_conv "--import-source on"
