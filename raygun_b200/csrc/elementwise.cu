@@ -272,38 +272,49 @@ __global__ void __launch_bounds__(256) pad_fold_kernel(T5 gd, __nv_bfloat16* __r
   const long long rows = gd.n * D * H;
   const int ncand = (lo_w + 1) + (hi_w + 1);            // w candidates of a row with a single (d, h) pre-image
   const bool edge_only_ok = ncand < W;
-  // one WARP per interior row: most rows only own their few edge voxels (ncand * cg 16-byte items)
-  const int lane = threadIdx.x & 31, warps = blockDim.x >> 5;
-  for (long long row = (long long)blockIdx.x * warps + (threadIdx.x >> 5); row < rows; row += (long long)gridDim.x * warps) {
-    const int h = (int)(row % H);
-    const long long t = row / H;
-    const int d = (int)(t % D);
-    const long long n = t / D;
-    const int nd = pad_npre(d, lo_d, hi_d, D, mode), nh = pad_npre(h, lo_h, hi_h, H, mode);
-    const bool full = (nd * nh > 1) || !edge_only_ok;
-    const int items = (full ? W : ncand) * cg;
-    __nv_bfloat16* base = g + n * gd.sn;
-    for (int j = lane; j < items; j += 32) {
-      const int wi = j / cg, c = (j - wi * cg) << 3;
-      const int w = full ? wi : (wi <= lo_w ? wi : W - 1 - hi_w + (wi - lo_w - 1));
-      const int nw = pad_npre(w, lo_w, hi_w, W, mode);
-      if (nd * nh * nw == 1) continue;
-      float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-      for (int a = 0; a < nd; ++a) {
-        const long long od = pad_pre(d, a, lo_d, hi_d, D, mode);
-        for (int b = 0; b < nh; ++b) {
-          const long long oh = pad_pre(h, b, lo_h, hi_h, H, mode);
-          const __nv_bfloat16* srow = base + od * gd.sd + oh * gd.sh + c;
-          for (int e = 0; e < nw; ++e) {
-            const long long ow = pad_pre(w, e, lo_w, hi_w, W, mode);
-            float v[8];
-            ld8(srow + ow * gd.sw, v);
+  // A block owns 8 consecutive interior rows.  Most rows only own their few edge voxels (ncand * cg 16-byte items): one WARP
+  // takes such a row.  A row with more than one (d, h) pre-image (d or h next to a face: whole planes of them) owns all W * cg
+  // items: the whole BLOCK splits it -- with one warp per row these rows took 16x longer than their neighbours and set the
+  // kernel's duration (0.65-0.9 TB/s under ncu).
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, warps = blockDim.x >> 5;
+  auto fold_item = [&](__nv_bfloat16* base, int d, int h, int nd, int nh, bool full, int j) {
+    const int wi = j / cg, c = (j - wi * cg) << 3;
+    const int w = full ? wi : (wi <= lo_w ? wi : W - 1 - hi_w + (wi - lo_w - 1));
+    const int nw = pad_npre(w, lo_w, hi_w, W, mode);
+    if (nd * nh * nw == 1) return;
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int a = 0; a < nd; ++a) {
+      const long long od = pad_pre(d, a, lo_d, hi_d, D, mode);
+      for (int b = 0; b < nh; ++b) {
+        const long long oh = pad_pre(h, b, lo_h, hi_h, H, mode);
+        const __nv_bfloat16* srow = base + od * gd.sd + oh * gd.sh + c;
+        for (int e = 0; e < nw; ++e) {
+          const long long ow = pad_pre(w, e, lo_w, hi_w, W, mode);
+          float v[8];
+          ld8(srow + ow * gd.sw, v);
 #pragma unroll
-            for (int k = 0; k < 8; ++k) acc[k] += v[k];
-          }
+          for (int k = 0; k < 8; ++k) acc[k] += v[k];
         }
       }
-      st8(base + (long long)(d + lo_d) * gd.sd + (long long)(h + lo_h) * gd.sh + (long long)(w + lo_w) * gd.sw + c, acc);
+    }
+    st8(base + (long long)(d + lo_d) * gd.sd + (long long)(h + lo_h) * gd.sh + (long long)(w + lo_w) * gd.sw + c, acc);
+  };
+  for (long long row0 = (long long)blockIdx.x * warps; row0 < rows; row0 += (long long)gridDim.x * warps) {
+    for (int r = 0; r < warps; ++r) {
+      const long long row = row0 + r;
+      if (row >= rows) break;
+      const int h = (int)(row % H);
+      const long long t = row / H;
+      const int d = (int)(t % D);
+      const long long n = t / D;
+      const int nd = pad_npre(d, lo_d, hi_d, D, mode), nh = pad_npre(h, lo_h, hi_h, H, mode);
+      const bool full = (nd * nh > 1) || !edge_only_ok;
+      __nv_bfloat16* base = g + n * gd.sn;
+      if (full) {
+        for (int j = threadIdx.x; j < W * cg; j += blockDim.x) fold_item(base, d, h, nd, nh, true, j);
+      } else if (warp == r) {
+        for (int j = lane; j < ncand * cg; j += 32) fold_item(base, d, h, nd, nh, false, j);
+      }
     }
   }
 }

@@ -331,7 +331,7 @@ static int launch_reduce2(const NormCtx& cx, const rg_tensor5* xd, const TX* x, 
   if (dense_ok(xd, x) && dense_cg_ok(xd) && xv.n <= 65535 &&
       (MODE == 0 || (dense_ok(gd, dy) && (cx.act == RG_ACT_NONE || dense_ok(yd, y))))) {
     dim3 grid;
-    DenseGeom gm = dense_geom(xd, &grid, 48);
+    DenseGeom gm = dense_geom(xd, &grid, 16);     // >= 16 voxels per voxel lane (48 left 1 block per SM on 32^3 maps)
     if (MODE) { gm.gn = gd->sn; if (yd) gm.yn = yd->sn; }
     dense_reduce2_kernel<MODE><<<grid, 256, 0, st>>>(cx, gm, (const __nv_bfloat16*)x, (const __nv_bfloat16*)dy,
                                                      (const __nv_bfloat16*)y, ro);
@@ -650,7 +650,7 @@ int rg_act_bwd_bias(const rg_tensor5* yd, const void* y, const rg_tensor5* dyd, 
                    "rg_act_bwd_bias: needs bf16 NDHWC tensors with C %% 8 == 0 and 256 %% (C/8) == 0");
     const long long rows = yd->n * yd->d * yd->h;
     long long rpb = (rows + 148LL * 8 - 1) / (148LL * 8);
-    const long long min_rpb = (48LL * lanes_v + yd->w - 1) / yd->w;
+    const long long min_rpb = (12LL * lanes_v + yd->w - 1) / yd->w;     // >= 12 voxels per voxel lane
     if (rpb < min_rpb) rpb = min_rpb;
     const long long blocks = (rows + rpb - 1) / rpb;
     row_act_bwd_sum_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(act, slope, cg, lanes_v, view(yd), view(dyd), view(dxd),
@@ -662,7 +662,7 @@ int rg_act_bwd_bias(const rg_tensor5* yd, const void* y, const rg_tensor5* dyd, 
   RG_UNSUPPORTED(!dense_cg_ok(yd), "rg_act_bwd_bias: needs C %% 8 == 0 and 256 %% (C/8) == 0");
   long long blocks = 148LL * 8;
   long long vpb = (vox + blocks - 1) / blocks;
-  const long long min_vpb = 48LL * lanes_v;                 // fat blocks: a fixed smem reduction tail per block
+  const long long min_vpb = 16LL * lanes_v;                 // a fixed smem reduction tail per block: >= 16 voxels per lane
   if (vpb < min_vpb) vpb = min_vpb;
   vpb = (vpb + lanes_v - 1) / lanes_v * lanes_v;
   blocks = (vox + vpb - 1) / vpb;

@@ -20,28 +20,35 @@ from ._C import (ACT_NONE, NORM_BATCH, NORM_INSTANCE, PAD_REFLECT, PAD_REPLICATE
 # --------------------------------------------------------------------------------------------
 # precision mode
 # --------------------------------------------------------------------------------------------
-_state = threading.local()
+# The mode is PROCESS-global, not thread-local: autograd executes backward on its own per-device worker thread, and the
+# backward-side dispatch (conv_wgrad / conv_dgrad choose tensor-core, pointwise or direct kernels by mode) must see the mode
+# the forward ran in.  (It was thread-local until round 2: inside `with precision("fp32")` the backward thread saw the
+# default "bf16" and took bf16 weight-gradient paths for eligible layers.)
+_precision = None
 
 
 def get_precision() -> str:
     """'bf16' (tensor-core path, bf16 NDHWC activations) or 'fp32' (CUDA-core parity path)."""
-    return getattr(_state, "precision", None) or os.environ.get("RAYGUN_B200_PRECISION", "bf16")
+    return _precision or os.environ.get("RAYGUN_B200_PRECISION", "bf16")
 
 
 def set_precision(p: str):
+    global _precision
     if p not in ("bf16", "fp32"):
         raise ValueError(f"precision must be 'bf16' or 'fp32', got {p!r}")
-    _state.precision = p
+    _precision = p
 
 
 @contextlib.contextmanager
 def precision(p: str):
-    old = getattr(_state, "precision", None)
+    """`with precision("fp32"):` -- forward AND the backward calls made inside the block run in mode `p`."""
+    global _precision
+    old = _precision
     set_precision(p)
     try:
         yield
     finally:
-        _state.precision = old
+        _precision = old
 
 
 def use_tensor_cores() -> bool:

@@ -574,3 +574,33 @@ def test_sampling_bottleneck_trilinear_kernels_vs_interpolate(shape, scale):
     m = CycleModel(torch.nn.Identity(), torch.nn.Identity(), scale_factor_A=scale, scale_factor_B=scale)
     fake_B, cycled_B, fake_A, cycled_A = m(x.detach(), x.detach())
     assert torch.equal(fake_B, y.detach()) and torch.equal(cycled_A, fake_B)
+
+
+@pytest.mark.parametrize("cin,cout", [(8, 3), (64, 1), (64, 64)])
+def test_fp32_mode_reaches_the_backward_thread(cin, cout):
+    """autograd runs backward on its own worker thread: the precision mode must be visible there.  Regression: with a
+    thread-local mode, `with precision("fp32")` still dispatched the weight gradient of pointwise-eligible (<= 4 output channels)
+    and tensor-core-eligible (64-multiple channels) layers to the bf16 kernels -- an error of ~2e-3 relative."""
+    import raygun_b200 as rb
+    from raygun_b200 import conv as CV
+    from raygun_b200.networks.UNet import ConvPass
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    dev = _dev()
+    torch.manual_seed(4)
+    k = [[1, 1, 1]] if cout < 64 else [[3, 3, 3]]
+    head = ConvPass(cin, cout, k, activation="Sigmoid").to(dev)
+    ref = torch.nn.Sequential(torch.nn.Conv3d(cin, cout, k[0]), torch.nn.Sigmoid()).to(dev)
+    ref[0].load_state_dict(head.conv_pass[0].state_dict())
+    x = torch.randn(1, cin, 10, 10, 10, device=dev)
+    xo, xr = x.clone().requires_grad_(True), x.clone().requires_grad_(True)
+    before = dict(CV.stats)
+    with rb.precision("fp32"):
+        yo = head(xo)
+        g = torch.randn_like(yo)
+        (yo * g).sum().backward()
+    (ref(xr) * g).sum().backward()
+    assert CV.stats.get("igemm", 0) == before.get("igemm", 0) and CV.stats.get("pointwise", 0) == before.get("pointwise", 0)
+    _close(head.conv_pass[0].weight.grad, ref[0].weight.grad, TOL, "dw")
+    _close(head.conv_pass[0].bias.grad, ref[0].bias.grad, TOL, "db")
+    _close(xo.grad, xr.grad, TOL, "dx")
