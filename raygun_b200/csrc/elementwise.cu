@@ -266,7 +266,7 @@ __global__ void __launch_bounds__(256) row_pad_bwd_kernel(T5 gd, const __nv_bflo
 // of the read + write of the whole volume an explicit adjoint copy costs (the backward twin of border_fill_kernel).
 // Only voxels with more than one pre-image are rewritten; every other pre-image of such a voxel lies in the shell,
 // which is never written, so the gather is race-free and deterministic.  One block per interior row (n, d, h).
-__global__ void __launch_bounds__(256) pad_fold_kernel(T5 gd, __nv_bfloat16* __restrict__ g, int lo_d, int lo_h, int lo_w,
+__global__ void __launch_bounds__(256, 4) pad_fold_kernel(T5 gd, __nv_bfloat16* __restrict__ g, int lo_d, int lo_h, int lo_w,
                                                        int hi_d, int hi_h, int hi_w, int mode) {
   const int D = (int)gd.d - lo_d - hi_d, H = (int)gd.h - lo_h - hi_h, W = (int)gd.w - lo_w - hi_w, cg = (int)(gd.c >> 3);
   const long long rows = gd.n * D * H;
@@ -300,21 +300,24 @@ __global__ void __launch_bounds__(256) pad_fold_kernel(T5 gd, __nv_bfloat16* __r
     st8(base + (long long)(d + lo_d) * gd.sd + (long long)(h + lo_h) * gd.sh + (long long)(w + lo_w) * gd.sw + c, acc);
   };
   for (long long row0 = (long long)blockIdx.x * warps; row0 < rows; row0 += (long long)gridDim.x * warps) {
-    for (int r = 0; r < warps; ++r) {
-      const long long row = row0 + r;
-      if (row >= rows) break;
-      const int h = (int)(row % H);
-      const long long t = row / H;
-      const int d = (int)(t % D);
-      const long long n = t / D;
+    // one 64-bit decode per block; the 8 rows step (h, d, n) incrementally
+    int h = (int)(row0 % H);
+    const long long t0 = row0 / H;
+    int d = (int)(t0 % D);
+    long long n = t0 / D;
+    const int nrows = (int)min((long long)warps, rows - row0);
+    for (int r = 0; r < nrows; ++r) {
       const int nd = pad_npre(d, lo_d, hi_d, D, mode), nh = pad_npre(h, lo_h, hi_h, H, mode);
       const bool full = (nd * nh > 1) || !edge_only_ok;
-      __nv_bfloat16* base = g + n * gd.sn;
-      if (full) {
-        for (int j = threadIdx.x; j < W * cg; j += blockDim.x) fold_item(base, d, h, nd, nh, true, j);
-      } else if (warp == r) {
-        for (int j = lane; j < ncand * cg; j += 32) fold_item(base, d, h, nd, nh, false, j);
+      if (full || warp == r) {
+        __nv_bfloat16* base = g + n * gd.sn;
+        if (full) {
+          for (int j = threadIdx.x; j < W * cg; j += blockDim.x) fold_item(base, d, h, nd, nh, true, j);
+        } else {
+          for (int j = lane; j < ncand * cg; j += 32) fold_item(base, d, h, nd, nh, false, j);
+        }
       }
+      if (++h == H) { h = 0; if (++d == D) { d = 0; ++n; } }
     }
   }
 }

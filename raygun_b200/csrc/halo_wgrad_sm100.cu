@@ -400,9 +400,7 @@ int rg_halo_wgrad(const rg_igemm_desc* d, const void* x, const void* dy, float* 
     if (rc) return rc;
     RG_LAUNCH_CHECK("rg_halo_wgrad");
   }
-  dim3 fg((d->cout + 31) / 32, d->cin, (taps + 31) / 32);
-  halo_wgrad_finish_kernel<<<fg, dim3(32, 8), 0, st>>>((const float*)workspace, splits, p.kh * p.kw, taps, d->cin, d->cout, dw,
-                                                      accumulate);
+  wgrad_finish_launch((const float*)workspace, splits, p.kh * p.kw, taps, d->cin, d->cout, dw, accumulate, st);
   RG_LAUNCH_CHECK("rg_halo_wgrad(finish)");
   return RG_OK;
 }

@@ -820,9 +820,7 @@ int rg_igemm_wgrad(const rg_plan* pl, const void* x, const void* dy, float* dw, 
   RG_LAUNCH_CHECK("rg_igemm_wgrad");
   HwSplits splits;
   for (int i = 0; i < 8; ++i) splits.of_kd[i] = p.n_splits;
-  dim3 fg((d.cout + 31) / 32, d.cin, (pl->taps + 31) / 32);
-  halo_wgrad_finish_kernel<<<fg, dim3(32, 8), 0, st>>>((const float*)workspace, splits, d.kernel[1] * d.kernel[2], pl->taps, d.cin,
-                                                      d.cout, dw, accumulate);
+  wgrad_finish_launch((const float*)workspace, splits, d.kernel[1] * d.kernel[2], pl->taps, d.cin, d.cout, dw, accumulate, st);
   RG_LAUNCH_CHECK("rg_igemm_wgrad(finish)");
   return RG_OK;
 }
