@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define RG_VERSION 200
+#define RG_VERSION 201
 
 enum { RG_OK = 0, RG_E_BADARG = -1, RG_E_UNSUPPORTED = -2, RG_E_CUDA = -3, RG_E_ARCH = -4 };
 enum { RG_F32 = 0, RG_BF16 = 1, RG_U8 = 2 };
@@ -129,6 +129,15 @@ int rg_ring_pack_weights(const float* w, int cout, int cin, const int* kernel3, 
 size_t rg_ring_workspace_bytes(const rg_igemm_desc* desc);     /* needed only when statistics are requested */
 int rg_ring_run(const rg_igemm_desc* desc, const void* in, const void* w_ring, const float* bias, void* out,
                 float* stats_sum, float* stats_sqsum, void* workspace, void* stream);
+/* The generator's last convolution with the network head folded into its epilogue (BaseSystem.py:209-224:
+ * Sequential(net, Conv3d(ngf -> output_nc, 1), final_activation); UNet.py:52-87 for the producing ConvPass layer):
+ *   head_out[n, o, d, h, w] = head_act(head_b[o] + sum_c head_w[o][c] * bf16(act(conv(in) + bias)[n, c, d, h, w]))
+ * `desc` describes the producing layer (mode 0, cout == 64, its activation in desc->act); its 64-channel output is
+ * never written.  head_w fp32 [head_n][64] (16-byte aligned), head_b fp32 [head_n] or NULL, 1 <= head_n <= 4;
+ * head_out bf16, channels innermost, element strides head_strides = {n, d, h, w}.  Inference only.            */
+int rg_ring_run_head(const rg_igemm_desc* desc, const void* in, const void* w_ring, const float* bias,
+                     const float* head_w, const float* head_b, int head_n, int head_act, float head_slope,
+                     void* head_out, const int64_t* head_strides, void* stream);
 
 /* ---- small-K stem convolution (stem_conv_sm100.cu) ---------------------------------------------------------
  * Forward of a stride-1 Conv3d whose whole reduction Cin*kD*kH*kW is <= 64 (the 1 -> ngf 3^3 convolution that

@@ -257,6 +257,48 @@ def _ring_desc(mode, n, cin, cout, in_dhw, out_dhw, kernel, stride, pad, xs, ys,
 
 
 STEM_DIRECT = os.environ.get("RAYGUN_B200_STEM_DIRECT", "1") != "0"
+FUSE_HEAD = os.environ.get("RAYGUN_B200_FUSE_HEAD", "1") != "0"
+
+
+class HeadRequest:
+    """The generator's head -- Conv3d(ngf -> output_nc, 1x1x1) [+ activation] (BaseSystem.py:209-224) -- offered to the
+    convolution that produces its input (`weight` identifies that layer).  When that layer runs on the slice-ring kernel
+    under no_grad, its epilogue reduces every voxel's 64 activated channels against the head weights and only the head's
+    output leaves the SM (rg_ring_run_head): the 64-channel tensor is neither written nor read back.  `done` tells the
+    caller whether the head was consumed; if not it runs the head layers itself."""
+
+    def __init__(self, weight, head_w, head_b, act=ACT_NONE, slope=0.0):
+        self.weight, self.head_w, self.head_b, self.act, self.slope = weight, head_w, head_b, act, float(slope)
+        self.done = False
+
+
+_head_request: "HeadRequest | None" = None
+
+
+class offer_head:
+    """Context manager: `with offer_head(HeadRequest(...)) as h: y = net(x)`; afterwards h.done."""
+
+    def __init__(self, req):
+        self.req = req
+
+    def __enter__(self):
+        global _head_request
+        self.prev, _head_request = _head_request, self.req
+        return self.req
+
+    def __exit__(self, *exc):
+        global _head_request
+        _head_request = self.prev
+        return False
+
+
+def _take_head(w, cout, want_stats, out):
+    h = _head_request
+    if (h is None or h.done or not FUSE_HEAD or torch.is_grad_enabled() or want_stats or out is not None or cout != 64
+            or not isinstance(w, torch.Tensor) or w.data_ptr() != h.weight.data_ptr() or w.shape != h.weight.shape
+            or not 1 <= h.head_w.shape[0] <= 4 or h.head_w.shape[1] != 64):
+        return None
+    return h
 
 
 def stem_direct_ok(w, want_stats):
@@ -447,6 +489,28 @@ def conv_fprop(x, w, bias, stride, pad, groups=1, act=ACT_NONE, slope=0.0, want_
 
     if _igemm_ok(cin_t, cout, kernel, stride, groups) and cdt == torch.bfloat16:
         xb = K.conv_operand(x)
+        head = _take_head(w, cout, want_stats, out)
+        if head is not None:
+            # strides of the (never materialised) 64-channel output only select the kernel; use the dense layout
+            rd = _ring_desc(0, n, cin_t, cout, (d, h, wd_), od, kernel, stride, pad, _sp_strides(xb),
+                            (od[0] * od[1] * od[2] * cout, od[1] * od[2] * cout, od[2] * cout, cout), act, float(slope))
+            if rd is not None:
+                hn = head.head_w.shape[0]
+                yh = K.empty5((n, hn, *od), torch.bfloat16, x.device)
+                hw = _src(head.head_w).fp32().reshape(hn, 64)
+                hb = head.head_b.detach() if head.head_b is not None else None
+                hs = (C.c_int64 * 4)(*_sp_strides(yh))
+                with _Timed("fprop", 2.0 * n * od[0] * od[1] * od[2] * cout * (cin_t * kernel[0] * kernel[1] * kernel[2] + hn),
+                            x.device, "ring_conv_kernel"):
+                    check(lib().rg_ring_run_head(C.byref(rd), ptr(xb), ptr(ring_packed_weights(w, 0)), ptr(bias_f), ptr(hw),
+                                                 ptr(hb), C.c_int(hn), C.c_int(head.act), C.c_float(head.slope), ptr(yh), hs,
+                                                 stream_ptr(x.device)), "rg_ring_run_head")
+                count_launch()
+                stats["igemm"] += 1
+                stats["ring"] = stats.get("ring", 0) + 1
+                stats["ring_head"] = stats.get("ring_head", 0) + 1
+                head.done = True
+                return yh, None, None
         y = _alloc(torch.bfloat16)
         rd = _ring_desc(0, n, cin_t, cout, (d, h, wd_), od, kernel, stride, pad, _sp_strides(xb), _sp_strides(y),
                         act, float(slope))

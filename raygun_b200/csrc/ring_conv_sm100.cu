@@ -36,7 +36,11 @@ constexpr int STAGE_KD = 4;               // kd blocks per weight stage (<= 256 
 constexpr int RING_TH = 16, RING_TW = 8;  // output tile (h, w); 8 = one swizzle-atom row group
 constexpr int MAX_NA = 12, MAX_NB = 4;
 constexpr int MAX_GS = 4;                                           // slices per group (S) the MMA warp unrolls
-constexpr int RING_TAIL_BYTES = 8 * (2 * MAX_NA + 2 * MAX_NB + 4) + 64;
+constexpr int RING_HEAD_MAX = 4;                                     // output channels of a fused 1x1x1 head
+constexpr int RING_BAR_BYTES = 8 * (2 * MAX_NA + 2 * MAX_NB + 4) + 64;
+constexpr int RING_HEAD_W_BYTES = RING_HEAD_MAX * 64 * 4;           // head weights [o][64] fp32
+constexpr int RING_HEAD_X_BYTES = 4 * 2 * 32 * RING_HEAD_MAX * 4;   // partial dots: [quad][plane parity][lane][o]
+constexpr int RING_TAIL_BYTES = RING_BAR_BYTES + RING_HEAD_W_BYTES + RING_HEAD_X_BYTES;
 
 struct alignas(64) RingParams {
   CUtensorMap a_map;      // 5-D {C, W, H, D, N}; box {64, WB, HB, 1, 1}
@@ -60,6 +64,13 @@ struct alignas(64) RingParams {
   const float* bias;
   float* stats_part;      // partial rows [4 * gridDim.x][2 * stats_G]: row = 4 * CTA + TMEM lane quadrant (reduce_rows.cuh)
   long long stats_G;      // batch * cout_total
+  // fused 1x1x1 head behind a 64-channel layer (rg_ring_run_head): the activated, bf16-rounded channels of a voxel are
+  // reduced against head_w in the epilogue and only head_n values per voxel leave the SM (y is not written)
+  const float* head_w;    // [head_n][64] fp32, nullptr = no head
+  const float* head_b;    // [head_n] or nullptr
+  int head_n, head_act; float head_slope;
+  __nv_bfloat16* head_y;
+  long long hs_n, hs_d, hs_h, hs_w;
 };
 
 struct RingUnit { int nt, n, h0, w0, d0, len, z_begin, z_end, zg0; };
@@ -137,6 +148,8 @@ __global__ void __launch_bounds__(RING_THREADS, 1) ring_conv_kernel(const __grid
   uint8_t* tail = base_ptr + (size_t)p.na * p.slice_bytes + (size_t)p.nb * p.stage_bytes;
   uint64_t* bars = reinterpret_cast<uint64_t*>(tail);     // afull[na] aempty[na] bfull[nb] bempty[nb] tfull[2] tempty[2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tail + 8 * (2 * MAX_NA + 2 * MAX_NB + 4));
+  float* head_ws = reinterpret_cast<float*>(tail + RING_BAR_BYTES);
+  float* head_xs = reinterpret_cast<float*>(tail + RING_BAR_BYTES + RING_HEAD_W_BYTES);
   const uint32_t bar0 = ptx::smem_u32(bars);
   auto afull = [&](int s) { return bar0 + 8u * s; };
   auto aempty = [&](int s) { return bar0 + 8u * (MAX_NA + s); };
@@ -158,6 +171,8 @@ __global__ void __launch_bounds__(RING_THREADS, 1) ring_conv_kernel(const __grid
     ptx::prefetch_tmap(&p.b_map);
   }
   if (warp == 1) ptx::tmem_alloc<512>(ptx::smem_u32(tmem_slot));
+  if (p.head_w)
+    for (int i = threadIdx.x; i < p.head_n * 64; i += RING_THREADS) head_ws[i] = p.head_w[i];
   ptx::tc_fence_before();
   __syncthreads();
   ptx::tc_fence_after();
@@ -354,6 +369,8 @@ __global__ void __launch_bounds__(RING_THREADS, 1) ring_conv_kernel(const __grid
       st_row[p.stats_G + c] += st_sq;
       st_sum = st_sq = 0.f;
     };
+    const bool has_head = p.head_w != nullptr;
+    uint32_t head_plane = 0;                    // planes this warp pair has drained (parity selects the exchange buffer)
     int g = 0;
     RingUnit r;
     for (RingWalk walk(p); walk.next(p, r);) {
@@ -411,7 +428,41 @@ __global__ void __launch_bounds__(RING_THREADS, 1) ring_conv_kernel(const __grid
             __nv_bfloat162 h2 = __floats2bfloat162_rn(valid ? f[c] : 0.f, valid ? f[c + 1] : 0.f);
             pk[c >> 1] = *reinterpret_cast<uint32_t*>(&h2);
           }
-          if (valid) {
+          if (has_head) {
+            // thread = voxel: dot of this warp's 32 (bf16-rounded, as the unfused layer would have stored them) channels
+            // with the head weights; the upper-half warp hands its partial sums to the lower-half warp of the same
+            // lane quadrant through shared memory (one named barrier per plane, buffers alternate by plane parity)
+            float hacc[RING_HEAD_MAX];
+#pragma unroll
+            for (int o = 0; o < RING_HEAD_MAX; ++o) {
+              hacc[o] = 0.f;
+              if (o < p.head_n) {
+                const float4* w4 = reinterpret_cast<const float4*>(head_ws + o * 64 + half * 32);
+#pragma unroll
+                for (int c = 0; c < 32; c += 4) {
+                  const float4 wv = w4[c >> 2];
+                  const float2 x0 = __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&pk[c >> 1]));
+                  const float2 x1 = __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&pk[(c >> 1) + 1]));
+                  hacc[o] = fmaf(x0.x, wv.x, hacc[o]); hacc[o] = fmaf(x0.y, wv.y, hacc[o]);
+                  hacc[o] = fmaf(x1.x, wv.z, hacc[o]); hacc[o] = fmaf(x1.y, wv.w, hacc[o]);
+                }
+              }
+            }
+            float* xch = head_xs + ((quad * 2 + (int)(head_plane & 1u)) * 32 + lane) * RING_HEAD_MAX;
+            if (half == 1) *reinterpret_cast<float4*>(xch) = make_float4(hacc[0], hacc[1], hacc[2], hacc[3]);
+            asm volatile("bar.sync %0, 64;" ::"r"(1 + quad) : "memory");
+            if (half == 0 && valid) {
+              const float4 up = *reinterpret_cast<const float4*>(xch);
+              __nv_bfloat16* hdst = p.head_y + (size_t)r.n * p.hs_n + (size_t)d * p.hs_d + (size_t)oh * p.hs_h + (size_t)ow * p.hs_w;
+#pragma unroll
+              for (int o = 0; o < RING_HEAD_MAX; ++o)
+                if (o < p.head_n) {
+                  const float other = o == 0 ? up.x : (o == 1 ? up.y : (o == 2 ? up.z : up.w));
+                  hdst[o] = __float2bfloat16_rn(act_apply(hacc[o] + other + (p.head_b ? p.head_b[o] : 0.f), p.head_act, p.head_slope));
+                }
+            }
+            ++head_plane;
+          } else if (valid) {
             uint4* dst = reinterpret_cast<uint4*>(ybase + (size_t)d * p.ys_d);
 #pragma unroll
             for (int j = 0; j < 4; ++j) dst[j] = make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
@@ -633,11 +684,14 @@ size_t rg_ring_workspace_bytes(const rg_igemm_desc* d) {
   return (size_t)4 * ring_num_sms() * 2 * d->n * rows * sizeof(float);
 }
 
-int rg_ring_run(const rg_igemm_desc* d, const void* in, const void* w_ring, const float* bias, void* out, float* stats_sum,
-                float* stats_sqsum, void* workspace, void* stream) {
-  RG_CHECK_ARG(d && in && w_ring && out, "rg_ring_run: null argument");
-  RG_CHECK_ARG((stats_sum == nullptr) == (stats_sqsum == nullptr), "rg_ring_run: stats pointers must come together");
-  RG_CHECK_ARG(!stats_sum || workspace, "rg_ring_run: statistics need rg_ring_workspace_bytes() of workspace");
+}  // extern "C"
+
+namespace rg {
+struct RingHead { const float* w; const float* b; int n, act; float slope; void* out; const int64_t* strides; };
+}
+
+static int ring_run(const rg_igemm_desc* d, const void* in, const void* w_ring, const float* bias, void* out, float* stats_sum,
+                    float* stats_sqsum, void* workspace, const rg::RingHead* head, void* stream) {
   RingGeom g;
   int rc = ring_geometry(d, &g);
   if (rc) return rc;
@@ -668,6 +722,11 @@ int rg_ring_run(const rg_igemm_desc* d, const void* in, const void* w_ring, cons
   }
   p.y = (__nv_bfloat16*)out;
   p.bias = bias;
+  if (head) {
+    p.head_w = head->w; p.head_b = head->b; p.head_n = head->n; p.head_act = head->act; p.head_slope = head->slope;
+    p.head_y = (__nv_bfloat16*)head->out;
+    p.hs_n = head->strides[0]; p.hs_d = head->strides[1]; p.hs_h = head->strides[2]; p.hs_w = head->strides[3];
+  }
   p.stats_part = stats_sum ? (float*)workspace : nullptr;
   p.stats_G = (long long)d->n * g.rows;
   if (stats_sum) {
@@ -690,6 +749,27 @@ int rg_ring_run(const rg_igemm_desc* d, const void* in, const void* w_ring, cons
     return launch_rows_sum((const float*)workspace, 4 * ring_num_sms(), 2 * p.stats_G, 2 * p.stats_G, stats_sum, stats_sqsum,
                            p.stats_G, 0, 1.0, (cudaStream_t)stream);
   return RG_OK;
+}
+
+extern "C" {
+
+int rg_ring_run(const rg_igemm_desc* d, const void* in, const void* w_ring, const float* bias, void* out, float* stats_sum,
+                float* stats_sqsum, void* workspace, void* stream) {
+  RG_CHECK_ARG(d && in && w_ring && out, "rg_ring_run: null argument");
+  RG_CHECK_ARG((stats_sum == nullptr) == (stats_sqsum == nullptr), "rg_ring_run: stats pointers must come together");
+  RG_CHECK_ARG(!stats_sum || workspace, "rg_ring_run: statistics need rg_ring_workspace_bytes() of workspace");
+  return ring_run(d, in, w_ring, bias, out, stats_sum, stats_sqsum, workspace, nullptr, stream);
+}
+
+int rg_ring_run_head(const rg_igemm_desc* d, const void* in, const void* w_ring, const float* bias, const float* head_w,
+                     const float* head_b, int head_n, int head_act, float head_slope, void* head_out,
+                     const int64_t* head_strides, void* stream) {
+  RG_CHECK_ARG(d && in && w_ring && head_w && head_out && head_strides, "rg_ring_run_head: null argument");
+  RG_UNSUPPORTED(d->mode != 0 || d->cout != 64, "rg_ring_run_head: the producing layer must be a forward convolution with 64 output channels");
+  RG_UNSUPPORTED(head_n < 1 || head_n > RING_HEAD_MAX, "rg_ring_run_head: 1..4 head channels");
+  RG_CHECK_ARG(((uintptr_t)head_w & 15) == 0, "rg_ring_run_head: head weights must be 16-byte aligned");
+  const rg::RingHead head{head_w, head_b, head_n, head_act, head_slope, head_out, head_strides};
+  return ring_run(d, in, w_ring, bias, nullptr, nullptr, nullptr, nullptr, &head, stream);
 }
 
 /* Introspection for tests / DESIGN.md: the configuration the host would pick for this layer. */

@@ -34,13 +34,38 @@ class Generator(tnn.Sequential):
         net = self[0]
         if getattr(net, "ndims", getattr(net, "_ndims", 3)) != 3:
             return super().forward(x)
+        tail = list(self)[1:]
+        req = self._head_request(net, tail) if not torch.is_grad_enabled() else None
         net._keep_compute_dtype = True
         try:
-            y = net(x)
+            if req is not None:
+                with CV.offer_head(req):
+                    y = net(x)
+            else:
+                y = net(x)
         finally:
             net._keep_compute_dtype = False
-        y = L.run_layers(list(self)[1:], y)
+        if req is None or not req.done:
+            y = L.run_layers(tail, y)
         return F.cast(y, torch.float32)
+
+    @staticmethod
+    def _head_request(net, tail):
+        """Inference: offer the 1x1x1 head (+ activation) to the network's last convolution (conv.HeadRequest) when the
+        network ends in conv -> activation with nothing behind it (a plain U-Net: the top r_conv ConvPass)."""
+        if not (1 <= len(tail) <= 2 and isinstance(tail[0], L.Conv3d) and tuple(tail[0].kernel_size) == (1, 1, 1)
+                and tail[0].groups == 1 and not any(tail[0]._pads()[0])):
+            return None
+        ac = (L.ACT_NONE, 0.0)
+        if len(tail) == 2:
+            ac = L.act_code(tail[1])
+            if ac is None:
+                return None
+        last = getattr(net, "last_conv_before_head", None)
+        conv = last() if callable(last) else None
+        if conv is None:
+            return None
+        return CV.HeadRequest(conv.weight, tail[0].weight, tail[0].bias, ac[0], ac[1])
 
 
 def _downsample_factors(kw, ndims):

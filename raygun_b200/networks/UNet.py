@@ -288,6 +288,16 @@ class UNet(tnn.Module):
             return None
         return last[-1].out_channels, up.out_channels
 
+    def last_conv_before_head(self):
+        """The convolution whose activated output IS the network output (the generator head may be folded into its
+        epilogue, cyclegan.Generator): the last conv of the top r_conv ConvPass of a plain single-head U-Net."""
+        if self.ndims != 3 or self.num_heads != 1 or self.residual or self.noise_layer is not None or self.num_levels < 2:
+            return None
+        layers = list(self.r_conv[0][0].conv_pass)
+        if len(layers) >= 2 and isinstance(layers[-2], L.Conv3d) and L.act_code(layers[-1]) is not None:
+            return layers[-2]
+        return None
+
     def rec_forward(self, level, f_in):
         i = self.num_levels - level - 1          # index into the module lists
         cat = None

@@ -25,7 +25,7 @@ def test_library_builds_and_exports_every_declared_symbol():
     assert declared == set(_C.SYMBOLS), declared ^ set(_C.SYMBOLS)
     for s in declared:
         assert hasattr(lib, s), s
-    assert lib.rg_version() == 200
+    assert lib.rg_version() == 201
 
 
 def test_sass_contains_blackwell_tensor_core_and_tma_instructions():

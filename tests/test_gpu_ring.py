@@ -170,3 +170,80 @@ def test_halo_wgrad_many_splits_is_linear_in_dy():
     ref = TF.conv3d(x.float().transpose(0, 1), comb.float().transpose(0, 1), padding=1).transpose(0, 1)   # [co][ci][k..]
     assert _rel(ab, ref) <= 5e-3
     assert _rel(ab, 2.0 * a + b) <= 1e-2
+
+
+HEAD = [
+    # cin, kernel, pad, spatial, batch, head channels, head activation
+    (64, 3, 1, (19, 17, 11), 2, 1, "tanh"),      # the G-UNet tail: 3^3 64 -> 64 ReLU, then 64 -> 1 + Tanh
+    (128, 3, 1, (9, 20, 13), 1, 3, "none"),      # two reduction chunks (the concat buffer), 3 head channels
+    (64, 7, 3, (9, 9, 9), 1, 4, "sigmoid"),
+]
+
+
+@pytest.mark.parametrize("case", HEAD)
+def test_ring_fused_head_equals_the_two_layer_result(case):
+    """rg_ring_run_head (BaseSystem.py:209-224 folded into the last ConvPass layer, UNet.py:52-87): the head's output
+    equals 1x1x1 conv + activation applied to the bf16 tensor the unfused layer stores -- compared with an fp32 CPU
+    evaluation of the same bf16-rounded operands and with the library's own two-kernel path."""
+    import raygun_b200 as rb
+    from raygun_b200 import conv as CV
+    cin, k, p, sp, n, hn, hact = case
+    torch.manual_seed(33)
+    x = _q(torch.randn(n, cin, *sp))
+    conv = torch.nn.Conv3d(cin, 64, k, padding=p)
+    head = torch.nn.Conv3d(64, hn, 1)
+    w, b = _q(conv.weight.detach()), conv.bias.detach()
+    hw, hb = head.weight.detach(), head.bias.detach()
+    mid = _q(TF.relu(TF.conv3d(x, w, b, padding=p)))
+    ref = TF.conv3d(mid, hw, hb)
+    code = {"none": 0, "tanh": 3, "sigmoid": 4}[hact]
+    ref = {"none": lambda t: t, "tanh": torch.tanh, "sigmoid": torch.sigmoid}[hact](ref)
+    with rb.precision("bf16"), torch.no_grad():
+        xg = x.to(DEV).bfloat16().contiguous(memory_format=torch.channels_last_3d)
+        wg, bg, hwg, hbg = w.to(DEV), b.to(DEV), hw.to(DEV), hb.to(DEV)
+        before = CV.stats.get("ring_head", 0)
+        with CV.offer_head(CV.HeadRequest(wg, hwg, hbg, code, 0.0)) as req:
+            y, _, _ = CV.conv_fprop(xg, wg, bg, (1, 1, 1), _t3(p), 1, 1, 0.0)
+        assert req.done and CV.stats.get("ring_head", 0) == before + 1, "fused head was not taken"
+        assert y.shape == (n, hn, *sp) and y.dtype == torch.bfloat16
+        y2, _, _ = CV.conv_fprop(xg, wg, bg, (1, 1, 1), _t3(p), 1, 1, 0.0)
+        z2, _, _ = CV.conv_fprop(y2, hwg, hbg, (1, 1, 1), (0, 0, 0), 1, code, 0.0)
+    scale = max(1.0, float(ref.abs().max()))
+    assert float((y.float().cpu() - ref).abs().max()) <= 1e-2 * scale
+    # against the two-kernel path: same operands, same bf16 intermediate; only the fp32 summation order of 64 products and
+    # the final bf16 rounding can differ (one bf16 ulp = 2^-8 relative)
+    assert float((y.float() - z2.float()).abs().max()) <= 2 ** -7 * scale
+    assert float((y.float() - z2.float()).abs().mean()) <= 2e-4 * scale
+
+
+def test_generator_inference_folds_the_head_into_the_last_convolution():
+    """cyclegan.Generator under no_grad: Sequential(UNet, Conv3d(64 -> 1, 1), Tanh) (BaseSystem.py:209-224) runs the head
+    inside the last ring launch; the result matches the unfused execution to one bf16 ulp, and training (grad enabled)
+    never takes the fused path."""
+    import contextlib
+    import sys
+    import raygun_b200 as rb
+    from raygun_b200 import conv as CV
+    from raygun_b200.cyclegan import make_generator
+    torch.manual_seed(8)
+    with contextlib.redirect_stdout(sys.stderr):
+        g = make_generator("unet", dict(input_nc=1, output_nc=1, ngf=64, fmap_inc_factor=2, num_downs=3,
+                                        padding_type="same", final_activation="Tanh")).to(DEV).eval()
+    x = torch.rand(1, 1, 40, 48, 56).mul(2).sub(1).to(DEV)
+    with rb.precision("bf16"):
+        with torch.no_grad():
+            before = CV.stats.get("ring_head", 0), CV.stats.get("pointwise", 0)
+            y = g(x)
+            assert CV.stats.get("ring_head", 0) == before[0] + 1 and CV.stats.get("pointwise", 0) == before[1]
+            old, CV.FUSE_HEAD = CV.FUSE_HEAD, False
+            try:
+                z = g(x)
+            finally:
+                CV.FUSE_HEAD = old
+            assert CV.stats.get("ring_head", 0) == before[0] + 1 and CV.stats.get("pointwise", 0) == before[1] + 1
+        before = CV.stats.get("ring_head", 0)
+        g(x).sum().backward()
+        assert CV.stats.get("ring_head", 0) == before
+    assert y.shape == z.shape == x.shape and y.dtype == torch.float32
+    assert float((y - z).abs().max()) <= 2 ** -7 and float((y - z).abs().mean()) <= 2e-4
+    assert float(y.std()) > 1e-3
