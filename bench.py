@@ -39,6 +39,9 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
+# cfg4 blocks peak at ~130 GB of the 180 GB and their shapes differ (clipped face / edge / corner blocks): with fixed-size
+# segments the caching allocator can end up with enough reserved-but-fragmented memory to fail a 60 GB request
+os.environ.setdefault("PYTORCH_CUDA_ALLOC_CONF", "expandable_segments:True")
 import torch  # noqa: E402
 
 WORKLOADS = {

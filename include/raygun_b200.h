@@ -144,10 +144,12 @@ int rg_ring_run_head(const rg_igemm_desc* desc, const void* in, const void* w_ri
  * opens a U-Net, UNet.py:52-87 with input_nc = 1): im2col rows are gathered straight into the tensor-core operand
  * tile in shared memory, so the 1-channel input and the output cross HBM once.  `x` is bf16 with arbitrary element
  * strides (desc->x_strides = n,d,h,w; x_channel_stride for c); `w64` = bf16 [Cout][64], row co = the flattened
- * [Cin][kD][kH][kW] weights of that output channel, zero padded; `y` bf16, channels innermost.  Zero padding only.  */
+ * [Cin][kD][kH][kW] weights of that output channel, zero padded; `y` bf16, channels innermost.  `pad_mode`
+ * (RG_PAD_*): how the desc->pad taps outside the input are read -- zeros, or mirrored / clamped indices, i.e. the
+ * reflect / replicate 'same' padding of UNet.py:61-69 without a padded copy of the input (forward only).        */
 int rg_stem_conv_supported(const rg_igemm_desc* desc);
 int rg_stem_conv_run(const rg_igemm_desc* desc, const void* x, long long x_channel_stride, const void* w64,
-                     const float* bias, void* y, void* stream);
+                     const float* bias, void* y, int pad_mode, void* stream);
 
 /* ---- ConvTranspose3d, kernel = stride = 2 (upconv2_sm100.cu) -------------------------------------------------
  * Forward of the U-Net up-sampling (`Upsample.up`, UNet.py:265-269) as one GEMM launch: every input voxel produces

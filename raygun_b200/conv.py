@@ -308,8 +308,9 @@ def stem_direct_ok(w, want_stats):
             and K.compute_dtype() == torch.bfloat16)
 
 
-def stem_conv_fprop(x, w, bias, pad, act=ACT_NONE, slope=0.0, out=None):
-    """Forward of the first U-Net convolution (UNet.py:52-87, input_nc -> ngf) without the folded intermediate."""
+def stem_conv_fprop(x, w, bias, pad, act=ACT_NONE, slope=0.0, out=None, pad_mode=0):
+    """Forward of the first U-Net convolution (UNet.py:52-87, input_nc -> ngf) without the folded intermediate.
+    `pad_mode` (functional.PAD_*): zeros, or reflect / replicate read through mirrored indices (inference only)."""
     require_device(x)
     n, cin, d, h, wd_ = x.shape
     cout = w.shape[0]
@@ -344,7 +345,7 @@ def stem_conv_fprop(x, w, bias, pad, act=ACT_NONE, slope=0.0, out=None):
     bias_f = bias.detach().float().contiguous() if bias is not None else None
     with _Timed("fprop", 2.0 * y.numel() * cin * kernel[0] * kernel[1] * kernel[2], x.device, "stem_conv_kernel"):
         check(lib().rg_stem_conv_run(C.byref(d_), ptr(xb), C.c_longlong(xb.stride(1)), ptr(w64), ptr(bias_f), ptr(y),
-                                     stream_ptr(x.device)), "rg_stem_conv_run")
+                                     C.c_int(int(pad_mode)), stream_ptr(x.device)), "rg_stem_conv_run")
     count_launch()
     stats["stem_direct"] = stats.get("stem_direct", 0) + 1
     return y

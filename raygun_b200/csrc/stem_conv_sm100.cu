@@ -37,6 +37,7 @@ struct alignas(64) StemParams {
   int in_d, in_h, in_w;
   int out_d, out_h, out_w, batch;
   int tiles_h, tiles_w;
+  int pad_mode;                              // RG_PAD_ZEROS / REFLECT / REPLICATE: how taps outside the input are read
   int tile_h, tile_w;                        // 16 x 8 (generic builders) or 4 x 32 (3^3 single-channel row builders)
   int quad_h;                                // h rows per TMEM lane quadrant = rows of one epilogue store box (4 or 1)
   int afull_count;                           // arrivals that complete an A stage: 128 builder threads, or 1 warp leader
@@ -53,6 +54,16 @@ __device__ __forceinline__ void stem_tile_coords(const StemParams& p, long long 
   const unsigned ih = u % (unsigned)p.tiles_h; u /= (unsigned)p.tiles_h;
   d = (int)(u % (unsigned)p.out_d); n = (int)(u / (unsigned)p.out_d);
   h0 = (int)ih * p.tile_h; w0 = (int)iw * p.tile_w;
+}
+
+// Source index of tap coordinate i along an axis of extent n.  Zero padding: out-of-range taps read 0 (ok = false);
+// reflect / replicate (the 'same' padding of UNet.py:61-69 folded into the gather: no padded copy of the input): the
+// mirrored / clamped index.  Tile overhang far outside the tensor is clamped too (those voxels are never stored).
+__device__ __forceinline__ int stem_src(int i, int n, int mode, bool& ok) {
+  if (mode == RG_PAD_ZEROS) { ok = i >= 0 && i < n; return i; }
+  ok = true;
+  if (mode == RG_PAD_REFLECT) { i = i < 0 ? -i : i; i = i >= n ? 2 * n - 2 - i : i; }
+  return min(max(i, 0), n - 1);
 }
 
 // KSTEPS = ceil(K / 16): the builder writes 2*KSTEPS 16-byte chunks per row, the issuer KSTEPS MMAs per tile
@@ -145,19 +156,19 @@ __global__ void __launch_bounds__(ST_THREADS, 1) stem_conv_kernel(const __grid_c
         int n, d, h0, w0;
         stem_tile_coords(p, t, n, d, h0, w0);
         const __nv_bfloat16* xn = p.x + (long long)n * p.xs_n;
-        const int xw = w0 - p.pw + lane;
-        const bool win = xw >= 0 && xw < p.in_w;
+        bool win, ein;
+        const int xw = stem_src(w0 - p.pw + lane, p.in_w, p.pad_mode, win);
         // columns 32, 33 of patch rows 2i, 2i+1 .. : lane l covers row l >> 1 (rows 0..15), lanes 0..3 rows 16, 17
-        const int xe = w0 - p.pw + 32 + (lane & 1);
-        const bool ein = xe >= 0 && xe < p.in_w;
+        const int xe = stem_src(w0 - p.pw + 32 + (lane & 1), p.in_w, p.pad_mode, ein);
 #pragma unroll
         for (int a = 0; a < 3; ++a) {
-          const int z = d - p.pd + a;
-          const bool zin = z >= 0 && z < p.in_d;
+          bool zin;
+          const int z = stem_src(d - p.pd + a, p.in_d, p.pad_mode, zin);
 #pragma unroll
           for (int hh = 0; hh < 6; ++hh) {
-            const int y = h0 - p.ph + hh;
-            const bool ok = zin && y >= 0 && y < p.in_h && win;
+            bool yin;
+            const int y = stem_src(h0 - p.ph + hh, p.in_h, p.pad_mode, yin);
+            const bool ok = zin && yin && win;
             uint16_t val = 0;
             if (ok) val = __ldg(reinterpret_cast<const uint16_t*>(xn + (long long)z * p.xs_d + (long long)y * p.xs_h) + xw * xsw);
             v[a * 6 + hh] = val;
@@ -167,8 +178,9 @@ __global__ void __launch_bounds__(ST_THREADS, 1) stem_conv_kernel(const __grid_c
         for (int e = 0; e < 2; ++e) {
           const int row = e * 16 + (lane >> 1);                  // patch row a * 6 + hh
           const int a = row / 6, hh = row - a * 6;
-          const int z = d - p.pd + a, y = h0 - p.ph + hh;
-          const bool ok = row < 18 && z >= 0 && z < p.in_d && y >= 0 && y < p.in_h && ein;
+          bool zin, yin;
+          const int z = stem_src(d - p.pd + a, p.in_d, p.pad_mode, zin), y = stem_src(h0 - p.ph + hh, p.in_h, p.pad_mode, yin);
+          const bool ok = row < 18 && zin && yin && ein;
           uint16_t val = 0;
           if (ok) val = __ldg(reinterpret_cast<const uint16_t*>(xn + (long long)z * p.xs_d + (long long)y * p.xs_h) + xe * xsw);
           v[18 + e] = val;
@@ -244,15 +256,17 @@ __global__ void __launch_bounds__(ST_THREADS, 1) stem_conv_kernel(const __grid_c
         int k = 0;
         for (int ci = 0; ci < p.cin; ++ci)
           for (int a = 0; a < p.kd; ++a) {
-            const int z = dd + a;
-            const bool zin = z >= 0 && z < p.in_d;
+            bool zin;
+            const int z = stem_src(dd + a, p.in_d, p.pad_mode, zin);
             for (int b = 0; b < p.kh; ++b) {
-              const int y = hh + b;
-              const bool rin = zin && y >= 0 && y < p.in_h;
+              bool yin;
+              const int y = stem_src(hh + b, p.in_h, p.pad_mode, yin);
+              const bool rin = zin && yin;
               const __nv_bfloat16* row = xn + ci * p.xs_c + (long long)z * p.xs_d + (long long)y * p.xs_h;
               for (int c = 0; c < p.kw; ++c, ++k) {
-                const int xw = ww + c;
-                if (rin && xw >= 0 && xw < p.in_w)
+                bool xin;
+                const int xw = stem_src(ww + c, p.in_w, p.pad_mode, xin);
+                if (rin && xin)
                   *reinterpret_cast<__nv_bfloat16*>(rowp + ((((k >> 3) ^ (v & 7)) << 4) | ((k & 7) << 1))) =
                       __ldg(row + (long long)xw * p.xs_w);
               }
@@ -391,10 +405,13 @@ int rg_stem_conv_supported(const rg_igemm_desc* d) {
 }
 
 int rg_stem_conv_run(const rg_igemm_desc* d, const void* x, long long x_channel_stride, const void* w64, const float* bias,
-                     void* y, void* stream) {
+                     void* y, int pad_mode, void* stream) {
   RG_CHECK_ARG(d && x && w64 && y, "rg_stem_conv_run: null argument");
+  RG_CHECK_ARG(pad_mode >= RG_PAD_ZEROS && pad_mode <= RG_PAD_REPLICATE, "rg_stem_conv_run: bad pad mode %d", pad_mode);
   int rc = stem_check(d);
   if (rc) return rc;
+  if (pad_mode == RG_PAD_REFLECT)
+    for (int i = 0; i < 3; ++i) RG_CHECK_ARG(d->pad[i] < d->in_dhw[i], "rg_stem_conv_run: reflect padding must be smaller than the input");
   RG_CHECK_ARG(((uintptr_t)y & 15) == 0 && ((uintptr_t)w64 & 15) == 0, "rg_stem_conv_run: output / weights must be 16-byte aligned");
   StemParams p;
   memset(&p, 0, sizeof(p));
@@ -404,6 +421,7 @@ int rg_stem_conv_run(const rg_igemm_desc* d, const void* x, long long x_channel_
   p.cin = d->cin; p.kd = d->kernel[0]; p.kh = d->kernel[1]; p.kw = d->kernel[2];
   p.pd = d->pad[0]; p.ph = d->pad[1]; p.pw = d->pad[2];
   p.K = d->cin * d->kernel[0] * d->kernel[1] * d->kernel[2];
+  p.pad_mode = pad_mode;
   p.in_d = d->in_dhw[0]; p.in_h = d->in_dhw[1]; p.in_w = d->in_dhw[2];
   p.out_d = d->out_dhw[0]; p.out_h = d->out_dhw[1]; p.out_w = d->out_dhw[2];
   p.batch = d->n;

@@ -34,6 +34,14 @@ class Generator(tnn.Sequential):
         net = self[0]
         if getattr(net, "ndims", getattr(net, "_ndims", 3)) != 3:
             return super().forward(x)
+        return F.cast(self.forward_compute(x), torch.float32)
+
+    def forward_compute(self, x):
+        """forward() without the final cast to fp32: the result stays in the compute dtype (bf16 storage in bf16 mode).
+        Blockwise prediction quantises it to uint8 directly (predict.predict_volume) -- same values, one pass less."""
+        net = self[0]
+        if getattr(net, "ndims", getattr(net, "_ndims", 3)) != 3:
+            return super().forward(x)
         tail = list(self)[1:]
         req = self._head_request(net, tail) if not torch.is_grad_enabled() else None
         net._keep_compute_dtype = True
@@ -47,7 +55,7 @@ class Generator(tnn.Sequential):
             net._keep_compute_dtype = False
         if req is None or not req.done:
             y = L.run_layers(tail, y)
-        return F.cast(y, torch.float32)
+        return y
 
     @staticmethod
     def _head_request(net, tail):

@@ -43,6 +43,8 @@ class _Cast(torch.autograd.Function):
 def cast(x, dtype):
     if x.dtype == dtype and (K.is_ndhwc(x) if dtype == torch.bfloat16 else x.is_contiguous()):
         return x
+    if x.dtype == dtype == torch.bfloat16 and x.dim() == 5 and x.shape[1] == 1 and not (x.requires_grad and torch.is_grad_enabled()):
+        return x          # one channel: every layout is "channels innermost"; the kernels that take it read element strides
     return _Cast.apply(x, dtype)
 
 

@@ -10,6 +10,7 @@ import functools
 import torch
 import torch.nn as tnn
 
+from . import conv as CV
 from . import functional as F
 from . import kernels as K
 from ._C import ACT_LEAKY, ACT_NONE, ACT_RELU, ACT_SIGMOID, ACT_TANH, NORM_BATCH, NORM_INSTANCE
@@ -102,6 +103,15 @@ class Conv3d(tnn.Conv3d):
         if any(lo) or any(hi):
             if self.padding_mode == "zeros" and lo == hi:
                 pad = lo
+            elif (self.padding_mode in ("reflect", "replicate") and lo == hi and not torch.is_grad_enabled() and x.dim() == 5
+                  and x.is_cuda and not want_stats and tuple(self.stride) == (1, 1, 1) and x.dtype == torch.bfloat16
+                  and K.arena_of(x, lo, hi) is None and F._stem_eligible(x, self.weight, (1, 1, 1), int(self.groups))
+                  and CV.stem_direct_ok(self.weight, False) and all(p_ < s_ for p_, s_ in zip(lo, x.shape[2:]))):
+                # inference, the 1 -> ngf stem of a U-Net: the small-K kernel gathers its taps through mirrored / clamped
+                # indices, so the explicit F.pad of the reference (UNet.py:61-69) costs no padded copy of the input
+                with K.arena_scope(True):
+                    return CV.stem_conv_fprop(x, self.weight, self.bias, lo, act, slope, out=out,
+                                              pad_mode=F.PAD_MODES[self.padding_mode])
             elif self.padding_mode in ("zeros", "reflect", "replicate"):
                 arena = K.arena_of(x, lo, hi) if (x.dim() == 5 and x.is_cuda) else None
                 if arena is not None and not torch.is_grad_enabled():

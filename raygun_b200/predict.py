@@ -167,6 +167,8 @@ def predict_volume(model, volume_u8: torch.Tensor, read_shape, write_shape, out:
         blocks = partition_blocks(block_list(volume_u8.shape, read_shape, write_shape, fit), rank, world)
     was_training = model.training
     model.eval()
+    # cyclegan.Generator: skip the final cast to fp32 (the uint8 quantisation reads the compute dtype directly)
+    run = getattr(model, "forward_compute", None) or model
     main = torch.cuda.current_stream(device)
     s_in, s_out = torch.cuda.Stream(device), torch.cuda.Stream(device)
     max_in = max((b.cost for b in blocks), default=0)
@@ -196,7 +198,21 @@ def predict_volume(model, volume_u8: torch.Tensor, read_shape, write_shape, out:
         x = _normalise(u8, lo_pad, hi_pad, *scale_shift, dtype)
         in_free[k & 1] = torch.cuda.Event()
         in_free[k & 1].record(main)
-        y = model(x)
+        for attempt in (0, 1):
+            oom = False
+            try:
+                y = run(x)
+            except torch.OutOfMemoryError:
+                if attempt:
+                    raise
+                oom = True
+            if not oom:
+                break
+            # block shapes differ (clipped face / edge / corner blocks): cached segments of the previous shape can leave
+            # the allocator fragmented.  Hand them back and retry once (PYTORCH_CUDA_ALLOC_CONF=expandable_segments:True
+            # avoids the situation altogether).
+            torch.cuda.synchronize(device)
+            torch.cuda.empty_cache()
         y = y[0] if isinstance(y, (list, tuple)) else y
         full = tuple(r for r in b.read_ext)
         if tuple(y.shape[2:]) == full:                # 'same' network: crop the halo (worker.py:124-129)

@@ -87,3 +87,45 @@ def test_unet_first_conv_takes_the_direct_stem_kernel_and_trains():
         y.float().sum().backward()
     assert _rel(y, yr) <= 2e-2
     assert _rel(conv.weight.grad, ref_conv.weight.grad) <= 2e-2
+
+
+PADDED = [
+    # cin, cout, kernel, spatial, batch, padding_mode
+    (1, 64, (3, 3, 3), (9, 17, 11), 2, "reflect"),        # the G-UNet stem with 'same' reflect padding (UNet.py:61-69)
+    (1, 64, (3, 3, 3), (37, 6, 70), 1, "reflect"),        # several 4 x 32 tiles per row, overhang on both in-plane axes
+    (1, 64, (3, 3, 3), (5, 9, 33), 1, "replicate"),
+    (2, 64, (3, 3, 3), (6, 10, 9), 1, "reflect"),         # generic builder (two input channels: K = 54)
+]
+
+
+@pytest.mark.parametrize("case", PADDED)
+def test_stem_conv_reads_reflect_and_replicate_padding_through_mirrored_indices(case):
+    """Inference: nn.Conv3d(padding='same', padding_mode='reflect') on the 1 -> ngf stem runs the small-K kernel on the
+    UNPADDED input (taps outside it gathered through mirrored / clamped indices) -- no padded copy -- and equals
+    F.pad + conv3d of the same bf16-rounded operands; a float input and the training path keep their routes."""
+    import raygun_b200 as rb
+    from raygun_b200 import conv as CV
+    from raygun_b200 import nn as L
+    cin, cout, k, sp, n, mode = case
+    torch.manual_seed(35)
+    x = _q(torch.randn(n, cin, *sp))
+    conv = L.Conv3d(cin, cout, k, padding="same", padding_mode=mode)
+    w, b = _q(conv.weight.detach()), conv.bias.detach()
+    ref = TF.relu(TF.conv3d(TF.pad(x, (1,) * 6, mode=mode), w, b))
+    conv = conv.to(DEV)
+    with rb.precision("bf16"):
+        xg = x.to(DEV).bfloat16()
+        if cin > 1:
+            xg = xg.contiguous(memory_format=torch.channels_last_3d)
+        before = dict(CV.stats)
+        with torch.no_grad():
+            from raygun_b200 import _C
+            launches = _C.launch_count
+            y = conv.fused(xg, 1, 0.0)
+        assert CV.stats.get("stem_direct", 0) == before.get("stem_direct", 0) + 1
+        assert _C.launch_count == launches + 1, "a padded copy was made"
+        assert y.shape == (n, cout, *sp) and y.dtype == torch.bfloat16
+        assert _rel(y, ref) <= 1e-2, _rel(y, ref)
+        # training keeps the explicit pad (its adjoint folds the data gradient) and agrees with the inference route
+        yt = conv.fused(xg, 1, 0.0)
+        assert _rel(yt, y.float()) <= 1e-2
