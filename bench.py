@@ -41,7 +41,9 @@ if ROOT not in sys.path:
 
 # cfg4 blocks peak at ~130 GB of the 180 GB and their shapes differ (clipped face / edge / corner blocks): with fixed-size
 # segments the caching allocator can end up with enough reserved-but-fragmented memory to fail a 60 GB request
-os.environ.setdefault("PYTORCH_CUDA_ALLOC_CONF", "expandable_segments:True")
+# (the stock-PyTorch comparator runs in its own process with torch's default allocator: --comparator-only)
+if "--comparator-only" not in sys.argv and not any(a in ("cfg2", "cfg3", "cfg5") for a in sys.argv):
+    os.environ.setdefault("PYTORCH_CUDA_ALLOC_CONF", "expandable_segments:True")
 import torch  # noqa: E402
 
 WORKLOADS = {
@@ -843,6 +845,30 @@ def gpu_comparator(dev):
     return res
 
 
+def comparator_subprocess():
+    """The comparator leg in a fresh process: torch's default caching allocator (this process runs with expandable
+    segments for the cfg4 blocks, which slows stock eager training -- it allocates every activation per step -- by 1.4-2.5x)
+    and none of our memory held."""
+    import gc
+    gc.collect()
+    torch.cuda.synchronize()
+    torch.cuda.empty_cache()
+    env = {k: v for k, v in os.environ.items() if k != "PYTORCH_CUDA_ALLOC_CONF"}
+    for k in ("RANK", "LOCAL_RANK", "WORLD_SIZE", "MASTER_ADDR", "MASTER_PORT"):
+        env.pop(k, None)
+    try:
+        r = subprocess.run([sys.executable, os.path.abspath(__file__), "--comparator-only"], env=env, capture_output=True,
+                           text=True, timeout=900)
+        lines = [ln for ln in r.stdout.splitlines() if ln.startswith("{")]
+        if r.returncode != 0 or not lines:
+            return {"error": f"comparator process rc={r.returncode}: {r.stderr[-300:]}"}
+        comp = json.loads(lines[-1])
+        comp["process"] = "fresh process, default torch caching allocator, started after our timed regions"
+        return comp
+    except Exception as e:  # noqa: BLE001
+        return {"error": f"comparator process failed: {e!r}"}
+
+
 def ratio(ours, comp, key):
     try:
         return ours / comp[key]
@@ -863,9 +889,13 @@ def main():
     ap.add_argument("--global-batch", type=int, default=8, help="cfg3: global batch (8 = BASELINE configs[2])")
     ap.add_argument("--no-graph", action="store_true", help="launch every kernel eagerly instead of replaying one CUDA graph")
     ap.add_argument("--no-comparator", action="store_true", help="skip the stock-PyTorch/cuDNN comparator leg")
+    ap.add_argument("--comparator-only", action="store_true", help="(internal) run the comparator leg alone and print its JSON")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
+        return
+    if args.comparator_only:
+        print(json.dumps(gpu_comparator(torch.device("cuda", 0))), flush=True)
         return
     ctx = Ctx()
     if args.workload == "cfg4":
@@ -881,7 +911,7 @@ def main():
         if ctx.rank == 0:
             line["cfg3"], line["cfg2"] = sub3, sub2
             if ctx.world == 1 and not args.no_comparator:
-                comp = gpu_comparator(ctx.dev)
+                comp = comparator_subprocess()
                 comp["ours_over_cudnn_bf16"] = dict(
                     cfg4_voxels_per_sec=ratio(line["roofline"]["whole_step"]["executed_incl_halo"] * 1e12 / UNET_FLOP_PER_VOXEL,
                                               comp.get("cfg4_autocast_bf16_channels_last_3d"), "voxels_per_sec"),
