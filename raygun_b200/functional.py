@@ -16,6 +16,7 @@ from ._C import (ACT_LEAKY, ACT_NONE, ACT_RELU, ACT_SIGMOID, ACT_TANH, LOSS_L1, 
 import os as _os
 TRAIN_ARENA = _os.environ.get("RAYGUN_B200_TRAIN_ARENA", "1") != "0"     # pad arenas for conv+activation outputs in training
 PAD_FOLD = _os.environ.get("RAYGUN_B200_PAD_FOLD", "1") != "0"           # in-place pad adjoint behind our convolutions
+TRAIN_CAT = _os.environ.get("RAYGUN_B200_TRAIN_CAT", "1") != "0"         # training-time in-place U-Net skip concat
 
 PAD_MODES = {"zeros": PAD_ZEROS, "constant": PAD_ZEROS, "reflect": PAD_REFLECT, "replicate": PAD_REPLICATE}
 
@@ -56,6 +57,34 @@ def to_compute(x):
 # ---------------------------------------------------------------------------------------------
 # convolution
 # ---------------------------------------------------------------------------------------------
+class _Out:
+    """A destination view handed to an autograd.Function WITHOUT being one of its tensor inputs: the kernel writes into it
+    and the Function returns it as a fresh output (training-time in-place skip concat; a tensor argument that is returned
+    would be treated by autograd as an aliased input)."""
+    __slots__ = ("t",)
+
+    def __init__(self, t):
+        self.t = t
+
+
+def _unbox(out):
+    return out.t if isinstance(out, _Out) else out
+
+
+def _dest(out):
+    """`out` as the Functions take it: dropped in training unless the caller marked it with `mark_train_out`."""
+    if out is None or not torch.is_grad_enabled():
+        return out
+    return _Out(out) if getattr(out, "_rg_train_out", False) else None
+
+
+def mark_train_out(view):
+    """Allow a convolution to write its TRAINING-mode output into `view` (a channel slice of a concat buffer whose
+    consumer is wired up with `cat_join`)."""
+    view._rg_train_out = True
+    return view
+
+
 class _Conv3d(torch.autograd.Function):
     """nn.Conv3d forward/backward with zero padding and a fused activation epilogue
     (UNet.py:61-69, ResNet.py:271-298,407-416, NLayerDiscriminator.py:137-174, BaseSystem.py:209-224).
@@ -73,6 +102,7 @@ class _Conv3d(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x, w, bias, stride, pad, groups, act, slope, want_stats, out=None):
+        out = _unbox(out)
         ctx.narrow = _Conv3d._narrow_out(x, w, stride, groups, want_stats)
         if ctx.narrow:
             cout = w.shape[0]
@@ -139,6 +169,7 @@ class _StemConv3d(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x, w, bias, pad, act, slope, want_stats, out=None):
+        out = _unbox(out)
         cout, cin, kd, kh, kw = w.shape
         cf = cin * kh * kw
         if CV.stem_direct_ok(w, want_stats):
@@ -192,8 +223,7 @@ def _stem_eligible(x, w, stride, groups):
 def conv3d(x, w, bias=None, stride=1, padding=0, groups=1, act=ACT_NONE, slope=0.0, want_stats=False, out=None):
     """`out` (inference only): a preallocated NDHWC view the kernel should write into, e.g. a channel slice of the
     skip-connection concat buffer; the result IS `out` when the kernel could honour it (callers check identity)."""
-    if torch.is_grad_enabled():
-        out = None
+    out = _dest(out)
     # training: a convolution + activation with no norm behind it (every G-UNet ConvPass conv) also writes into a pad
     # arena -- the next reflect-padded conv mirrors the shell in place, the activation backward reads the interior view
     train_arena = TRAIN_ARENA and act != ACT_NONE and not want_stats
@@ -213,6 +243,7 @@ class _ConvTranspose3d(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x, w, bias, stride, pad, out_pad, act, slope, want_stats, out=None):
+        out = _unbox(out)
         n, cin, d, h, wd_ = x.shape
         k = w.shape[2:]
         osz = [(i - 1) * s - 2 * p + kk + op for i, s, p, kk, op in zip((d, h, wd_), stride, pad, k, out_pad)]
@@ -252,8 +283,7 @@ class _ConvTranspose3d(torch.autograd.Function):
 
 def conv_transpose3d(x, w, bias=None, stride=1, padding=0, output_padding=0, act=ACT_NONE, slope=0.0,
                      want_stats=False, out=None):
-    if torch.is_grad_enabled():
-        out = None
+    out = _dest(out)
     with K.arena_scope(not torch.is_grad_enabled()):
         y, s, q = _ConvTranspose3d.apply(x, w, bias, _t3(stride), _t3(padding), _t3(output_padding), act, float(slope),
                                          bool(want_stats), out)
@@ -515,6 +545,31 @@ class _CropCat(torch.autograd.Function):
         ga = part(slice(0, sa[1]), sa, da) if ctx.needs_input_grad[0] else None
         gb = part(slice(sa[1], sa[1] + sb[1]), sb, db) if ctx.needs_input_grad[1] else None
         return ga, gb, None, None
+
+
+class _CatJoin(torch.autograd.Function):
+    """torch.cat([f_left, g_up], dim=1) (UNet.py:349-351, 'same' padding: no crop) when both producers have ALREADY written
+    their outputs into the two channel slices of one concat buffer (`mark_train_out`): no data moves in forward; this node
+    only ties the buffer to both producers.  Backward = `_CropCat`'s: the two channel slices of dy, densified."""
+
+    @staticmethod
+    def forward(ctx, a, b, cat):
+        cat = _unbox(cat)
+        ca = a.shape[1]
+        assert a.data_ptr() == cat[:, :ca].data_ptr() and b.data_ptr() == cat[:, ca:].data_ptr()
+        ctx.meta = (ca, b.shape[1], a.dtype, b.dtype)
+        return cat
+
+    @staticmethod
+    def backward(ctx, dy):
+        ca, cb, da, db = ctx.meta
+        ga = K.convert(dy[:, :ca], da) if ctx.needs_input_grad[0] else None
+        gb = K.convert(dy[:, ca: ca + cb], db) if ctx.needs_input_grad[1] else None
+        return ga, gb, None
+
+
+def cat_join(a, b, cat):
+    return _CatJoin.apply(a, b, _Out(cat))
 
 
 def crop_cat(a, b, spatial):

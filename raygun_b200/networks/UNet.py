@@ -298,9 +298,40 @@ class UNet(tnn.Module):
             return layers[-2]
         return None
 
+    def _train_cat_forward(self, level, i, f_in):
+        """Training twin of the in-place skip concat below: the left ConvPass and the transposed conv write their outputs
+        into the two channel slices of ONE pad-arena concat buffer (functional.mark_train_out) and `F.cat_join` ties the
+        buffer to both producers for autograd -- the two strided copies of `F.crop_cat` per level and traversal leave the
+        step.  Returns None (nothing executed) when the level's shape does not qualify."""
+        ch = self._cat_channels(i)
+        if ch is None or (ch[0] + ch[1]) % 8 or ch[0] % 8:
+            return None
+        lp = [m for m in self.l_conv[i].conv_pass]
+        if not (len(lp) >= 2 and isinstance(lp[-2], L.Conv3d) and L.act_code(lp[-1]) is not None):
+            return None                                   # a norm layer behind the last conv: its output is not the conv's
+        with torch.no_grad():          # plain buffer views, like the ones the kernels' autograd Functions create themselves
+            cat = K.empty5_arena((f_in.shape[0], ch[0] + ch[1], *f_in.shape[2:]), torch.bfloat16, f_in.device)
+            left, right = F.mark_train_out(cat[:, : ch[0]]), F.mark_train_out(cat[:, ch[0]:])
+        f_left = self.l_conv[i](f_in, out=left)
+        if f_left.shape != left.shape or f_left.data_ptr() != left.data_ptr():
+            raise RuntimeError("UNet: the skip ConvPass did not write into the concat buffer (unexpected kernel route)")
+        g_in = self.l_down[i](f_left)
+        gs_out = self.rec_forward(level - 1, g_in)
+        g_up = self.r_up[0][i].up.fused(gs_out[0], out=right)
+        if g_up.shape != right.shape or g_up.data_ptr() != right.data_ptr():
+            # the up-sampled tensor came out elsewhere (e.g. a shape the fused kernel does not take): classic concat
+            return [self.r_conv[0][i](F.crop_cat(f_left, g_up, tuple(g_up.shape[2:])))]
+        return [self.r_conv[0][i](F.cat_join(f_left, g_up, cat))]
+
     def rec_forward(self, level, f_in):
         i = self.num_levels - level - 1          # index into the module lists
         cat = None
+        train_cat = (level > 0 and f_in.dim() == 5 and f_in.is_cuda and torch.is_grad_enabled() and F.TRAIN_ARENA
+                     and F.TRAIN_CAT and K.get_precision() == "bf16" and K.use_tensor_cores())
+        if train_cat:
+            out = self._train_cat_forward(level, i, f_in)
+            if out is not None:
+                return out
         if level > 0 and f_in.dim() == 5 and f_in.is_cuda and K.arena_enabled():
             ch = self._cat_channels(i)
             if ch is not None:

@@ -176,3 +176,30 @@ def test_blockwise_prediction_is_bitwise_independent_of_block_geometry_and_equal
             P.predict_volume(g, vol, (120,) * 3, (72,) * 3, out=out2, rank=r, world=2, dtype=torch.bfloat16, fit="clip")
         assert torch.equal(out2, whole)
         assert float(whole.float().std()) > 1.0
+
+
+def test_training_skip_concat_in_place_equals_the_copying_concat_bit_for_bit():
+    """U-Net training forward + backward with the producers writing straight into the channel slices of the concat
+    buffer (UNet._train_cat_forward / functional.cat_join; UNet.py:338-351) vs the two strided copies of F.crop_cat:
+    same kernels on the same values -> identical outputs and identical parameter gradients, 2 copies per level fewer."""
+    import raygun_b200 as rb
+    from raygun_b200 import _C
+    from raygun_b200 import functional as F
+    from raygun_b200.cyclegan import make_generator
+    gen = torch.Generator().manual_seed(11)
+    x = torch.rand(2, 1, 32, 40, 48, generator=gen).mul(2).sub(1).to(DEV)
+    t = torch.rand(2, 1, 32, 40, 48, generator=gen).mul(2).sub(1).to(DEV)
+    make = lambda: make_generator("unet", dict(G_KW))
+    res = {}
+    for flag in (True, False):
+        old, F.TRAIN_CAT = F.TRAIN_CAT, flag
+        try:
+            n0 = _C.launch_count
+            res[flag] = _grads_of(make, x, t, "bf16") + (_C.launch_count - n0,)
+        finally:
+            F.TRAIN_CAT = old
+    (y1, l1, g1, n1), (y0, l0, g0, n0) = res[True], res[False]
+    assert torch.equal(y1, y0) and torch.equal(l1, l0)
+    for a, b in zip(g1, g0):
+        assert torch.equal(a, b)
+    assert n1 == n0 - 4, (n1, n0)          # two levels x two copies of the forward concat
