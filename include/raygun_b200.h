@@ -81,6 +81,16 @@ size_t rg_conv3d_direct_wgrad_workspace_bytes(const rg_tensor5* xd, const rg_ten
 int rg_conv3d_direct_wgrad(const rg_tensor5* xd, const void* x, const rg_tensor5* dyd, const void* dy,
                            float* dw, float* dbias, const rg_conv_geom* g, int accumulate, float* ws, void* stream);
 
+/* Weight gradient of small-reduction convolutions, Cin * kD * kH * kW <= 64 (smallk_wgrad.cu): the 1 -> ngf stem of a
+ * U-Net (UNet.py:61-69) and the first, stride-2 convolution of NLayerDiscriminator (NLayerDiscriminator.py:137-145).
+ * dy bf16, channels innermost, Cout % 64 == 0, strides multiples of 16 bytes; x bf16 or f32, any strides; zero padding,
+ * any stride.  dw fp32 [Cout,Cin,kD,kH,kW] overwritten, or added to when accumulate != 0; dbias (may be NULL) overwritten;
+ * ws = rg_smallk_wgrad_workspace_bytes(Cout, Cin*kD*kH*kW) bytes of partial rows (ordered two-stage sum).          */
+int rg_smallk_wgrad_supported(const rg_tensor5* xd, const rg_tensor5* dyd, const rg_conv_geom* g);
+size_t rg_smallk_wgrad_workspace_bytes(int cout, int k);
+int rg_smallk_wgrad(const rg_tensor5* xd, const void* x, const rg_tensor5* dyd, const void* dy, const rg_conv_geom* g,
+                    float* dw, float* dbias, float* ws, int accumulate, void* stream);
+
 /* ---- tcgen05 / TMEM / TMA implicit-GEMM convolutions (bf16 NDHWC, fp32 accumulate) --
  * The performance path for the same call sites when Cin%64==0 and Cout%16==0.
  * A plan owns the CUtensorMap descriptors of one (layer, shape) pair. */

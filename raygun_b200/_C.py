@@ -27,7 +27,7 @@ SYMBOLS = [
     "rg_conv3d_direct_fprop", "rg_conv3d_direct_dgrad", "rg_conv3d_direct_wgrad", "rg_conv3d_direct_wgrad_workspace_bytes",
     "rg_plan_create", "rg_plan_destroy", "rg_plan_workspace_bytes", "rg_pack_weights",
     "rg_igemm_run", "rg_igemm_wgrad", "rg_ring_supported", "rg_ring_config", "rg_ring_pack_weights", "rg_ring_workspace_bytes",
-    "rg_ring_run", "rg_ring_run_head",
+    "rg_ring_run", "rg_ring_run_head", "rg_smallk_wgrad_supported", "rg_smallk_wgrad_workspace_bytes", "rg_smallk_wgrad",
     "rg_stem_conv_supported", "rg_stem_conv_run", "rg_upconv2_supported", "rg_upconv2_run",
     "rg_halo_wgrad_supported", "rg_halo_wgrad_workspace_bytes", "rg_halo_wgrad",
     "rg_pw_conv_fprop", "rg_pw_conv_dgrad", "rg_pw_conv_wgrad_workspace_bytes", "rg_pw_conv_wgrad", "rg_smallcin_dgrad",
@@ -91,6 +91,7 @@ def lib():
                 l.rg_ring_workspace_bytes.restype = C.c_size_t
                 l.rg_pw_conv_wgrad_workspace_bytes.restype = C.c_size_t
                 l.rg_conv3d_direct_wgrad_workspace_bytes.restype = C.c_size_t
+                l.rg_smallk_wgrad_workspace_bytes.restype = C.c_size_t
                 l.rg_reduce_ws_floats.restype = C.c_longlong
                 _lib = l
     return _lib

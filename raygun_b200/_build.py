@@ -10,7 +10,7 @@ PKG = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG, "csrc")
 LIBDIR = os.path.join(PKG, "lib")
 LIB = os.path.join(LIBDIR, "libraygun_b200.so")
-SOURCES = ["api.cu", "elementwise.cu", "pool_loss.cu", "norm.cu", "conv_direct.cu", "igemm_sm100.cu", "ring_conv_sm100.cu", "halo_wgrad_sm100.cu", "stem_conv_sm100.cu", "upconv2_sm100.cu", "pointwise.cu", "blockcopy.cu", "resize.cu"]
+SOURCES = ["api.cu", "elementwise.cu", "pool_loss.cu", "norm.cu", "conv_direct.cu", "smallk_wgrad.cu", "igemm_sm100.cu", "ring_conv_sm100.cu", "halo_wgrad_sm100.cu", "stem_conv_sm100.cu", "upconv2_sm100.cu", "pointwise.cu", "blockcopy.cu", "resize.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC"]
 

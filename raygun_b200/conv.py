@@ -637,6 +637,17 @@ def conv_dgrad(dy, w, x_shape, stride, pad, groups=1, bias=None, act=ACT_NONE, s
     return dx, None, None
 
 
+SMALLK_WGRAD = os.environ.get("RAYGUN_B200_SMALLK_WGRAD", "1") != "0"
+
+
+def smallk_wgrad_ok(x, dy, w_shape, groups=1):
+    """The CUDA-core small-reduction weight gradient (smallk_wgrad.cu): Cin * taps <= 64 onto a multiple of 64 channels."""
+    cout, cin_g = w_shape[0], w_shape[1]
+    return (SMALLK_WGRAD and K.get_precision() == "bf16" and groups == 1 and cout % 64 == 0
+            and 1 < cin_g * w_shape[2] * w_shape[3] * w_shape[4] <= 64 and x.dim() == 5 and x.is_cuda
+            and x.dtype in (torch.bfloat16, torch.float32) and K.channels_inner_bf16(dy))
+
+
 def conv_wgrad(x, dy, w_shape, stride, pad, groups=1, want_bias=False, db=None, dw_out=None, accumulate=False):
     """dw (fp32, conv layout) and optionally dbias = sum(dy) (`db`: already computed by the caller's activation pass).
     `dw_out`: write (or, with `accumulate`, add) the weight gradient into this fp32 tensor of shape `w_shape` -- a view of
@@ -686,6 +697,21 @@ def conv_wgrad(x, dy, w_shape, stride, pad, groups=1, want_bias=False, db=None, 
             stats["igemm"] += 1
             db = (db if db is not None else K.norm_stats(dyb, _C.NORM_BATCH)[0]) if want_bias else None
             return dw, db
+    if smallk_wgrad_ok(x, dy, w_shape, groups):
+        g = _geom(kernel, stride, pad, 1)
+        xd, dyd = t5(x), t5(dy)
+        if lib().rg_smallk_wgrad_supported(C.byref(xd), C.byref(dyd), C.byref(g)) == 1:
+            kk = cin_g * kernel[0] * kernel[1] * kernel[2]
+            dw = _dw()
+            own_db = want_bias and db is None
+            if own_db:
+                db = torch.empty(cout, dtype=torch.float32, device=x.device)
+            ws = K.ws_bytes(lib().rg_smallk_wgrad_workspace_bytes(C.c_int(cout), C.c_int(kk)), x.device)
+            check(lib().rg_smallk_wgrad(C.byref(xd), ptr(x), C.byref(dyd), ptr(dy), C.byref(g), ptr(dw),
+                                        ptr(db) if own_db else None, ptr(ws), acc, stream_ptr(x.device)), "rg_smallk_wgrad")
+            count_launch(3 if own_db else 2)
+            stats["smallk_wgrad"] = stats.get("smallk_wgrad", 0) + 1
+            return dw, (db if want_bias else None)
     if _pw_ok(cin_g, cout, kernel, stride, pad, groups):
         xb = K.conv_operand(x)
         dw = _dw()

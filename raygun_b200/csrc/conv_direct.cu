@@ -185,19 +185,35 @@ __global__ void __launch_bounds__(256) direct_wgrad_kernel(ConvP p, const TX* __
   float acc[4][4] = {};
   float rowsum[4] = {0.f, 0.f, 0.f, 0.f};
   const bool do_bias = want_bias && blockIdx.y == 0;
+  const bool co_fast = p.y.sc == 1 && BM == 64 && BK == 16;
+  // output voxel index -> (n, d, h, w): 32-bit divisions whenever the index space allows (a 64-bit division is ~60
+  // instructions; eight of them per thread and K step dominated this kernel on the discriminator's 1 -> 64 stem)
+  const bool small = Ktot < (1LL << 31);
+  const unsigned ovox32 = (unsigned)ovox, yw32 = (unsigned)p.y.w, yh32 = (unsigned)p.y.h;
+  auto decode = [&](long long k, long long& n, long long& qd, long long& qh, long long& qw) {
+    if (small) {
+      const unsigned k32 = (unsigned)k, n32 = k32 / ovox32;
+      unsigned r = k32 - n32 * ovox32;
+      const unsigned t = r / yw32;
+      qw = r - t * yw32; qd = t / yh32; qh = t - (unsigned)qd * yh32; n = n32;
+    } else {
+      n = k / ovox; long long r = k % ovox;
+      qw = r % p.y.w; r /= p.y.w; qh = r % p.y.h; qd = r / p.y.h;
+    }
+  };
   float* dw = part + (long long)blockIdx.z * ld;
   float* dbias = dw + (long long)p.cout * NN;
   for (long long k0 = kbeg; k0 < kend; k0 += BK) {
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {   // A: dy[vox][co]; threads fastest over vox (kk) for W-inner coalescing
-      int idx = tid + j * 256;
-      int kk = idx & 15, mm = idx >> 4;
+    for (int j = 0; j < 4; ++j) {   // A: dy[vox][co]; threads fastest over vox (kk) for W-inner coalescing (NCDHW), or over
+      int idx = tid + j * 256;      // co when the channels are innermost (NDHWC bf16: a warp reads 64 contiguous bytes)
+      int kk = co_fast ? idx >> 6 : idx & 15, mm = co_fast ? idx & 63 : idx >> 4;
       long long k = k0 + kk;
       int co = m0 + mm;
       float v = 0.f;
       if (k < kend && co < p.cout) {
-        long long n = k / ovox, r = k % ovox;
-        long long qw = r % p.y.w; r /= p.y.w; long long qh = r % p.y.h, qd = r / p.y.h;
+        long long n, qd, qh, qw;
+        decode(k, n, qd, qh, qw);
         v = ldf(dy + p.y.off(n, co, qd, qh, qw));
       }
       As[kk][mm] = v;
@@ -208,8 +224,8 @@ __global__ void __launch_bounds__(256) direct_wgrad_kernel(ConvP p, const TX* __
       long long k = k0 + kk;
       float v = 0.f;
       if (nvalid && k < kend) {
-        long long n = k / ovox, r = k % ovox;
-        long long qw = r % p.y.w; r /= p.y.w; long long qh = r % p.y.h, qd = r / p.y.h;
+        long long n, qd, qh, qw;
+        decode(k, n, qd, qh, qw);
         long long id = qd * p.sd - p.pd + bkd, ih = qh * p.sh - p.ph + bkh, iw = qw * p.sw - p.pw + bkw;
         if (id >= 0 && id < p.x.d && ih >= 0 && ih < p.x.h && iw >= 0 && iw < p.x.w)
           v = ldf(x + p.x.off(n, bci, id, ih, iw));

@@ -207,10 +207,18 @@ class _StemConv3d(torch.autograd.Function):
         if ctx.needs_input_grad[0]:
             dx, _, _ = CV.conv_dgrad(dy, w, x.shape, (1, 1, 1), pad, 1, out_dtype=x.dtype)
         if ctx.needs_input_grad[1] or (ctx.has_bias and ctx.needs_input_grad[2]):
-            xc = K.im2col_hw(x, kh, kw, pad[1], pad[2], 64)
-            dw2, db = CV.conv_wgrad(xc, dy, w2shape, (1, 1, 1), (pad[0], 0, 0), 1, want_bias=ctx.has_bias, db=db_pre)
-            dw = dw2.reshape(cout, 64, kd)[:, : cin * kh * kw].reshape(cout, cin, kh, kw, kd).permute(0, 1, 4, 2, 3)
-            dw = dw.contiguous() if ctx.needs_input_grad[1] else None
+            if CV.smallk_wgrad_ok(x, dy, wshape):
+                # whole reduction <= 64: FMA-bound on the CUDA cores, straight into the gradient bucket when there is one
+                bg = bucket_grad(w) if ctx.needs_input_grad[1] else None
+                dw, db = CV.conv_wgrad(x, dy, wshape, (1, 1, 1), pad, 1, want_bias=ctx.has_bias, db=db_pre, dw_out=bg,
+                                       accumulate=bg is not None)
+                if not ctx.needs_input_grad[1] or bg is not None:
+                    dw = None
+            else:
+                xc = K.im2col_hw(x, kh, kw, pad[1], pad[2], 64)
+                dw2, db = CV.conv_wgrad(xc, dy, w2shape, (1, 1, 1), (pad[0], 0, 0), 1, want_bias=ctx.has_bias, db=db_pre)
+                dw = dw2.reshape(cout, 64, kd)[:, : cin * kh * kw].reshape(cout, cin, kh, kw, kd).permute(0, 1, 4, 2, 3)
+                dw = dw.contiguous() if ctx.needs_input_grad[1] else None
         return dx, dw, db, None, None, None, None, None
 
 

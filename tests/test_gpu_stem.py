@@ -129,3 +129,45 @@ def test_stem_conv_reads_reflect_and_replicate_padding_through_mirrored_indices(
         # training keeps the explicit pad (its adjoint folds the data gradient) and agrees with the inference route
         yt = conv.fused(xg, 1, 0.0)
         assert _rel(yt, y.float()) <= 1e-2
+
+
+SMALLK = [
+    # cin, cout, kernel, stride, pad, spatial, batch
+    (1, 64, (3, 3, 3), (1, 1, 1), (1, 1, 1), (9, 17, 11), 2),       # U-Net stem, zero 'same' padding, ragged row tiles
+    (1, 64, (3, 3, 3), (1, 1, 1), (0, 0, 0), (12, 10, 70), 1),      # valid conv on a pre-padded tensor, two tiles per row
+    (1, 64, (3, 3, 3), (2, 2, 2), (1, 1, 1), (16, 16, 16), 3),      # NLayerDiscriminator's first conv (stride 2)
+    (2, 128, (2, 3, 3), (1, 1, 1), (1, 1, 1), (5, 9, 12), 1),       # K = 36 (64-wide accumulators), two channel tiles
+    (1, 64, (4, 4, 4), (2, 2, 2), (1, 1, 1), (12, 12, 12), 1),      # K = 64, the classic PatchGAN kw = 4
+]
+
+
+@pytest.mark.parametrize("case", SMALLK)
+def test_smallk_wgrad_matches_autograd_and_accumulates_into_a_bucket(case):
+    """rg_smallk_wgrad (the FMA-bound weight gradient of Cin * taps <= 64 layers: UNet.py:61-69 stem,
+    NLayerDiscriminator.py:137-145 first conv) vs torch autograd on the same bf16-rounded operands; the bias gradient; the
+    accumulate flag (gradient buckets); bit-reproducible across two calls."""
+    import raygun_b200 as rb
+    from raygun_b200 import conv as CV
+    cin, cout, k, s, p, sp, n = case
+    torch.manual_seed(37)
+    x = _q(torch.randn(n, cin, *sp))
+    w = torch.randn(cout, cin, *k, requires_grad=True)
+    b = torch.zeros(cout, requires_grad=True)
+    y = TF.conv3d(x, w, b, stride=s, padding=p)
+    dy = _q(torch.randn_like(y))
+    y.backward(dy)
+    with rb.precision("bf16"):
+        xg = x.to(DEV).bfloat16()
+        if cin > 1:
+            xg = xg.contiguous(memory_format=torch.channels_last_3d)
+        dyg = dy.to(DEV).bfloat16().contiguous(memory_format=torch.channels_last_3d)
+        before = CV.stats.get("smallk_wgrad", 0)
+        dw, db = CV.conv_wgrad(xg, dyg, tuple(w.shape), s, p, 1, want_bias=True)
+        assert CV.stats.get("smallk_wgrad", 0) == before + 1, "small-K kernel was not taken"
+        dw2, db2 = CV.conv_wgrad(xg, dyg, tuple(w.shape), s, p, 1, want_bias=True)
+        bucket = torch.full(tuple(w.shape), 0.5, device=DEV)
+        CV.conv_wgrad(xg, dyg, tuple(w.shape), s, p, 1, dw_out=bucket, accumulate=True)
+    assert torch.equal(dw, dw2) and torch.equal(db, db2)
+    assert _rel(dw, w.grad) <= 2e-5, _rel(dw, w.grad)
+    assert _rel(db, b.grad) <= 2e-5
+    assert float((bucket - 0.5 - dw).abs().max()) <= 1e-5 * max(1.0, float(dw.abs().max()))
