@@ -342,6 +342,15 @@ class Ctx:
             self.dist.destroy_process_group()
 
 
+def release_cached(ctx):
+    """Hand cached device memory back between workloads -- single-process runs only.  Under the expandable-segments allocator
+    a release unmaps > 100 GB per rank in 20 MB granules, and those driver calls serialise ACROSS processes: the 8-rank run of
+    the default line took > 2x longer with them (the later workloads fit beside the cached cfg4 segments, and the allocator
+    unmaps on demand if they ever do not)."""
+    if ctx.world == 1:
+        torch.cuda.empty_cache()
+
+
 def profile_convs(run_once, ms_step, peaks, traffic_key=None):
     """Per-launch device timing of the tensor-core kernels over one extra (eager) pass: every launch between its own pair
     of CUDA events on the launching stream (`conv.profile` hooks).  A kernel timed alone runs at burst clocks, so the
@@ -365,17 +374,20 @@ def profile_convs(run_once, ms_step, peaks, traffic_key=None):
     dfl, dms, dn = by_kernel[dom]
     achieved = dfl / (dms * 1e-3) / 1e12 if dms > 0 else 0.0
     peak = peaks["tf_burst"]
-    traffic = None
-    try:        # DRAM bytes per launch of that kernel from the committed `ncu --set full` capture (profiles/)
+    traffic = traffic_alg = traffic_src = None
+    try:        # DRAM bytes per launch of that kernel from the committed ncu capture (profiles/)
         with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
             tj = json.load(f)
-        traffic = (tj.get(traffic_key or dom) or tj.get(dom) or {}).get("dram_bytes_per_launch")
+        entry = tj.get(traffic_key or dom) or tj.get(dom) or {}
+        traffic, traffic_alg, traffic_src = (entry.get("dram_bytes_per_launch"), entry.get("algorithmic_bytes_per_launch"),
+                                             entry.get("source"))
     except OSError:
         pass
     tf = lambda v: v[0] / (v[1] * 1e-3) / 1e12 if v[1] > 0 else 0.0
     return dict(bound="tensor", kernel=f"{dom} (tcgen05; {dn} launches per pass)", achieved=achieved, peak=peak, unit="TFLOP/s",
                 frac=achieved / peak, frac_of_sustained=achieved / peaks["tf_sustained"],
                 peak_kind=f"{peaks['source']} burst bf16 (sustained {peaks['tf_sustained']})", traffic=traffic,
+                traffic_algorithmic=traffic_alg, traffic_source=traffic_src,
                 algorithmic_tflop_per_launch=dfl / dn / 1e12, ms_per_launch=dms / dn, share_of_step=dms / ms_step,
                 all_convs=dict(tflops=tf([tot_fl, tot_ms]), frac=tf([tot_fl, tot_ms]) / peak, launches=sum(v[2] for v in by_kind.values()),
                                share_of_step=tot_ms / ms_step),
@@ -496,7 +508,7 @@ def bench_generator_train(args, ctx, workload, steps, warmup, with_cpu=True):
         if with_cpu:
             line["cpu_baseline"] = cpu_line(workload)[0]
     del graph, g, params
-    torch.cuda.empty_cache()
+    release_cached(ctx)
     return line
 
 
@@ -603,7 +615,7 @@ def bench_predict(args, ctx, steps, warmup, with_cpu=True):
         if with_cpu:
             line["cpu_baseline"] = cpu_line("cfg4")[0]
     del g, vol_dev, out_dev, vol, out
-    torch.cuda.empty_cache()
+    release_cached(ctx)
     return line
 
 
@@ -658,12 +670,14 @@ def bench_cyclegan(args, ctx, steps, warmup, with_cpu=True):
         del step
         gc.collect()
         ctx.barrier()
-        torch.cuda.empty_cache()
+        release_cached(ctx)
 
     # the reference's schedule (two retain_graph backward calls = 6 generator traversals, LinkCycleLoss.py:87-135), a few steps
-    ref_step = build(False, not args.no_graph)
-    ms_ref, _, _ = measure(ref_step, min(steps, 5), 3)
-    drop(ref_step)
+    ms_ref = None
+    if world == 1:                 # informational (config.reference_schedule_ms): not repeated in the multi-rank runs
+        ref_step = build(False, not args.no_graph)
+        ms_ref, _, _ = measure(ref_step, min(steps, 5), 3)
+        drop(ref_step)
     # the timed schedule: both generator losses summed and back-propagated once (4 traversals; same gradients)
     step = build(True, not args.no_graph)
     sampler = ClockSampler(ctx.local)
@@ -898,16 +912,17 @@ def main():
         print(json.dumps(gpu_comparator(torch.device("cuda", 0))), flush=True)
         return
     ctx = Ctx()
+    cpu = ctx.world == 1            # the CPU arm is timed on rank 0 of the single-GPU run only (the other ranks would idle)
     if args.workload == "cfg4":
-        line = bench_predict(args, ctx, args.steps, args.warmup)
+        line = bench_predict(args, ctx, args.steps, args.warmup, with_cpu=cpu)
     elif args.workload == "cfg3":
-        line = bench_cyclegan(args, ctx, args.steps, args.warmup)
+        line = bench_cyclegan(args, ctx, args.steps, args.warmup, with_cpu=cpu)
     elif args.workload is not None:
-        line = bench_generator_train(args, ctx, args.workload, args.steps, args.warmup)
+        line = bench_generator_train(args, ctx, args.workload, args.steps, args.warmup, with_cpu=cpu)
     else:
-        line = bench_predict(args, ctx, args.steps, args.warmup)
-        sub3 = bench_cyclegan(args, ctx, args.steps, args.warmup)
-        sub2 = bench_generator_train(args, ctx, "cfg2", args.steps, args.warmup)
+        line = bench_predict(args, ctx, args.steps, args.warmup, with_cpu=cpu)
+        sub3 = bench_cyclegan(args, ctx, args.steps, args.warmup, with_cpu=cpu)
+        sub2 = bench_generator_train(args, ctx, "cfg2", args.steps, args.warmup, with_cpu=cpu)
         if ctx.rank == 0:
             line["cfg3"], line["cfg2"] = sub3, sub2
             if ctx.world == 1 and not args.no_comparator:
