@@ -161,3 +161,41 @@ def test_split_cycle_loss_surface_mirrors_the_reference():
     loss = SplitCycleLoss(nets[0], nets[1], nets[2], nets[3], opt(nets[1]), opt(nets[3]), opt(nets[0], nets[2]), 3)
     assert loss.g_lambda_dict["A"]["l1_loss"] == {"cycled": 10, "identity": 0} and loss.d_lambda_dict["B"]["fake"] == 1
     assert loss.optimizer_G is None and loss.gan_mode == "lsgan"
+
+
+def test_generator_offers_its_head_only_to_networks_that_end_in_conv_activation():
+    """Host logic of the fused network head (cyclegan.Generator._head_request / UNet.last_conv_before_head;
+    BaseSystem.py:209-224): a plain single-head U-Net offers Conv3d(ngf -> output_nc, 1) + final activation to its last
+    convolution; a U-Net with norm layers, a residual U-Net, a ResNet and a head that is not 1x1x1 do not."""
+    import contextlib
+    import functools
+    import io
+    from raygun_b200 import conv as CV
+    from raygun_b200 import nn as L
+    from raygun_b200.cyclegan import Generator, make_generator
+    kw = dict(input_nc=1, output_nc=1, ngf=8, fmap_inc_factor=2, num_downs=3, padding_type="same")
+    with contextlib.redirect_stdout(io.StringIO()):
+        plain = make_generator("unet", dict(kw, final_activation="Tanh"))
+        no_act = make_generator("unet", dict(kw))
+        IN = functools.partial(torch.nn.InstanceNorm3d, affine=False, track_running_stats=False)
+        normed = make_generator("unet", dict(kw, final_activation="Tanh", norm_layer=IN))
+        resid = make_generator("residualunet", dict(kw, final_activation="Tanh"))
+        resnet = make_generator("resnet", dict(input_nc=1, output_nc=1, ngf=8, n_blocks=2, padding_type="same",
+                                               final_activation="Tanh"))
+    assert isinstance(plain, Generator)
+    req = Generator._head_request(plain[0], list(plain)[1:])
+    last = plain[0].last_conv_before_head()
+    assert isinstance(req, CV.HeadRequest) and isinstance(last, L.Conv3d)
+    assert req.weight is last.weight and req.head_w is plain[1].weight and req.act == rb._C.ACT_TANH and not req.done
+    assert last is list(plain[0].r_conv[0][0].conv_pass)[-2]
+    req = Generator._head_request(no_act[0], list(no_act)[1:])
+    assert req is not None and req.act == rb._C.ACT_NONE
+    for g in (normed, resid, resnet):
+        assert Generator._head_request(g[0], list(g)[1:]) is None
+    # a head with a spatial kernel is left alone
+    odd = torch.nn.Sequential(plain[0], L.Conv3d(8, 1, 3, padding=1))
+    assert Generator._head_request(odd[0], list(odd)[1:]) is None
+    # the offer is scoped: nothing is pending outside the context manager
+    with CV.offer_head(CV.HeadRequest(last.weight, plain[1].weight, plain[1].bias)) as r:
+        assert CV._head_request is r
+    assert CV._head_request is None
