@@ -122,3 +122,81 @@ def shard_batch(x: torch.Tensor, rank: int, world: int) -> torch.Tensor:
         raise ValueError(f"global batch {x.shape[0]} is not divisible by world size {world}")
     per = x.shape[0] // world
     return x[rank * per: (rank + 1) * per]
+
+
+# ---------------------------------------------------------------------------------------------
+# Spatial sharding building block (spatial model parallelism for networks whose single sample does not fit
+# one GPU, e.g. Deep-UNet).  NOT wired into the networks and not measured on NVLink: the exchange primitive and its
+# adjoint only, verified under gloo (tests/test_dist_cpu.py).
+# ---------------------------------------------------------------------------------------------
+def _exchange(send_prev, send_next, recv_prev_like, recv_next_like, rank, world, group):
+    """Send `send_prev` to rank - 1 and `send_next` to rank + 1; receive the matching slabs.  Missing neighbours (the two ends
+    of the chain) and empty slabs are skipped.  Returns (from_prev, from_next), None where nothing was received."""
+    ops, from_prev, from_next = [], None, None
+    if rank > 0 and recv_prev_like is not None:
+        from_prev = torch.empty_like(recv_prev_like)
+        ops.append(dist.P2POp(dist.irecv, from_prev, rank - 1, group))
+    if rank + 1 < world and recv_next_like is not None:
+        from_next = torch.empty_like(recv_next_like)
+        ops.append(dist.P2POp(dist.irecv, from_next, rank + 1, group))
+    if rank > 0 and send_prev is not None:
+        ops.append(dist.P2POp(dist.isend, send_prev.contiguous(), rank - 1, group))
+    if rank + 1 < world and send_next is not None:
+        ops.append(dist.P2POp(dist.isend, send_next.contiguous(), rank + 1, group))
+    if ops:
+        for req in dist.batch_isend_irecv(ops):
+            req.wait()
+    return from_prev, from_next
+
+
+class _HaloExchange(torch.autograd.Function):
+    """y = x extended along `dim` by `lo` planes taken from the previous rank's END and `hi` planes from the next rank's START.
+    The two ranks at the ends of the chain get zeros there (the caller applies the network's own padding at the volume faces).
+    Adjoint: the gradient of a halo plane is sent back to the rank that owns the plane and added to it."""
+
+    @staticmethod
+    def forward(ctx, x, dim, lo, hi, group):
+        rank, world = dist.get_rank(group), dist.get_world_size(group)
+        n = x.shape[dim]
+        if max(lo, hi) > n:
+            raise ValueError("halo_exchange: halo wider than the local shard")
+        first = x.narrow(dim, 0, hi) if hi else None             # what the previous rank needs as its high halo
+        last = x.narrow(dim, n - lo, lo) if lo else None          # what the next rank needs as its low halo
+        from_prev, from_next = _exchange(first, last, last, first, rank, world, group)
+        parts = []
+        if lo:
+            parts.append(from_prev if from_prev is not None else torch.zeros_like(last))
+        parts.append(x)
+        if hi:
+            parts.append(from_next if from_next is not None else torch.zeros_like(first))
+        ctx.meta = (dim, lo, hi, group, n)
+        return torch.cat(parts, dim)
+
+    @staticmethod
+    def backward(ctx, g):
+        dim, lo, hi, group, n = ctx.meta
+        rank, world = dist.get_rank(group), dist.get_world_size(group)
+        g_lo = g.narrow(dim, 0, lo) if lo else None               # belongs to the previous rank's last `lo` planes
+        g_hi = g.narrow(dim, lo + n, hi) if hi else None          # belongs to the next rank's first `hi` planes
+        from_prev, from_next = _exchange(g_lo, g_hi, g_hi, g_lo, rank, world, group)
+        gx = g.narrow(dim, lo, n).clone()
+        if from_prev is not None:                                 # the previous rank's high halo = my first `hi` planes
+            gx.narrow(dim, 0, hi).add_(from_prev)
+        if from_next is not None:                                 # the next rank's low halo = my last `lo` planes
+            gx.narrow(dim, n - lo, lo).add_(from_next)
+        return gx, None, None, None, None
+
+
+def halo_exchange(x, dim: int, lo: int, hi: int | None = None, group=None):
+    """Extend the local shard `x` of a tensor that is split in equal chunks along `dim` over the ranks of `group` (rank order =
+    position) by the neighbouring ranks' boundary planes: what a convolution with `lo` / `hi` taps before / after the centre
+    needs in order to produce this rank's outputs exactly as the unsharded layer would.  Differentiable.  World size 1: the
+    zero-extended tensor (identical semantics, no communication)."""
+    hi = lo if hi is None else hi
+    if lo == 0 and hi == 0:
+        return x
+    if not (dist.is_available() and dist.is_initialized()):
+        pad = [0, 0] * x.dim()
+        pad[2 * (x.dim() - 1 - dim)], pad[2 * (x.dim() - 1 - dim) + 1] = lo, hi
+        return torch.nn.functional.pad(x, pad)
+    return _HaloExchange.apply(x, dim, lo, hi, group)

@@ -135,3 +135,59 @@ def test_clip_fit_geometry_and_cost_balanced_partition_of_the_cfg4_grid():
     # equal-cost blocks (the reference's "valid" fit): the partition degenerates to the round robin of rank_blocks
     valid = P.block_list((100, 64, 70), (64,) * 3, (16,) * 3, "valid")
     assert [b.origin for b in P.partition_blocks(valid, 1, 2)] == P.rank_blocks([b.origin for b in valid], 1, 2)
+
+
+def _halo_worker(rank, world, port, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
+                      LOCAL_RANK=str(rank))
+    import torch.nn.functional as TF
+    from raygun_b200.dist import halo_exchange, init_from_env
+    r, w, _ = init_from_env("gloo")
+    torch.manual_seed(3)
+    x = torch.randn(2, 3, 8 * w, 6, 5, dtype=torch.float64)          # full tensor, identical on every rank
+    w1 = torch.randn(4, 3, 3, 3, 3, dtype=torch.float64, requires_grad=True)
+    w2 = torch.randn(2, 4, 5, 1, 1, dtype=torch.float64, requires_grad=True)
+    t = torch.randn(2, 2, 8 * w, 6, 5, dtype=torch.float64)
+
+    def net(xin, sharded):
+        # two 'same' convolutions (zero padding): depth taps come from the neighbours when sharded, from F.pad when not
+        def ext(v, k):
+            return halo_exchange(v, 2, k) if sharded else TF.pad(v, (0, 0, 0, 0, k, k))
+        y = TF.relu(TF.conv3d(ext(xin, 1), w1, padding=(0, 1, 1)))
+        return TF.conv3d(ext(y, 2), w2)
+
+    n = x.shape[2] // w
+    xs = x[:, :, r * n: (r + 1) * n].clone().requires_grad_(True)
+    ys = net(xs, True)
+    loss = ((ys - t[:, :, r * n: (r + 1) * n]) ** 2).sum()
+    loss.backward()
+    g1, g2 = w1.grad.clone(), w2.grad.clone()
+    dist.all_reduce(g1)                                                # weight gradients: sum of the shards' partial sums
+    dist.all_reduce(g2)
+    w1.grad = w2.grad = None
+    xf = x.clone().requires_grad_(True)
+    yf = net(xf, False)
+    ((yf - t) ** 2).sum().backward()
+    err = max(float((ys - yf[:, :, r * n: (r + 1) * n]).abs().max()),
+              float((xs.grad - xf.grad[:, :, r * n: (r + 1) * n]).abs().max()),
+              float((g1 - w1.grad).abs().max()), float((g2 - w2.grad).abs().max()))
+    q.put((r, err))
+    dist.destroy_process_group()
+
+
+def test_halo_exchange_makes_a_depth_sharded_conv_stack_equal_the_unsharded_one_gloo_world2():
+    """dist.halo_exchange (the building block of spatial model parallelism): two stacked convolutions on a tensor
+    split along depth over 2 ranks, halos of 1 and 2 planes -> outputs, input gradients and (all-reduced) weight gradients
+    equal the unsharded computation in float64."""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_halo_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=180) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for r, err in res:
+        assert err < 1e-10, (r, err)
